@@ -1,0 +1,240 @@
+/* libb200sd -- C ABI of the B200-native (sm_100a) Stable Diffusion 2.1 denoising hot path.
+ *
+ * The reference (vin2803/scalable-hw-agnostic-inference) has no FFI and no native code: its hot path is
+ * one Python call, `pipe(**model_args)` (app/run-sd.py:140), into un-vendored diffusers, and its plugin
+ * seam is attribute replacement on the pipeline object (app/run-sd.py:108-134).  Every entry point below
+ * therefore cites the diffusers module / torch op it stands in for and the run-sd.py line through which
+ * the reference reaches it.  The Python host (b200sd/ops.py) binds these with ctypes and registers them
+ * as torch.library ops in namespace `b200sd::`; INTEGRATION.md shows the reference-side binding.
+ *
+ * Conventions
+ *   - C linkage, plain pointers and sizes; no torch / C++ types cross this boundary.
+ *   - every compute entry point is  int32_t fn(const params*, b200sd_stream_t)  -> 0 or a negative
+ *     b200sd_status; b200sd_last_error() gives the thread-local message.
+ *   - entry points never allocate or free device memory, never synchronise the device, never throw.
+ *     All buffers (including scratch, see *_workspace_bytes) are caller-owned device memory that must
+ *     stay alive until `stream` reaches the op.
+ *   - activations are NHWC; "tokens" [n_img, h*w, C] are the same memory as NHWC [n_img, h, w, C].
+ *   - bf16 operands, fp32 accumulation / statistics / softmax / scheduler state.
+ */
+#ifndef B200SD_H_
+#define B200SD_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200SD_ABI_VERSION 1
+
+typedef struct CUstream_st* b200sd_stream_t; /* == cudaStream_t / CUstream */
+
+typedef enum {
+    B200SD_OK = 0,
+    B200SD_ERR_BAD_ARG = -1,
+    B200SD_ERR_UNSUPPORTED = -2,
+    B200SD_ERR_DEVICE = -3,
+    B200SD_ERR_WORKSPACE = -4,
+    B200SD_ERR_CUDA = -5
+} b200sd_status;
+
+typedef enum { B200SD_BF16 = 1, B200SD_F32 = 2 } b200sd_dtype;
+
+/* ---- library / device ------------------------------------------------------------------------ */
+/* no reference counterpart (the reference never checks the device: app/run-sd.py:107 hard-codes "cuda") */
+int32_t b200sd_abi_version(void);
+const char* b200sd_last_error(void);
+/* 0 iff device `dev` is compute capability 10.x (sm_100a cubins load there) */
+int32_t b200sd_check_device(int32_t dev);
+/* number of kernel launches issued by this library in this process (bench.py's gpu_launches) */
+int64_t b200sd_launch_count(void);
+
+/* ---- K1/K2: implicit-GEMM conv3x3 / conv1x1 / linear on tcgen05 + TMEM, fed by TMA --------------
+ * Replaces torch.nn.Conv2d (3x3 pad 1 stride 1, and 1x1) and torch.nn.Linear inside diffusers'
+ * ResnetBlock2D / Transformer2DModel / Attention / FeedForward / Decoder, which the reference reaches
+ * through pipe.unet(...) and pipe.vae.decode(...) (app/run-sd.py:110-116,124-134,140).
+ *   out[m, n] = epilogue( sum_{tap,c} A[pixel(m)+offset(tap), c] * W[n, tap*cin + c] )
+ * A is an NHWC bf16 activation; a plain [M,K] matrix is n_img=1, img_h=1, img_w=M, cin=K, taps=1.
+ * epilogue: + bias[n]  + row_bias[img(m)*row_bias_stride + n]  + residual[m, n]  then optional GEGLU.
+ */
+typedef struct {
+    const void* a;          /* bf16 NHWC [n_img, img_h, img_w, cin]; 16-byte aligned; cin % 8 == 0 */
+    int32_t n_img, img_h, img_w, cin;
+    int32_t taps;           /* 1 or 9 */
+    const void* w;          /* bf16 [n_out, taps*cin], K contiguous, K order = (tap, c)  (KRSC) */
+    int32_t n_out;
+    const float* bias;      /* fp32 [n_out] (or [M] when bias_along_m), may be NULL */
+    int32_t bias_along_m;
+    const float* row_bias;  /* fp32, per-image additive row (timestep-embedding projection), may be NULL */
+    int64_t row_bias_stride;/* elements between consecutive images; 0 broadcasts one row */
+    const void* residual;   /* [M, ld_res] of residual_dtype, may be NULL; may alias `out` */
+    int32_t residual_dtype;
+    int64_t ld_res;
+    void* out;              /* [M, ld_out] of out_dtype (GEGLU: n_out/2 columns are written) */
+    int32_t out_dtype;
+    int64_t ld_out;
+    int32_t geglu;          /* 1: out[m,j] = val_j * gelu_erf(gate_j); weight/bias rows interleaved per block_n
+                               tile by b200sd_pack_geglu_rows (first half of a tile = values, second = gates) */
+    int32_t block_n;        /* 0 = choose; else one of 64, 128, 160, 256 */
+} b200sd_gemm_params;
+int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stream);
+/* the block_n the library would choose for this problem (weight packers for GEGLU need it) */
+int32_t b200sd_gemm_pick_block_n(int32_t n_out, int32_t geglu);
+
+/* ---- K3: fused flash attention, head_dim 64, tcgen05 QK^T / PV, online softmax in registers -----
+ * Replaces diffusers Attention (attn1 self-attention and attn2 cross-attention of BasicTransformerBlock),
+ * which the reference runs through SlicedAttnProcessor because of pipe.enable_attention_slicing()
+ * (app/run-sd.py:135).  Row r of batch b is q[(b*sq + r)*ld_q + h*64 + d]; same for k/v with skv.
+ */
+typedef struct {
+    const void *q, *k, *v;  /* bf16 */
+    int64_t ld_q, ld_k, ld_v;
+    void* out;              /* bf16 [batch*sq, ld_out], head h at columns h*64 */
+    int64_t ld_out;
+    int32_t batch, heads, head_dim; /* head_dim must be 64 */
+    int32_t sq, skv;
+    float scale;            /* softmax(scale * q.k) */
+} b200sd_attention_params;
+int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_stream_t stream);
+
+/* ---- K1b: GroupNorm(32) (+SiLU) over NHWC, optional channel-concat of two inputs ------------------
+ * Replaces torch.nn.GroupNorm + F.silu in ResnetBlock2D.norm1/norm2, Transformer2DModel.norm,
+ * conv_norm_out, and the torch.cat([h, skip], dim=1) feeding up-block resnets (via pipe.unet /
+ * pipe.vae.decoder, app/run-sd.py:110-116,124-128).  Two kernels: deterministic split statistics into
+ * `workspace`, then normalise+affine(+SiLU) -> bf16.  `raw` (optional) receives the un-normalised bf16
+ * concat, the A operand of the 1x1 conv_shortcut.
+ */
+typedef struct {
+    const void* x1;         /* [n_img, hw, c1] of in_dtype */
+    int32_t c1;
+    const void* x2;         /* [n_img, hw, c2] or NULL */
+    int32_t c2;
+    int32_t in_dtype;
+    int32_t n_img, hw, groups;
+    float eps;
+    const float *gamma, *beta; /* fp32 [c1+c2] */
+    int32_t silu;
+    void* y;                /* bf16 [n_img, hw, c1+c2] */
+    void* raw;              /* bf16 [n_img, hw, c1+c2] or NULL */
+    float* workspace;
+    int64_t workspace_bytes;
+} b200sd_groupnorm_params;
+int64_t b200sd_groupnorm_workspace_bytes(const b200sd_groupnorm_params* p);
+int32_t b200sd_groupnorm(const b200sd_groupnorm_params* p, b200sd_stream_t stream);
+
+/* ---- LayerNorm over the last dim -> bf16 (BasicTransformerBlock.norm1/2/3) -------------------------- */
+typedef struct {
+    const void* x;          /* [rows, cols] of in_dtype, contiguous */
+    int32_t in_dtype;
+    int64_t rows;
+    int32_t cols;
+    float eps;
+    const float *gamma, *beta;
+    void* y;                /* bf16 [rows, cols] */
+} b200sd_layernorm_params;
+int32_t b200sd_layernorm(const b200sd_layernorm_params* p, b200sd_stream_t stream);
+
+/* ---- im2col for the convs TMA cannot tile: stride-2 Downsample2D and the 4-channel conv_in ---------
+ * out[m, (r*3+s)*cin + c] = x[(n % n_src), oy*stride + r - 1, ox*stride + s - 1, c]   (0 outside, 0 for k >= 9*cin)
+ * n % n_src lets the CFG pair (uncond, cond) share one latent: n_img = 2B, n_src = B.
+ */
+typedef struct {
+    const void* x;          /* NHWC [n_src, in_h, in_w, cin] of in_dtype */
+    int32_t in_dtype;
+    int32_t n_img, n_src, in_h, in_w, cin, stride;
+    void* out;              /* bf16 [n_img*out_h*out_w, k_pad], k_pad >= 9*cin, k_pad % 8 == 0 */
+    int32_t k_pad;
+} b200sd_im2col_params;
+int32_t b200sd_im2col3x3(const b200sd_im2col_params* p, b200sd_stream_t stream);
+
+/* ---- nearest-neighbour 2x upsample NHWC -> bf16 (Upsample2D's F.interpolate) ---------------------- */
+typedef struct {
+    const void* x;          /* [n_img, h, w, c] of in_dtype */
+    int32_t in_dtype;
+    int32_t n_img, h, w, c;
+    void* out;              /* bf16 [n_img, 2h, 2w, c] */
+} b200sd_upsample_params;
+int32_t b200sd_upsample2x(const b200sd_upsample_params* p, b200sd_stream_t stream);
+
+/* ---- K4: classifier-free guidance + scheduler step, one pass -----------------------------------------
+ * Replaces, per denoising step, `noise_pred_uncond + g*(noise_pred_text - noise_pred_uncond)` and
+ * DDIMScheduler.step (forced at app/run-sd.py:108) / DPMSolverMultistep / EulerDiscrete (BASELINE.json)
+ * inside StableDiffusionPipeline.__call__ (app/run-sd.py:140):
+ *   m = u + g (c - u);  x0 = ax x + am m;  x' = cx x + cm m + cp x0_prev
+ * coefficients: fp32[6] = {g, cx, cm, cp, ax, am} read from DEVICE memory at coef[step_index*6] so that a
+ * CUDA graph of the step can be replayed for every timestep.  eps2 = [2B, ...] (uncond first), any layout
+ * shared by all operands.  x is updated in place; x0_prev (optional) is read then overwritten with x0.
+ */
+typedef struct {
+    const void* eps2;       /* [2*n] of eps_dtype: first n uncond, last n cond */
+    int32_t eps_dtype;
+    float* x;               /* fp32 [n], in place */
+    float* x0_prev;         /* fp32 [n] or NULL */
+    const float* coef;      /* device fp32 [6 * n_steps] */
+    const int32_t* step_index; /* device int32 scalar, or NULL for step 0 */
+    int64_t n;
+} b200sd_cfg_sched_params;
+int32_t b200sd_cfg_sched_step(const b200sd_cfg_sched_params* p, b200sd_stream_t stream);
+
+/* ---- K5: small-M linear for the timestep path -----------------------------------------------------------
+ * y[m, n] = act_out( sum_k act_in(x[m,k]) * w[n,k] + b[n] ),  m < 64.  Used for Timesteps (sinusoid, when
+ * `sinusoid_dim` > 0 x is a device fp32 [rows] vector of timesteps), TimestepEmbedding.linear_1/2 and the 22
+ * ResnetBlock2D.time_emb_proj (batched into one weight), all inside pipe.unet (app/run-sd.py:140).
+ */
+typedef struct {
+    const float* x;         /* fp32 [rows, k]   (or fp32 [rows] timesteps when sinusoid_dim > 0) */
+    int32_t rows, k, n;
+    int32_t sinusoid_dim;   /* 0, or == k: x[m] -> cat(cos, sin)(x[m] * 10000^(-i/(k/2))) */
+    int32_t silu_in, silu_out;
+    const void* w;          /* bf16 [n, k] */
+    const float* b;         /* fp32 [n] or NULL */
+    float* y;               /* fp32 [rows, n] */
+} b200sd_small_linear_params;
+int32_t b200sd_small_linear(const b200sd_small_linear_params* p, b200sd_stream_t stream);
+
+/* ---- row softmax y = softmax(scale * x) -> bf16 (VAE mid-block attention, 1 head x 512) ------------------
+ * x may be fp32 or bf16; y may alias x when x is bf16. */
+typedef struct {
+    const void* x;          /* [rows, ld_in] of in_dtype, first `cols` of each row are live */
+    int32_t in_dtype;
+    int64_t ld_in;
+    void* y;                /* bf16 [rows, ld_out] */
+    int64_t ld_out;
+    int64_t rows;
+    int32_t cols;
+    float scale;
+} b200sd_softmax_params;
+int32_t b200sd_softmax_rows(const b200sd_softmax_params* p, b200sd_stream_t stream);
+
+/* ---- K7: VaeImageProcessor.postprocess on device: (x/2+0.5).clamp(0,1)*255 round -> uint8 -------------
+ * (the reference does this on the CPU after a fp32 D2H copy; app/run-sd.py:140 `.images[0]`, :177-181) */
+typedef struct {
+    const void* x;          /* [n] of in_dtype */
+    int32_t in_dtype;
+    uint8_t* out;           /* [n] */
+    int64_t n;
+} b200sd_denorm_u8_params;
+int32_t b200sd_denorm_u8(const b200sd_denorm_u8_params* p, b200sd_stream_t stream);
+
+/* ---- dtype cast fp32 <-> bf16 (boundary tensors) -------------------------------------------------------- */
+typedef struct {
+    const void* x;
+    int32_t in_dtype;
+    void* y;
+    int32_t out_dtype;
+    int64_t n;
+} b200sd_cast_params;
+int32_t b200sd_cast(const b200sd_cast_params* p, b200sd_stream_t stream);
+
+/* ---- UMMA self-test: one 128 x n x 64k tile product with the B operand K-major or MN-major ---------------
+ * no reference counterpart; used by tests to pin the shared-memory descriptor encodings on real hardware. */
+int32_t b200sd_umma_selftest(const void* a_bf16 /*[128,k]*/, const void* b_bf16 /*[n,k] or [k,n]*/,
+                             float* d /*[128,n]*/, int32_t n, int32_t k, int32_t b_mn_major,
+                             b200sd_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SD_H_ */

@@ -1,0 +1,215 @@
+"""torch.library ops `b200sd::*` over the C ABI of libb200sd.so (include/b200sd.h).
+
+Every op is an out-variant: the caller (torch) owns all device memory, the library only launches kernels
+on torch's current CUDA stream.  CUDA only -- there is deliberately no CPU implementation.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib as L
+
+_DT = {torch.bfloat16: L.BF16, torch.float32: L.F32}
+
+
+def _dt(t: torch.Tensor) -> int:
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise TypeError(f"b200sd: unsupported dtype {t.dtype}") from None
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("b200sd ops are CUDA-only (no CPU fallback); got a CPU tensor")
+    return t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def launch_count() -> int:
+    return int(L.load().b200sd_launch_count())
+
+
+def check_device(dev: int = 0) -> None:
+    L.check(L.load().b200sd_check_device(dev), "check_device")
+
+
+def pick_block_n(n_out: int, geglu: bool) -> int:
+    return int(L.load().b200sd_gemm_pick_block_n(n_out, int(geglu)))
+
+
+# ------------------------------------------------------------------------------------------------ impls
+def _gemm(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, row_bias_stride, residual, out,
+          geglu, block_n):
+    assert a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
+    p = L.GemmParams()
+    p.a, p.n_img, p.img_h, p.img_w, p.cin, p.taps = _ptr(a), n_img, img_h, img_w, cin, taps
+    p.w, p.n_out = _ptr(w), w.shape[0]
+    assert w.shape[1] == taps * cin, (tuple(w.shape), taps, cin)
+    p.bias, p.bias_along_m = _ptr(bias), int(bias_along_m)
+    p.row_bias, p.row_bias_stride = _ptr(row_bias), row_bias_stride
+    if residual is not None:
+        p.residual, p.residual_dtype, p.ld_res = _ptr(residual), _dt(residual), residual.stride(-2)
+    p.out, p.out_dtype, p.ld_out = _ptr(out), _dt(out), out.stride(-2)
+    p.geglu, p.block_n = int(geglu), block_n
+    L.check(L.load().b200sd_gemm(C.byref(p), _stream()), "gemm")
+
+
+def _attention(q, k, v, out, batch, heads, sq, skv, scale):
+    p = L.AttentionParams()
+    p.q, p.k, p.v, p.out = _ptr(q), _ptr(k), _ptr(v), _ptr(out)
+    p.ld_q, p.ld_k, p.ld_v, p.ld_out = q.stride(-2), k.stride(-2), v.stride(-2), out.stride(-2)
+    p.batch, p.heads, p.head_dim, p.sq, p.skv, p.scale = batch, heads, 64, sq, skv, scale
+    L.check(L.load().b200sd_attention(C.byref(p), _stream()), "attention")
+
+
+def _gn_params(x1, x2, n_img, hw, groups, eps, gamma, beta, silu, y, raw, workspace):
+    p = L.GroupNormParams()
+    p.x1, p.c1 = _ptr(x1), x1.shape[-1]
+    p.x2, p.c2 = (_ptr(x2), x2.shape[-1]) if x2 is not None else (None, 0)
+    p.in_dtype, p.n_img, p.hw, p.groups, p.eps = _dt(x1), n_img, hw, groups, eps
+    p.gamma, p.beta, p.silu = _ptr(gamma), _ptr(beta), int(silu)
+    p.y, p.raw = _ptr(y), _ptr(raw)
+    if workspace is not None:
+        p.workspace, p.workspace_bytes = _ptr(workspace), workspace.numel() * workspace.element_size()
+    return p
+
+
+def groupnorm_workspace_bytes(n_img: int, hw: int, groups: int = 32) -> int:
+    p = L.GroupNormParams()
+    p.n_img, p.hw, p.groups = n_img, hw, groups
+    return int(L.load().b200sd_groupnorm_workspace_bytes(C.byref(p)))
+
+
+def _groupnorm(x1, x2, n_img, hw, groups, eps, gamma, beta, silu, y, raw, workspace):
+    if x2 is not None:
+        assert x2.dtype == x1.dtype
+    p = _gn_params(x1, x2, n_img, hw, groups, eps, gamma, beta, silu, y, raw, workspace)
+    L.check(L.load().b200sd_groupnorm(C.byref(p), _stream()), "groupnorm")
+
+
+def _layernorm(x, eps, gamma, beta, y):
+    p = L.LayerNormParams()
+    p.x, p.in_dtype, p.rows, p.cols, p.eps = _ptr(x), _dt(x), x.numel() // x.shape[-1], x.shape[-1], eps
+    p.gamma, p.beta, p.y = _ptr(gamma), _ptr(beta), _ptr(y)
+    L.check(L.load().b200sd_layernorm(C.byref(p), _stream()), "layernorm")
+
+
+def _im2col3x3(x, n_img, n_src, in_h, in_w, cin, stride, out):
+    p = L.Im2colParams()
+    p.x, p.in_dtype, p.n_img, p.n_src, p.in_h, p.in_w, p.cin, p.stride = _ptr(x), _dt(x), n_img, n_src, in_h, in_w, cin, stride
+    p.out, p.k_pad = _ptr(out), out.shape[-1]
+    L.check(L.load().b200sd_im2col3x3(C.byref(p), _stream()), "im2col3x3")
+
+
+def _upsample2x(x, n_img, h, w, c, out):
+    p = L.UpsampleParams()
+    p.x, p.in_dtype, p.n_img, p.h, p.w, p.c, p.out = _ptr(x), _dt(x), n_img, h, w, c, _ptr(out)
+    L.check(L.load().b200sd_upsample2x(C.byref(p), _stream()), "upsample2x")
+
+
+def _cfg_sched_step(eps2, x, x0_prev, coef, step_index):
+    p = L.CfgSchedParams()
+    p.eps2, p.eps_dtype, p.x, p.x0_prev = _ptr(eps2), _dt(eps2), _ptr(x), _ptr(x0_prev)
+    p.coef, p.step_index, p.n = _ptr(coef), _ptr(step_index), x.numel()
+    assert eps2.numel() == 2 * x.numel() and x.dtype == torch.float32 and coef.dtype == torch.float32
+    assert step_index is None or step_index.dtype == torch.int32
+    L.check(L.load().b200sd_cfg_sched_step(C.byref(p), _stream()), "cfg_sched_step")
+
+
+def _small_linear(x, rows, k, sinusoid_dim, silu_in, silu_out, w, b, y):
+    p = L.SmallLinearParams()
+    p.x, p.rows, p.k, p.n = _ptr(x), rows, k, w.shape[0]
+    p.sinusoid_dim, p.silu_in, p.silu_out = sinusoid_dim, int(silu_in), int(silu_out)
+    p.w, p.b, p.y = _ptr(w), _ptr(b), _ptr(y)
+    assert x.dtype == torch.float32 and w.dtype == torch.bfloat16 and y.dtype == torch.float32 and w.shape[1] == k
+    L.check(L.load().b200sd_small_linear(C.byref(p), _stream()), "small_linear")
+
+
+def _softmax_rows(x, y, rows, cols, scale):
+    p = L.SoftmaxParams()
+    p.x, p.in_dtype, p.ld_in, p.y, p.ld_out = _ptr(x), _dt(x), x.stride(-2), _ptr(y), y.stride(-2)
+    p.rows, p.cols, p.scale = rows, cols, scale
+    assert y.dtype == torch.bfloat16
+    L.check(L.load().b200sd_softmax_rows(C.byref(p), _stream()), "softmax_rows")
+
+
+def _denorm_u8(x, out):
+    p = L.DenormU8Params()
+    p.x, p.in_dtype, p.out, p.n = _ptr(x), _dt(x), _ptr(out), x.numel()
+    assert out.dtype == torch.uint8 and out.numel() == x.numel()
+    L.check(L.load().b200sd_denorm_u8(C.byref(p), _stream()), "denorm_u8")
+
+
+def _cast(x, y):
+    p = L.CastParams()
+    p.x, p.in_dtype, p.y, p.out_dtype, p.n = _ptr(x), _dt(x), _ptr(y), _dt(y), x.numel()
+    L.check(L.load().b200sd_cast(C.byref(p), _stream()), "cast")
+
+
+def umma_selftest(a: torch.Tensor, b: torch.Tensor, b_mn_major: bool) -> torch.Tensor:
+    """D[128,n] = A[128,k] @ B^T (B [n,k]) or A @ B (B [k,n], MN-major); pins the UMMA descriptor encodings."""
+    k = a.shape[1]
+    n = b.shape[1] if b_mn_major else b.shape[0]
+    d = torch.empty(128, n, device=a.device, dtype=torch.float32)
+    L.check(L.load().b200sd_umma_selftest(_ptr(a), _ptr(b), _ptr(d), n, k, int(b_mn_major), _stream()), "umma_selftest")
+    return d
+
+
+# ------------------------------------------------------------------------------------------------ registration
+_SCHEMAS = {
+    "gemm": ("(Tensor a, int n_img, int img_h, int img_w, int cin, int taps, Tensor w, Tensor? bias, bool bias_along_m, "
+             "Tensor? row_bias, int row_bias_stride, Tensor? residual, Tensor(a!) out, bool geglu, int block_n) -> ()", _gemm),
+    "attention": ("(Tensor q, Tensor k, Tensor v, Tensor(a!) out, int batch, int heads, int sq, int skv, float scale) -> ()",
+                  _attention),
+    "groupnorm": ("(Tensor x1, Tensor? x2, int n_img, int hw, int groups, float eps, Tensor gamma, Tensor beta, bool silu, "
+                  "Tensor(a!) y, Tensor(b!)? raw, Tensor(c!) workspace) -> ()", _groupnorm),
+    "layernorm": ("(Tensor x, float eps, Tensor gamma, Tensor beta, Tensor(a!) y) -> ()", _layernorm),
+    "im2col3x3": ("(Tensor x, int n_img, int n_src, int in_h, int in_w, int cin, int stride, Tensor(a!) out) -> ()",
+                  _im2col3x3),
+    "upsample2x": ("(Tensor x, int n_img, int h, int w, int c, Tensor(a!) out) -> ()", _upsample2x),
+    "cfg_sched_step": ("(Tensor eps2, Tensor(a!) x, Tensor(b!)? x0_prev, Tensor coef, Tensor? step_index) -> ()",
+                       _cfg_sched_step),
+    "small_linear": ("(Tensor x, int rows, int k, int sinusoid_dim, bool silu_in, bool silu_out, Tensor w, Tensor? b, "
+                     "Tensor(a!) y) -> ()", _small_linear),
+    "softmax_rows": ("(Tensor x, Tensor(a!) y, int rows, int cols, float scale) -> ()", _softmax_rows),
+    "denorm_u8": ("(Tensor x, Tensor(a!) out) -> ()", _denorm_u8),
+    "cast": ("(Tensor x, Tensor(a!) y) -> ()", _cast),
+}
+
+_library = None
+
+
+def _register() -> None:
+    global _library
+    if _library is not None:
+        return
+    lib = torch.library.Library("b200sd", "DEF")
+    for name, (schema, fn) in _SCHEMAS.items():
+        lib.define(name + schema)
+        lib.impl(name, fn, "CUDA")
+        # out-variants: shape inference has nothing to compute
+        lib.impl(name, (lambda *a, **k: None), "Meta")
+    _library = lib
+
+
+_register()
+gemm = torch.ops.b200sd.gemm
+attention = torch.ops.b200sd.attention
+groupnorm = torch.ops.b200sd.groupnorm
+layernorm = torch.ops.b200sd.layernorm
+im2col3x3 = torch.ops.b200sd.im2col3x3
+upsample2x = torch.ops.b200sd.upsample2x
+cfg_sched_step = torch.ops.b200sd.cfg_sched_step
+small_linear = torch.ops.b200sd.small_linear
+softmax_rows = torch.ops.b200sd.softmax_rows
+denorm_u8 = torch.ops.b200sd.denorm_u8
+cast = torch.ops.b200sd.cast

@@ -1,0 +1,306 @@
+// K3: fused flash attention for head_dim 64 on sm_100a (self- and cross-attention of BasicTransformerBlock).
+//
+//   warp 0      TMA producer : Q tile once, then K/V tiles (128 kv rows x 64) through a 3-stage ring
+//   warp 1      UMMA issuer  : S = Q K^T (128x128x64) into a double-buffered TMEM tile,
+//                              O += P V (128x64x128) with P from shared memory and V as an MN-major operand
+//   warps 2..5  softmax      : one query row per thread (tcgen05.ld 32x32b => no cross-lane reductions),
+//                              exp2 with the scale folded in, lazy rescale of O (only when the running max
+//                              grows by more than 2^8), P written as bf16 into the SWIZZLE_128B layout
+//
+// The S x S score matrix never leaves the SM.  FLOPs per launch: 4 * batch * heads * sq * skv * 64.
+#include "common.h"
+#include "ptx.cuh"
+
+namespace b200sd {
+using namespace ptx;
+
+constexpr int ATT_BM = 128;
+constexpr int ATT_BN = 128;
+constexpr int ATT_D = 64;
+constexpr int ATT_STAGES = 3;
+constexpr int ATT_TILE = 128 * 128;  // bytes of a [128 x 64] bf16 tile
+constexpr int ATT_THREADS = 192;
+constexpr int ATT_SMEM = ATT_TILE /*Q*/ + ATT_STAGES * 2 * ATT_TILE /*K,V*/ + 2 * 2 * ATT_TILE /*P x2*/ + 1024 + 256;
+constexpr uint32_t ATT_TMEM_S0 = 0, ATT_TMEM_S1 = 128, ATT_TMEM_O = 256;
+
+struct AttnKernelParams {
+    int sq, skv, n_kv_tiles;
+    float scale_log2;  // scale * log2(e)
+    __nv_bfloat16* out;
+    long long ld_out;
+};
+
+__global__ void __launch_bounds__(ATT_THREADS, 1)
+    attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                     const __grid_constant__ CUtensorMap tmV, const AttnKernelParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+    uint8_t* sQ = smem;
+    uint8_t* sKV = sQ + ATT_TILE;                       // stage s: K at s*2*TILE, V at s*2*TILE + TILE
+    uint8_t* sP = sKV + ATT_STAGES * 2 * ATT_TILE;      // buffer b at b*2*TILE; two 64-wide kv chunks each
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * 2 * ATT_TILE);
+    uint64_t* q_full = bars;
+    uint64_t* kv_full = bars + 1;
+    uint64_t* kv_empty = kv_full + ATT_STAGES;
+    uint64_t* s_full = kv_empty + ATT_STAGES;  // [2] UMMA -> softmax : S tile ready
+    uint64_t* s_free = s_full + 2;             // [2] softmax -> UMMA : S tile read out
+    uint64_t* p_full = s_free + 2;             // [2] softmax -> UMMA : P tile written (and O rescaled)
+    uint64_t* pv_done = p_full + 2;            // [2] UMMA -> softmax : O += P V finished
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q0 = blockIdx.x * ATT_BM;
+    const int head = blockIdx.y, b = blockIdx.z;
+    const int n_tiles = p.n_kv_tiles;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmQ);
+        prefetch_tmap(&tmK);
+        prefetch_tmap(&tmV);
+    }
+    if (warp == 1 && lane == 0) {
+        mbar_init(q_full, 1);
+        for (int s = 0; s < ATT_STAGES; ++s) mbar_init(&kv_full[s], 1), mbar_init(&kv_empty[s], 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&s_full[s], 1);
+            mbar_init(&s_free[s], 4);
+            mbar_init(&p_full[s], 4);
+            mbar_init(&pv_done[s], 1);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(q_full, ATT_TILE);
+            tma_load_2d(sQ, &tmQ, q_full, head * ATT_D, b * p.sq + q0);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int j = 0; j < n_tiles; ++j) {
+                mbar_wait(&kv_empty[stage], phase ^ 1);
+                uint8_t* sk = sKV + stage * 2 * ATT_TILE;
+                mbar_expect_tx(&kv_full[stage], 2 * ATT_TILE);
+                tma_load_2d(sk, &tmK, &kv_full[stage], head * ATT_D, b * p.skv + j * ATT_BN);
+                tma_load_2d(sk + ATT_TILE, &tmV, &kv_full[stage], head * ATT_D, b * p.skv + j * ATT_BN);
+                if (++stage == ATT_STAGES) stage = 0, phase ^= 1;
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc_qk = umma_idesc_bf16(128, ATT_BN, 0, 0);
+            constexpr uint32_t idesc_pv = umma_idesc_bf16(128, ATT_D, 0, 1);  // V is MN-major
+            const uint32_t q_addr = smem_u32(sQ);
+            auto issue_qk = [&](int j, int stage) {
+                const uint32_t k_addr = smem_u32(sKV + stage * 2 * ATT_TILE);
+                const uint32_t d = tmem_base + ((j & 1) ? ATT_TMEM_S1 : ATT_TMEM_S0);
+#pragma unroll
+                for (int ks = 0; ks < ATT_D / 16; ++ks)
+                    umma_bf16(d, umma_desc_sw128(q_addr + ks * 32), umma_desc_sw128(k_addr + ks * 32), idesc_qk,
+                              ks != 0);
+                umma_commit(&s_full[j & 1]);
+            };
+            mbar_wait(q_full, 0);
+            mbar_wait(&kv_full[0], 0);
+            tc_fence_after();
+            issue_qk(0, 0);
+            int stage = 0;       // stage of tile j
+            uint32_t phase = 0;  // phase of tile j's stage
+            for (int j = 0; j < n_tiles; ++j) {
+                int nstage = stage + 1;
+                uint32_t nphase = phase;
+                if (nstage == ATT_STAGES) nstage = 0, nphase ^= 1;
+                if (j + 1 < n_tiles) {
+                    mbar_wait(&kv_full[nstage], nphase);
+                    if (j + 1 >= 2) mbar_wait(&s_free[(j + 1) & 1], (((j + 1) >> 1) - 1) & 1);
+                    tc_fence_after();
+                    issue_qk(j + 1, nstage);
+                }
+                mbar_wait(&p_full[j & 1], (j >> 1) & 1);
+                tc_fence_after();
+                const uint32_t p_addr = smem_u32(sP + (j & 1) * 2 * ATT_TILE);
+                const uint32_t v_addr = smem_u32(sKV + stage * 2 * ATT_TILE + ATT_TILE);
+#pragma unroll
+                for (int ks = 0; ks < ATT_BN / 16; ++ks) {
+                    const uint64_t adesc = umma_desc_sw128(p_addr + (ks >> 2) * ATT_TILE + (ks & 3) * 32);
+                    const uint64_t bdesc = umma_desc_sw128(v_addr + ks * 2048, /*lbo*/ 128 * 128, /*sbo*/ 1024);
+                    umma_bf16(tmem_base + ATT_TMEM_O, adesc, bdesc, idesc_pv, (j | ks) != 0);
+                }
+                umma_commit(&kv_empty[stage]);
+                umma_commit(&pv_done[j & 1]);
+                stage = nstage, phase = nphase;
+            }
+        }
+        __syncwarp();
+    } else {
+        // ---------------------------------------------------------------- softmax + output (128 threads)
+        const int quad = warp & 3;
+        const int row = quad * 32 + lane;
+        const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
+        float m_used = 0.f, l = 0.f;
+        for (int j = 0; j < n_tiles; ++j) {
+            mbar_wait(&s_full[j & 1], (j >> 1) & 1);
+            tc_fence_after();
+            uint32_t s[4][32];
+            const uint32_t s_addr = tmem_base + ((j & 1) ? ATT_TMEM_S1 : ATT_TMEM_S0) + lane_off;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) tmem_ld_x32(s_addr + c * 32, s[c]);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_free[j & 1]);
+
+            const int valid = min(ATT_BN, p.skv - j * ATT_BN);  // live kv columns of this tile
+            float mx = -INFINITY;
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const float v = (c * 32 + i < valid) ? __uint_as_float(s[c][i]) : -INFINITY;
+                    mx = fmaxf(mx, v);
+                }
+            const float m_new = mx * p.scale_log2;
+            float alpha = 1.f;
+            bool need = false;
+            if (j == 0) {
+                m_used = m_new;
+            } else if (m_new > m_used + 8.0f) {
+                alpha = exp2f(m_used - m_new);
+                m_used = m_new;
+                need = true;
+            }
+            if (__any_sync(0xffffffffu, need)) {
+                // O holds tiles 0..j-1 once PV(j-1) has completed
+                mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);
+                tc_fence_after();
+                l *= alpha;
+#pragma unroll
+                for (int c = 0; c < ATT_D / 16; ++c) {
+                    uint32_t o[16];
+                    tmem_ld_x16(tmem_base + ATT_TMEM_O + lane_off + c * 16, o);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                    tmem_st_x16(tmem_base + ATT_TMEM_O + lane_off + c * 16, o);
+                }
+                tmem_st_wait();
+            }
+            // P buffer (j&1) was last read by PV(j-2)
+            if (j >= 2) mbar_wait(&pv_done[j & 1], ((j >> 1) - 1) & 1);
+            uint8_t* prow = sP + (j & 1) * 2 * ATT_TILE + row * 128;
+            float lsum = 0.f;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    float e[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int col = c * 32 + g * 8 + i;
+                        const float v = exp2f(__uint_as_float(s[c][g * 8 + i]) * p.scale_log2 - m_used);
+                        e[i] = (col < valid) ? v : 0.f;
+                        lsum += e[i];
+                    }
+                    const int col0 = c * 32 + g * 8;
+                    const int chunk = col0 >> 6;             // which 64-wide kv chunk
+                    const int cc = (col0 & 63) >> 3;         // 16-byte chunk inside the 128-byte row
+                    *reinterpret_cast<uint4*>(prow + chunk * ATT_TILE + ((cc ^ (row & 7)) << 4)) =
+                        make_uint4(pack_bf16x2(e[0], e[1]), pack_bf16x2(e[2], e[3]), pack_bf16x2(e[4], e[5]),
+                                   pack_bf16x2(e[6], e[7]));
+                }
+            }
+            l += lsum;
+            fence_proxy_async_smem();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[j & 1]);
+        }
+        // ---- epilogue: O / l -> bf16
+        const int last = n_tiles - 1;
+        mbar_wait(&pv_done[last & 1], (last >> 1) & 1);
+        tc_fence_after();
+        const float inv = 1.0f / l;
+        const int qrow = q0 + row;
+        __nv_bfloat16* orow = p.out + ((long long)b * p.sq + qrow) * p.ld_out + head * ATT_D;
+#pragma unroll
+        for (int c = 0; c < ATT_D / 16; ++c) {
+            uint32_t o[16];
+            tmem_ld_x16(tmem_base + ATT_TMEM_O + lane_off + c * 16, o);
+            tmem_ld_wait();
+            if (qrow < p.sq) {
+                uint4 v0 = make_uint4(pack_bf16x2(__uint_as_float(o[0]) * inv, __uint_as_float(o[1]) * inv),
+                                      pack_bf16x2(__uint_as_float(o[2]) * inv, __uint_as_float(o[3]) * inv),
+                                      pack_bf16x2(__uint_as_float(o[4]) * inv, __uint_as_float(o[5]) * inv),
+                                      pack_bf16x2(__uint_as_float(o[6]) * inv, __uint_as_float(o[7]) * inv));
+                uint4 v1 = make_uint4(pack_bf16x2(__uint_as_float(o[8]) * inv, __uint_as_float(o[9]) * inv),
+                                      pack_bf16x2(__uint_as_float(o[10]) * inv, __uint_as_float(o[11]) * inv),
+                                      pack_bf16x2(__uint_as_float(o[12]) * inv, __uint_as_float(o[13]) * inv),
+                                      pack_bf16x2(__uint_as_float(o[14]) * inv, __uint_as_float(o[15]) * inv));
+                *reinterpret_cast<uint4*>(orow + c * 16) = v0;
+                *reinterpret_cast<uint4*>(orow + c * 16 + 8) = v1;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace b200sd
+
+using namespace b200sd;
+
+extern "C" int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_stream_t stream) {
+    B200SD_CHECK_ARG(p && p->q && p->k && p->v && p->out, "attention: null pointer");
+    if (p->head_dim != 64) return set_error(B200SD_ERR_UNSUPPORTED, "attention: head_dim %d (only 64)", p->head_dim);
+    B200SD_CHECK_ARG(p->batch > 0 && p->heads > 0 && p->sq > 0 && p->skv > 0, "attention: bad shape");
+    B200SD_CHECK_ARG(p->ld_q % 8 == 0 && p->ld_k % 8 == 0 && p->ld_v % 8 == 0 && p->ld_out % 8 == 0,
+                     "attention: leading dimensions must be multiples of 8");
+    B200SD_CHECK_ARG(((reinterpret_cast<uintptr_t>(p->q) | reinterpret_cast<uintptr_t>(p->k) |
+                       reinterpret_cast<uintptr_t>(p->v) | reinterpret_cast<uintptr_t>(p->out)) & 15) == 0,
+                     "attention: pointers must be 16-byte aligned");
+    B200SD_CHECK_ARG(p->batch <= 65535 && p->heads <= 65535, "attention: batch/heads too large for the grid");
+    CUtensorMap tmQ, tmK, tmV;
+    const uint32_t box[2] = {ATT_D, 128};
+    {
+        uint64_t dims[2] = {(uint64_t)p->heads * ATT_D, (uint64_t)p->batch * p->sq};
+        uint64_t str[1] = {(uint64_t)p->ld_q * 2};
+        int32_t r = encode_tmap_bf16(&tmQ, p->q, 2, dims, str, box);
+        if (r) return r;
+    }
+    {
+        uint64_t dims[2] = {(uint64_t)p->heads * ATT_D, (uint64_t)p->batch * p->skv};
+        uint64_t strk[1] = {(uint64_t)p->ld_k * 2};
+        uint64_t strv[1] = {(uint64_t)p->ld_v * 2};
+        int32_t r = encode_tmap_bf16(&tmK, p->k, 2, dims, strk, box);
+        if (r) return r;
+        r = encode_tmap_bf16(&tmV, p->v, 2, dims, strv, box);
+        if (r) return r;
+    }
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        cudaError_t e =
+            cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM);
+        if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "attention smem attribute: %s", cudaGetErrorString(e));
+        attr_set[dev] = true;
+    }
+    AttnKernelParams kp;
+    kp.sq = p->sq, kp.skv = p->skv;
+    kp.n_kv_tiles = (p->skv + ATT_BN - 1) / ATT_BN;
+    kp.scale_log2 = p->scale * 1.4426950408889634f;
+    kp.out = static_cast<__nv_bfloat16*>(p->out);
+    kp.ld_out = p->ld_out;
+    dim3 grid((p->sq + ATT_BM - 1) / ATT_BM, p->heads, p->batch);
+    attention_kernel<<<grid, ATT_THREADS, ATT_SMEM, as_stream(stream)>>>(tmQ, tmK, tmV, kp);
+    count_launch();
+    B200SD_CHECK_LAUNCH("attention_kernel");
+    return B200SD_OK;
+}

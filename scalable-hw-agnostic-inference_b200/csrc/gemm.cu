@@ -1,0 +1,585 @@
+// K1/K2: persistent, warp-specialised implicit-GEMM for conv3x3 / conv1x1 / linear on sm_100a.
+//
+//   warp 0      TMA producer   : A = 4-D NHWC box (64 ch x bw x bh x bn pixels, shifted by the filter tap,
+//                                zero-filled outside the image = the conv padding), B = 64 x BLOCK_N weight box
+//   warp 1      UMMA issuer    : tcgen05.mma 128 x BLOCK_N x 16, fp32 accumulators in TMEM, double-buffered
+//   warps 2..5  epilogue       : tcgen05.ld -> bias / timestep-row bias / residual / GEGLU -> bf16|fp32 stores
+//
+// One CTA per SM; tiles are walked n-fastest so an A tile is fetched from HBM once and the weight matrix
+// stays L2-resident.  Algorithmic work per launch: 2*M*n_out*taps*cin FLOP.
+#include "common.h"
+#include "ptx.cuh"
+
+namespace b200sd {
+using namespace ptx;
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;
+constexpr int A_TILE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
+constexpr int ACC_STRIDE = 256;                      // TMEM columns between the two accumulator buffers
+constexpr int TMEM_COLS = 512;
+constexpr int GEMM_THREADS = 192;
+
+struct GemmKernelParams {
+    int n_img, img_h, img_w, cin, taps;
+    int bw, bh, bn;
+    int tiles_x, tiles_y, m_tiles, n_tiles, kb_per_tap;
+    int n_out, n_cols;  // n_cols = columns actually written (n_out, or n_out/2 for GEGLU)
+    uint32_t a_box_bytes;
+    const float* bias;
+    int bias_along_m;
+    const float* row_bias;
+    long long row_bias_stride;
+    const void* residual;
+    int res_dtype;
+    long long ld_res;
+    void* out;
+    int out_dtype;
+    long long ld_out;
+    int geglu;
+};
+
+template <int BLOCK_N>
+struct GemmCfg {
+    static constexpr int B_TILE_BYTES = BLOCK_N * 128;
+    static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
+    static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+
+// Applies the epilogue to 32 consecutive output columns [col0, col0+32) of one row and stores them.
+__device__ __forceinline__ void epilogue_store32(const GemmKernelParams& p, float (&v)[32], long long m, int img,
+                                                 int col0) {
+    const bool full = (col0 + 32 <= p.n_cols);
+    if (full) {
+        if (p.residual) {
+            if (p.res_dtype == B200SD_F32) {
+                const float4* r = reinterpret_cast<const float4*>(static_cast<const float*>(p.residual) +
+                                                                  m * p.ld_res + col0);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float4 t = r[j];
+                    v[4 * j + 0] += t.x, v[4 * j + 1] += t.y, v[4 * j + 2] += t.z, v[4 * j + 3] += t.w;
+                }
+            } else {
+                const uint4* r = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) +
+                                                                m * p.ld_res + col0);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    uint4 t = r[j];
+                    v[8 * j + 0] += bf16_lo(t.x), v[8 * j + 1] += bf16_hi(t.x);
+                    v[8 * j + 2] += bf16_lo(t.y), v[8 * j + 3] += bf16_hi(t.y);
+                    v[8 * j + 4] += bf16_lo(t.z), v[8 * j + 5] += bf16_hi(t.z);
+                    v[8 * j + 6] += bf16_lo(t.w), v[8 * j + 7] += bf16_hi(t.w);
+                }
+            }
+        }
+        if (p.out_dtype == B200SD_F32) {
+            float4* o = reinterpret_cast<float4*>(static_cast<float*>(p.out) + m * p.ld_out + col0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        } else {
+            uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + m * p.ld_out + col0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                o[j] = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                                  pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+        }
+    } else {
+        for (int j = 0; j < 32; ++j) {
+            int col = col0 + j;
+            if (col >= p.n_cols) break;
+            float x = v[j];
+            if (p.residual) {
+                if (p.res_dtype == B200SD_F32)
+                    x += static_cast<const float*>(p.residual)[m * p.ld_res + col];
+                else
+                    x += __bfloat162float(static_cast<const __nv_bfloat16*>(p.residual)[m * p.ld_res + col]);
+            }
+            if (p.out_dtype == B200SD_F32)
+                static_cast<float*>(p.out)[m * p.ld_out + col] = x;
+            else
+                static_cast<__nv_bfloat16*>(p.out)[m * p.ld_out + col] = __float2bfloat16(x);
+        }
+    }
+}
+
+// adds bias[n0 + j] (n0 = index into the bias vector, guarded by n_out) and the per-image row bias
+__device__ __forceinline__ void add_col_bias32(const GemmKernelParams& p, float (&v)[32], long long m, int img,
+                                               int n0) {
+    if (p.bias) {
+        if (p.bias_along_m) {
+            float b = p.bias[m];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] += b;
+        } else if (n0 + 32 <= p.n_out) {
+            const float4* b = reinterpret_cast<const float4*>(p.bias + n0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float4 t = __ldg(b + j);
+                v[4 * j + 0] += t.x, v[4 * j + 1] += t.y, v[4 * j + 2] += t.z, v[4 * j + 3] += t.w;
+            }
+        } else {
+            for (int j = 0; j < 32 && n0 + j < p.n_out; ++j) v[j] += p.bias[n0 + j];
+        }
+    }
+    if (p.row_bias) {
+        const float* rb = p.row_bias + (long long)img * p.row_bias_stride + n0;
+        if (n0 + 32 <= p.n_out) {
+            const float4* b = reinterpret_cast<const float4*>(rb);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float4 t = __ldg(b + j);
+                v[4 * j + 0] += t.x, v[4 * j + 1] += t.y, v[4 * j + 2] += t.z, v[4 * j + 3] += t.w;
+            }
+        } else {
+            for (int j = 0; j < 32 && n0 + j < p.n_out; ++j) v[j] += rb[j];
+        }
+    }
+}
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+    gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const GemmKernelParams p) {
+    using Cfg = GemmCfg<BLOCK_N>;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    // SWIZZLE_128B tiles need 1024-byte alignment in the shared address space
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full = empty_bar + STAGES;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA);
+        prefetch_tmap(&tmB);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full[s], 1);
+            mbar_init(&tmem_empty[s], 4);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_base_slot, TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_base_slot;
+
+    const int total_tiles = p.m_tiles * p.n_tiles;
+    const int num_kb = p.taps * p.kb_per_tap;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+                const int n_tile = t % p.n_tiles;
+                const int m_tile = t / p.n_tiles;
+                const int tx = m_tile % p.tiles_x;
+                const int ty = (m_tile / p.tiles_x) % p.tiles_y;
+                const int tn = m_tile / (p.tiles_x * p.tiles_y);
+                const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bn;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    const int tap = kb / p.kb_per_tap;
+                    const int c0 = (kb - tap * p.kb_per_tap) * BLOCK_K;
+                    int dx = 0, dy = 0;
+                    if (p.taps == 9) {
+                        dy = tap / 3 - 1;
+                        dx = tap - (tap / 3) * 3 - 1;
+                    }
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+                    uint8_t* sb = sa + A_TILE_BYTES;
+                    mbar_expect_tx(&full_bar[stage], p.a_box_bytes + Cfg::B_TILE_BYTES);
+                    tma_load_4d(sa, &tmA, &full_bar[stage], c0, x0 + dx, y0 + dy, n0);
+                    tma_load_2d(sb, &tmB, &full_bar[stage], tap * p.cin + c0, n_tile * BLOCK_N);
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ UMMA issuer
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BLOCK_N);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * ACC_STRIDE;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+                    const uint64_t adesc = umma_desc_sw128(a_addr);
+                    const uint64_t bdesc = umma_desc_sw128(a_addr + A_TILE_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / 16; ++k) {
+                        // +32 bytes along K inside the 128-byte swizzle row = +2 in the (addr >> 4) field
+                        umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[stage]);
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                umma_commit(&tmem_full[acc]);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
+        }
+        __syncwarp();
+    } else {
+        // ------------------------------------------------------------------ epilogue (warps 2..5)
+        const int quad = warp & 3;  // TMEM lane quadrant this warp may read
+        const int row_in_tile = quad * 32 + lane;
+        const int box_pix = p.bw * p.bh;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+            const int n_tile = t % p.n_tiles;
+            const int m_tile = t / p.n_tiles;
+            const int tx = m_tile % p.tiles_x;
+            const int ty = (m_tile / p.tiles_x) % p.tiles_y;
+            const int tn = m_tile / (p.tiles_x * p.tiles_y);
+            const int ln = row_in_tile / box_pix;
+            const int rem = row_in_tile - ln * box_pix;
+            const int ly = rem / p.bw;
+            const int lx = rem - ly * p.bw;
+            const int img = tn * p.bn + ln;
+            const int y = ty * p.bh + ly;
+            const int x = tx * p.bw + lx;
+            const bool valid = (ln < p.bn) && (img < p.n_img) && (y < p.img_h) && (x < p.img_w);
+            const long long m = ((long long)img * p.img_h + y) * p.img_w + x;
+
+            mbar_wait(&tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const uint32_t t_addr = tmem_base + acc * ACC_STRIDE + ((uint32_t)(quad * 32) << 16);
+            if (!p.geglu) {
+#pragma unroll 1
+                for (int c = 0; c < BLOCK_N / 32; ++c) {
+                    uint32_t r[32];
+                    tmem_ld_x32(t_addr + c * 32, r);
+                    tmem_ld_wait();
+                    const int col0 = n_tile * BLOCK_N + c * 32;
+                    if (valid && col0 < p.n_cols) {
+                        float v[32];
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                        add_col_bias32(p, v, m, img, col0);
+                        epilogue_store32(p, v, m, img, col0);
+                    }
+                }
+            } else {
+                constexpr int HALF = BLOCK_N / 2;
+#pragma unroll 1
+                for (int c = 0; c < HALF / 32; ++c) {
+                    uint32_t rv[32], rg[32];
+                    tmem_ld_x32(t_addr + c * 32, rv);
+                    tmem_ld_x32(t_addr + HALF + c * 32, rg);
+                    tmem_ld_wait();
+                    if (valid) {
+                        float v[32], g[32];
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(rv[j]), g[j] = __uint_as_float(rg[j]);
+                        add_col_bias32(p, v, m, img, n_tile * BLOCK_N + c * 32);
+                        add_col_bias32(p, g, m, img, n_tile * BLOCK_N + HALF + c * 32);
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] *= gelu_erf(g[j]);
+                        epilogue_store32(p, v, m, img, n_tile * HALF + c * 32);
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ------------------------------------------------------------------------------------------ host side
+static void choose_box(int n_img, int h, int w, int* bw, int* bh, int* bn) {
+    if (h == 1 && n_img == 1) {
+        *bw = w < 128 ? w : 128, *bh = 1, *bn = 1;
+        return;
+    }
+    double best = -1.0;
+    int b_w = 1, b_h = 1, b_n = 1;
+    const int maxw = w < 128 ? w : 128;
+    for (int cw = maxw; cw >= 1; --cw) {
+        const int maxh = (128 / cw) < h ? (128 / cw) : h;
+        for (int ch = maxh; ch >= 1; --ch) {
+            int cn = 1;
+            if (cw == w && ch == h) {
+                cn = 128 / (cw * ch);
+                if (cn > n_img) cn = n_img;
+                if (cn < 1) cn = 1;
+            }
+            const long long tiles = (long long)((w + cw - 1) / cw) * ((h + ch - 1) / ch) * ((n_img + cn - 1) / cn);
+            // efficiency, with a mild preference for long contiguous rows
+            const double eff = (double)w * h * n_img / (double)(tiles * 128) + 1e-4 * cw;
+            if (eff > best) best = eff, b_w = cw, b_h = ch, b_n = cn;
+        }
+    }
+    *bw = b_w, *bh = b_h, *bn = b_n;
+}
+
+static int pick_block_n_auto(int n_out, int geglu, long long m_tiles) {
+    if (geglu) return (n_out % 256 == 0) ? 256 : 128;
+    const int sms = num_sms();
+    const int cands[4] = {256, 160, 128, 64};
+    int divisible[4], nd = 0;
+    for (int i = 0; i < 4; ++i)
+        if (n_out % cands[i] == 0) divisible[nd++] = cands[i];
+    if (nd == 0) {
+        if (n_out <= 64) return 64;
+        // least padded
+        int best = 128, waste = 1 << 30;
+        for (int i = 0; i < 3; ++i) {
+            int w = ((n_out + cands[i] - 1) / cands[i]) * cands[i] - n_out;
+            if (w < waste) waste = w, best = cands[i];
+        }
+        return best;
+    }
+    // largest tile that still gives every SM a tile; else the smallest available
+    for (int i = 0; i < nd; ++i)
+        if (m_tiles * (n_out / divisible[i]) >= sms) return divisible[i];
+    return divisible[nd - 1];
+}
+
+template <int BLOCK_N>
+static int32_t launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmKernelParams& kp,
+                           cudaStream_t stream) {
+    using Cfg = GemmCfg<BLOCK_N>;
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "gemm smem attribute: %s", cudaGetErrorString(e));
+        attr_set[dev] = true;
+    }
+    long long total = (long long)kp.m_tiles * kp.n_tiles;
+    int grid = (int)(total < num_sms() ? total : num_sms());
+    gemm_kernel<BLOCK_N><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, kp);
+    count_launch();
+    B200SD_CHECK_LAUNCH("gemm_kernel");
+    return B200SD_OK;
+}
+
+}  // namespace b200sd
+
+using namespace b200sd;
+
+extern "C" int32_t b200sd_gemm_pick_block_n(int32_t n_out, int32_t geglu) {
+    return pick_block_n_auto(n_out, geglu, 1 << 20);
+}
+
+extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stream) {
+    B200SD_CHECK_ARG(p && p->a && p->w && p->out, "gemm: null pointer");
+    B200SD_CHECK_ARG(p->taps == 1 || p->taps == 9, "gemm: taps must be 1 or 9 (got %d)", p->taps);
+    B200SD_CHECK_ARG(p->n_img > 0 && p->img_h > 0 && p->img_w > 0 && p->cin > 0 && p->n_out > 0, "gemm: bad shape");
+    B200SD_CHECK_ARG(p->cin % 8 == 0, "gemm: cin (%d) must be a multiple of 8", p->cin);
+    B200SD_CHECK_ARG((reinterpret_cast<uintptr_t>(p->a) & 15) == 0 && (reinterpret_cast<uintptr_t>(p->w) & 15) == 0,
+                     "gemm: a / w must be 16-byte aligned");
+    B200SD_CHECK_ARG(p->out_dtype == B200SD_BF16 || p->out_dtype == B200SD_F32, "gemm: bad out_dtype");
+    B200SD_CHECK_ARG(!p->residual || p->residual_dtype == B200SD_BF16 || p->residual_dtype == B200SD_F32,
+                     "gemm: bad residual_dtype");
+    const int n_cols = p->geglu ? p->n_out / 2 : p->n_out;
+    if (n_cols >= 32) {
+        // vector path requirements
+        const int oa = p->out_dtype == B200SD_F32 ? 4 : 8;
+        B200SD_CHECK_ARG(p->ld_out % oa == 0 && (reinterpret_cast<uintptr_t>(p->out) & 15) == 0,
+                         "gemm: out must be 16-byte aligned with ld_out %% %d == 0", oa);
+        if (p->residual) {
+            const int ra = p->residual_dtype == B200SD_F32 ? 4 : 8;
+            B200SD_CHECK_ARG(p->ld_res % ra == 0 && (reinterpret_cast<uintptr_t>(p->residual) & 15) == 0,
+                             "gemm: residual must be 16-byte aligned with ld_res %% %d == 0", ra);
+        }
+        if (p->bias && !p->bias_along_m)
+            B200SD_CHECK_ARG((reinterpret_cast<uintptr_t>(p->bias) & 15) == 0, "gemm: bias must be 16-byte aligned");
+        if (p->row_bias)
+            B200SD_CHECK_ARG((reinterpret_cast<uintptr_t>(p->row_bias) & 15) == 0 && p->row_bias_stride % 4 == 0,
+                             "gemm: row_bias must be 16-byte aligned, stride %% 4 == 0");
+    }
+
+    GemmKernelParams kp{};
+    kp.n_img = p->n_img, kp.img_h = p->img_h, kp.img_w = p->img_w, kp.cin = p->cin, kp.taps = p->taps;
+    choose_box(p->n_img, p->img_h, p->img_w, &kp.bw, &kp.bh, &kp.bn);
+    kp.tiles_x = (p->img_w + kp.bw - 1) / kp.bw;
+    kp.tiles_y = (p->img_h + kp.bh - 1) / kp.bh;
+    const int tiles_n = (p->n_img + kp.bn - 1) / kp.bn;
+    kp.m_tiles = kp.tiles_x * kp.tiles_y * tiles_n;
+    kp.kb_per_tap = (p->cin + BLOCK_K - 1) / BLOCK_K;
+    kp.n_out = p->n_out, kp.n_cols = n_cols;
+    kp.a_box_bytes = (uint32_t)(kp.bw * kp.bh * kp.bn) * BLOCK_K * 2;
+    kp.bias = p->bias, kp.bias_along_m = p->bias_along_m;
+    kp.row_bias = p->row_bias, kp.row_bias_stride = p->row_bias_stride;
+    kp.residual = p->residual, kp.res_dtype = p->residual_dtype, kp.ld_res = p->ld_res;
+    kp.out = p->out, kp.out_dtype = p->out_dtype, kp.ld_out = p->ld_out;
+    kp.geglu = p->geglu ? 1 : 0;
+
+    int block_n = p->block_n ? p->block_n : pick_block_n_auto(p->n_out, kp.geglu, kp.m_tiles);
+    B200SD_CHECK_ARG(block_n == 64 || block_n == 128 || block_n == 160 || block_n == 256,
+                     "gemm: block_n %d not in {64,128,160,256}", block_n);
+    if (kp.geglu) {
+        B200SD_CHECK_ARG((block_n == 128 || block_n == 256) && p->n_out % block_n == 0,
+                         "gemm: GEGLU needs block_n in {128,256} dividing n_out (%d)", p->n_out);
+        B200SD_CHECK_ARG(!p->bias_along_m, "gemm: GEGLU with bias_along_m is not supported");
+    }
+    kp.n_tiles = (p->n_out + block_n - 1) / block_n;
+
+    CUtensorMap tmA, tmB;
+    {
+        const uint64_t c = (uint64_t)p->cin;
+        uint64_t dims[4] = {c, (uint64_t)p->img_w, (uint64_t)p->img_h, (uint64_t)p->n_img};
+        uint64_t strides[3] = {c * 2, c * 2 * p->img_w, c * 2 * p->img_w * p->img_h};
+        uint32_t box[4] = {BLOCK_K, (uint32_t)kp.bw, (uint32_t)kp.bh, (uint32_t)kp.bn};
+        int32_t r = encode_tmap_bf16(&tmA, p->a, 4, dims, strides, box);
+        if (r) return r;
+    }
+    {
+        const uint64_t k_total = (uint64_t)p->taps * p->cin;
+        uint64_t dims[2] = {k_total, (uint64_t)p->n_out};
+        uint64_t strides[1] = {k_total * 2};
+        uint32_t box[2] = {BLOCK_K, (uint32_t)block_n};
+        int32_t r = encode_tmap_bf16(&tmB, p->w, 2, dims, strides, box);
+        if (r) return r;
+    }
+    cudaStream_t s = as_stream(stream);
+    switch (block_n) {
+        case 64: return launch_gemm<64>(tmA, tmB, kp, s);
+        case 128: return launch_gemm<128>(tmA, tmB, kp, s);
+        case 160: return launch_gemm<160>(tmA, tmB, kp, s);
+        default: return launch_gemm<256>(tmA, tmB, kp, s);
+    }
+}
+
+// ------------------------------------------------------------------------------------------ UMMA self-test
+namespace b200sd {
+
+// Single CTA, 128 threads.  Operands are written to shared memory by ordinary stores in the SWIZZLE_128B
+// pattern (16-byte chunk c of 128-byte row r lives at chunk c ^ (r & 7)), then consumed by tcgen05.mma.
+__global__ void __launch_bounds__(128, 1)
+    umma_selftest_kernel(const __nv_bfloat16* __restrict__ A, const __nv_bfloat16* __restrict__ B,
+                         float* __restrict__ D, int n, int k, int b_mn_major) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+    uint8_t* sA = smem;                  // k/64 tiles of [128 rows x 128 B]
+    uint8_t* sB = smem + 128 * k * 2;    // K-major: k/64 tiles of [n rows x 128 B]; MN-major: n/64 atoms of [k rows x 128 B]
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    // A: row r, 16-byte chunk index cc (8 bf16) over the whole K extent
+    for (int i = tid; i < 128 * (k / 8); i += 128) {
+        int r = i / (k / 8), cc = i % (k / 8);
+        int kc = cc / 8, c = cc % 8;
+        uint4 v = *reinterpret_cast<const uint4*>(A + (size_t)r * k + cc * 8);
+        *reinterpret_cast<uint4*>(sA + kc * 16384 + r * 128 + ((c ^ (r & 7)) << 4)) = v;
+    }
+    if (!b_mn_major) {
+        for (int i = tid; i < n * (k / 8); i += 128) {
+            int r = i / (k / 8), cc = i % (k / 8);
+            int kc = cc / 8, c = cc % 8;
+            uint4 v = *reinterpret_cast<const uint4*>(B + (size_t)r * k + cc * 8);
+            *reinterpret_cast<uint4*>(sB + kc * (n * 128) + r * 128 + ((c ^ (r & 7)) << 4)) = v;
+        }
+    } else {
+        // B given as [k, n] (n contiguous): atom na covers n-columns [64 na, 64 na + 64); row = k index
+        for (int i = tid; i < k * (n / 8); i += 128) {
+            int r = i / (n / 8), cc = i % (n / 8);
+            int na = cc / 8, c = cc % 8;
+            uint4 v = *reinterpret_cast<const uint4*>(B + (size_t)r * n + cc * 8);
+            *reinterpret_cast<uint4*>(sB + na * (k * 128) + r * 128 + ((c ^ (r & 7)) << 4)) = v;
+        }
+    }
+    fence_proxy_async_smem();
+    if (tid == 0) {
+        mbar_init(&bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc(&tmem_slot, 256);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (tid == 0) {
+        const uint32_t idesc = umma_idesc_bf16(128, (uint32_t)n, 0, b_mn_major ? 1u : 0u);
+        for (int kk = 0; kk < k / 16; ++kk) {
+            const uint32_t a_addr = smem_u32(sA) + (kk / 4) * 16384 + (kk % 4) * 32;
+            uint64_t adesc = umma_desc_sw128(a_addr);
+            uint64_t bdesc;
+            if (!b_mn_major)
+                bdesc = umma_desc_sw128(smem_u32(sB) + (kk / 4) * (n * 128) + (kk % 4) * 32);
+            else
+                bdesc = umma_desc_sw128(smem_u32(sB) + kk * 2048, /*lbo=*/(uint32_t)k * 128, /*sbo=*/1024);
+            umma_bf16(tmem_base, adesc, bdesc, idesc, kk != 0);
+        }
+        umma_commit(&bar);
+    }
+    __syncwarp();
+    mbar_wait(&bar, 0);
+    tc_fence_after();
+    for (int c = 0; c < n / 16; ++c) {
+        uint32_t r[16];
+        tmem_ld_x16(tmem_base + c * 16 + ((uint32_t)(warp * 32) << 16), r);
+        tmem_ld_wait();
+        for (int j = 0; j < 16; ++j) D[(size_t)(warp * 32 + lane) * n + c * 16 + j] = __uint_as_float(r[j]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_base, 256);
+}
+
+}  // namespace b200sd
+
+extern "C" int32_t b200sd_umma_selftest(const void* a, const void* b, float* d, int32_t n, int32_t k,
+                                        int32_t b_mn_major, b200sd_stream_t stream) {
+    B200SD_CHECK_ARG(a && b && d, "umma_selftest: null pointer");
+    B200SD_CHECK_ARG(n >= 16 && n <= 256 && n % 16 == 0 && k >= 64 && k <= 256 && k % 64 == 0,
+                     "umma_selftest: need 16<=n<=256 (n%%16==0), 64<=k<=256 (k%%64==0)");
+    B200SD_CHECK_ARG(!b_mn_major || n % 64 == 0, "umma_selftest: MN-major B needs n %% 64 == 0");
+    const int smem = 128 * k * 2 + n * k * 2 + 1024;
+    cudaError_t e =
+        cudaFuncSetAttribute(umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "umma_selftest attr: %s", cudaGetErrorString(e));
+    umma_selftest_kernel<<<1, 128, smem, as_stream(stream)>>>(static_cast<const __nv_bfloat16*>(a),
+                                                              static_cast<const __nv_bfloat16*>(b), d, n, k,
+                                                              b_mn_major);
+    count_launch();
+    B200SD_CHECK_LAUNCH("umma_selftest_kernel");
+    return B200SD_OK;
+}
