@@ -1,0 +1,375 @@
+#!/usr/bin/env python
+"""bench.py -- SD2.1 768^2 / 25-step images per second on N B200s (BASELINE.json metric), one JSON line on rank 0.
+
+A "step" is one pass of the hot path over one batch: 25 denoising steps (UNet at CFG batch 2B + CFG/scheduler
+kernel, replayed as one CUDA graph per step) + VAE decode + uint8 post-process.
+  value : whole-job images/s with latents and text embeddings already resident in HBM (CUDA-event timed)
+  e2e   : the same through the public API  pipe(prompt_embeds=, negative_prompt_embeds=, latents=, ...)  with
+          pinned HOST inputs and the uint8 images read back to the host inside the timed region
+  roofline : dominant kernel class, algorithmic FLOPs / CUDA-event time per launch, vs the measured bf16 peak
+  cpu_baseline : the fp32 oracle (a port: diffusers is not installable here) on this box's host cores, bounded sample
+`--impl reference` times that CPU oracle alone (the reference ships no other implementation of the path).
+
+N > 1 (torchrun): one replica per GPU, independent prompts, no data-path collective; value = all images / max time.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+PKG = ROOT / "scalable-hw-agnostic-inference_b200"
+for p in (str(ROOT), str(PKG)):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+UNET_TFLOP = {64: 1.6085, 96: 4.2982, 128: 9.3500}    # per image-step, CFG batch 2
+VAE_TFLOP = {64: 2.5145, 96: 5.7543, 128: 10.4704}    # per image
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10, help="timed passes of the hot path")
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=1, help="images per GPU per pass (BASELINE configs[1] = 1, configs[2] = 16)")
+    ap.add_argument("--denoise-steps", type=int, default=25)
+    ap.add_argument("--size", type=int, default=768)
+    ap.add_argument("--scheduler", default="ddim", choices=["ddim", "dpm++2m", "euler"])
+    ap.add_argument("--operand-dtype", default=None, choices=[None, "fp16", "bf16"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-only", action="store_true", help="one eager profiled pass, no timing (for ncu runs)")
+    return ap.parse_args()
+
+
+def peaks():
+    f = ROOT / "MEASURED_PEAKS.json"
+    if f.exists():
+        d = json.loads(f.read_text())
+        return {"tflops": float(d.get("bf16_tflops_sustained", d.get("bf16_tflops", 1590.0))), "hbm_gbs": float(d.get("hbm_gbs", 6650.0)),
+                "source": "measured (MEASURED_PEAKS.json, sustained bf16 GEMM)"}
+    return {"tflops": 1590.0, "hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """samples nvidia-smi clocks and throttle reasons during the timed region"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.lines, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for name, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------- CPU oracle leg
+def cpu_oracle_sample(size: int, denoise_steps: int, n_unet: int = 1):
+    """fp32 oracle on all host cores: n_unet UNet forwards (CFG batch 2) + one VAE decode at `size`, extrapolated to a
+    full image.  Returns (images_per_s, info)."""
+    import torch
+    from oracle import sd21 as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    hw = size // 8
+    unet = O.seeded_init_(O.UNet2DCondition(O.sd21_unet_config(sample_size=hw)), 0).eval()
+    vae = O.seeded_init_(O.VAEDecoder(O.VAEConfig()), 1).eval()
+    lat, ctx = O.seeded_inputs(1, hw, 1024)
+    x2 = torch.cat([lat, lat])
+    t_unet = []
+    with torch.no_grad():
+        for i in range(n_unet):
+            t0 = time.perf_counter()
+            unet(x2, 961.0, ctx)
+            t_unet.append(time.perf_counter() - t0)
+        t0 = time.perf_counter()
+        vae.decode(lat / 0.18215)
+        t_vae = time.perf_counter() - t0
+    tu = min(t_unet)
+    per_image = denoise_steps * tu + t_vae
+    return 1.0 / per_image, {"unet_step_s": tu, "vae_decode_s": t_vae, "cores": cores, "unet_times_s": t_unet}
+
+
+def run_reference(args):
+    """`--impl reference`: the reference's own implementation of the path is diffusers on torch, which cannot be
+    installed here (no network, not in the wheelhouse); the timed stand-in is the fp32 CPU oracle, all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    budget_s = 200.0
+    t0 = time.perf_counter()
+    n = max(1, args.warmup + args.steps)
+    # first forward doubles as warm-up; cap the number of timed UNet forwards by the time budget
+    ips, info = cpu_oracle_sample(args.size, args.denoise_steps, n_unet=2)
+    est = info["unet_step_s"]
+    extra = int(max(0, min(args.steps - 1, (budget_s - (time.perf_counter() - t0)) / max(est, 1e-3) - 1)))
+    if extra > 0:
+        ips2, info2 = cpu_oracle_sample(args.size, args.denoise_steps, n_unet=extra)
+        info["unet_times_s"] += info2["unet_times_s"]
+        info["unet_step_s"] = min(info["unet_step_s"], info2["unet_step_s"])
+        ips = 1.0 / (args.denoise_steps * info["unet_step_s"] + info["vae_decode_s"])
+    sample = (f"{len(info['unet_times_s'])} UNet forwards (CFG batch 2, best taken) + 1 VAE decode at {args.size}^2 fp32, "
+              f"extrapolated to {args.denoise_steps} steps/image")
+    line = {"impl": "reference", "metric": "sd21_images_per_sec", "value": ips, "unit": "images/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 / ips, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+            "config": workload_config(args, 1),
+            "cpu_baseline": {"value": ips, "unit": "images/s", "cores": info["cores"], "kind": "port", "sample": sample,
+                             "unet_step_s": info["unet_step_s"], "vae_decode_s": info["vae_decode_s"]},
+            "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, batch):
+    return {"workload": f"SD2.1 {args.size}x{args.size}, {args.denoise_steps} {args.scheduler} steps, CFG 7.5, "
+                        f"batch {batch} per GPU, random-init weights (BASELINE configs[{1 if batch == 1 else 2}])",
+            "size": args.size, "denoise_steps": args.denoise_steps, "batch_per_gpu": batch, "scheduler": args.scheduler,
+            "l2": "no explicit flush: each pass streams 1.8 GB of weights plus activations, far beyond the 126 MB L2",
+            "parallelism": f"dp{args.gpus} (one replica per GPU, no collective)"}
+
+
+# ---------------------------------------------------------------------------------------------------- GPU arm
+def run_b200(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.operand_dtype:
+        os.environ["B200SD_OPERAND_DTYPE"] = args.operand_dtype
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist_mod.init_process_group("nccl", device_id=dev)
+        dist = dist_mod
+
+    import b200sd
+    from b200sd import ops
+    from b200sd._randinit import random_state_dicts
+
+    hw = args.size // 8
+    B = args.batch
+    ucfg = b200sd.UNetConfig(sample_size=hw, prediction_type="v_prediction" if hw == 96 else "epsilon")
+    vcfg = b200sd.VAEConfig()
+    usd, vsd = random_state_dicts(ucfg, vcfg, 0)
+    unet = b200sd.B200UNet(usd, ucfg, dev)
+    vae = b200sd.B200VAEDecoder(vsd, vcfg, dev)
+    del usd, vsd
+    pipe = b200sd.B200Pipeline(unet, vae, b200sd.B200Scheduler(args.scheduler, ucfg.prediction_type, dev))
+    op_name = {torch.float16: "fp16", torch.bfloat16: "bf16"}[unet.K.op_dtype]
+
+    # synthetic inputs: distinct seeded latents / embeddings per rank (independent prompts), pinned on the host
+    g = torch.Generator("cpu").manual_seed(1234 + rank)
+    lat_host = torch.randn(B, 4, hw, hw, generator=g).pin_memory()
+    cond_host = torch.randn(B, 77, 1024, generator=g).pin_memory()
+    unc_host = torch.randn(1, 77, 1024, generator=torch.Generator("cpu").manual_seed(7)).expand(B, -1, -1).contiguous().pin_memory()
+    lat_dev = lat_host.to(dev).permute(0, 2, 3, 1).contiguous()
+    ctx2_dev = torch.cat([unc_host.to(dev), cond_host.to(dev)]).to(unet.K.op_dtype)
+
+    def one_pass_device():
+        final = pipe.denoise(lat_dev, ctx2_dev, args.denoise_steps)
+        return pipe.decode(final, "uint8")
+
+    def one_pass_e2e():
+        res = pipe(prompt_embeds=cond_host, negative_prompt_embeds=unc_host, latents=lat_host,
+                   num_inference_steps=args.denoise_steps, height=args.size, width=args.size, output_type="uint8")
+        return res.images.cpu()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    if args.profile_only:
+        pipe.use_cuda_graph = False
+        one_pass_device()
+        torch.cuda.synchronize()
+        return
+
+    for _ in range(max(args.warmup, 1)):
+        one_pass_device()
+    torch.cuda.synchronize()
+
+    # ---- launches per pass: graph replays carry the launches counted at capture
+    n0 = ops.launch_count()
+    eager_pipe_flag = pipe.use_cuda_graph
+    pipe.use_cuda_graph = False
+    saved_graph, pipe._graph = pipe._graph, None
+    one_pass_device()
+    torch.cuda.synchronize()
+    launches_per_pass = ops.launch_count() - n0
+    pipe.use_cuda_graph, pipe._graph = eager_pipe_flag, saved_graph
+
+    # ---- timed region 1: device-resident inputs
+    clocks = ClockSampler(local)
+    barrier()
+    clocks.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        one_pass_device()
+    ev1.record()
+    torch.cuda.synchronize()
+    ms_dev = ev0.elapsed_time(ev1)
+    clk = clocks.stop()
+    barrier()
+
+    # ---- timed region 2: end to end through the public API with host buffers
+    for _ in range(2):
+        one_pass_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        img = one_pass_e2e()
+    torch.cuda.synchronize()
+    ms_e2e = (time.perf_counter() - t0) * 1000.0
+    barrier()
+    h2d = lat_host.numel() * 4 + cond_host.numel() * 4 + unc_host.numel() * 4
+    d2h = img.numel()
+
+    if dist is not None:
+        t = torch.tensor([ms_dev, ms_e2e], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_dev, ms_e2e = float(t[0]), float(t[1])
+
+    if rank != 0:
+        if dist is not None:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # ---- per-kernel-class profile (eager, every launch bracketed by CUDA events on the launching stream)
+    pipe.use_cuda_graph = False
+    pipe._graph, saved_graph = None, pipe._graph
+    ops.profile_begin()
+    one_pass_device()
+    prof = ops.profile_end()
+    pipe.use_cuda_graph, pipe._graph = True, saved_graph
+    total_ms = sum(d["ms"] for d in prof.values())
+    pk = peaks()
+    classes = {}
+    for kind, d in sorted(prof.items(), key=lambda kv: -kv[1]["ms"]):
+        tensor = kind in ("gemm", "attention")
+        rate = d["work"] / (d["ms"] * 1e-3) if d["ms"] > 0 else 0.0
+        classes[kind] = {"launches": d["launches"], "ms": round(d["ms"], 3), "share": round(d["ms"] / total_ms, 4),
+                         ("tflops" if tensor else "gbs"): round(rate / (1e12 if tensor else 1e9), 2)}
+    dom = max(prof.items(), key=lambda kv: kv[1]["ms"])
+    dk, dd = dom
+    tensor = dk in ("gemm", "attention")
+    achieved = dd["work"] / (dd["ms"] * 1e-3) / (1e12 if tensor else 1e9)
+    peak = pk["tflops"] if tensor else pk["hbm_gbs"]
+    traffic = None
+    tf = ROOT / "profiles" / "roofline_traffic.json"
+    if tf.exists():
+        try:
+            traffic = json.loads(tf.read_text()).get(dk)
+        except Exception:
+            traffic = None
+    roofline = {"kernel": {"gemm": "gemm_kernel (implicit-GEMM conv/linear, tcgen05)", "attention": "attention_kernel"}.get(dk, dk),
+                "bound": "tensor" if tensor else "hbm", "achieved": round(achieved, 2), "peak": peak,
+                "unit": "TFLOP/s" if tensor else "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
+                "peak_source": pk["source"], "launches_per_pass": dd["launches"],
+                "avg_launch_ms": round(dd["ms"] / dd["launches"], 4),
+                "how": "sum of algorithmic work over all launches of this kernel in one pass / sum of their CUDA-event "
+                       "durations (eager pass, events on the launching stream)",
+                "classes": classes}
+
+    images = B * world
+    value = images * args.steps / (ms_dev * 1e-3)
+    e2e_val = images * args.steps / (ms_e2e * 1e-3)
+    tflop_img = args.denoise_steps * UNET_TFLOP.get(hw, 0) + VAE_TFLOP.get(hw, 0)
+    line = {"metric": "sd21_images_per_sec", "value": round(value, 4), "unit": "images/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_dev / args.steps, 3),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": op_name, "data": "synthetic",
+            "config": workload_config(args, B),
+            "unet_step_ms": round((ms_dev / args.steps) * (1 - classes_share_vae(prof, pipe)) / args.denoise_steps, 3),
+            "whole_image_tensor_roofline_frac": round(value * tflop_img / (world * pk["tflops"]), 4) if tflop_img else None,
+            "e2e": {"value": round(e2e_val, 4), "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": round(ms_e2e / args.steps, 3)},
+            "gpu_launches": int(launches_per_pass * args.steps),
+            "clocks": clk, "roofline": roofline}
+    if not args.no_cpu_baseline and world == 1:
+        ips, info = cpu_oracle_sample(args.size, args.denoise_steps, n_unet=2)
+        line["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": info["cores"], "kind": "port",
+                                "sample": f"2 UNet forwards (CFG batch 2, best taken) + 1 VAE decode at {args.size}^2 fp32, "
+                                          f"extrapolated to {args.denoise_steps} steps/image",
+                                "unet_step_s": round(info["unet_step_s"], 3), "vae_decode_s": round(info["vae_decode_s"], 3)}
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def classes_share_vae(prof, pipe) -> float:
+    """fraction of one pass spent outside the denoising loop (VAE decode + post-process), from a separate timing"""
+    import torch
+    st = pipe._static
+    x = st["x"].clone()
+    for _ in range(2):
+        pipe.decode(x, "uint8")
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    pipe.decode(x, "uint8")
+    e1.record()
+    torch.cuda.synchronize()
+    t_vae = e0.elapsed_time(e1)
+    e0.record()
+    pipe.denoise(x * 0 + 1, st["ctx2"], pipe.scheduler.num_inference_steps)
+    e1.record()
+    torch.cuda.synchronize()
+    t_den = e0.elapsed_time(e1)
+    return t_vae / (t_vae + t_den)
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -15,7 +15,8 @@
  *     All buffers (including scratch, see *_workspace_bytes) are caller-owned device memory that must
  *     stay alive until `stream` reaches the op.
  *   - activations are NHWC; "tokens" [n_img, h*w, C] are the same memory as NHWC [n_img, h, w, C].
- *   - bf16 operands, fp32 accumulation / statistics / softmax / scheduler state.
+ *   - tensor-core operands are 16-bit (bf16 or fp16, chosen per tensor by a dtype code); accumulation,
+ *     statistics, softmax and scheduler state are fp32.
  */
 #ifndef B200SD_H_
 #define B200SD_H_
@@ -27,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200SD_ABI_VERSION 1
+#define B200SD_ABI_VERSION 2
 
 typedef struct CUstream_st* b200sd_stream_t; /* == cudaStream_t / CUstream */
 
@@ -40,7 +41,7 @@ typedef enum {
     B200SD_ERR_CUDA = -5
 } b200sd_status;
 
-typedef enum { B200SD_BF16 = 1, B200SD_F32 = 2 } b200sd_dtype;
+typedef enum { B200SD_BF16 = 1, B200SD_F32 = 2, B200SD_F16 = 3 } b200sd_dtype;
 
 /* ---- library / device ------------------------------------------------------------------------ */
 /* no reference counterpart (the reference never checks the device: app/run-sd.py:107 hard-codes "cuda") */
@@ -56,27 +57,30 @@ int64_t b200sd_launch_count(void);
  * ResnetBlock2D / Transformer2DModel / Attention / FeedForward / Decoder, which the reference reaches
  * through pipe.unet(...) and pipe.vae.decode(...) (app/run-sd.py:110-116,124-134,140).
  *   out[m, n] = epilogue( sum_{tap,c} A[pixel(m)+offset(tap), c] * W[n, tap*cin + c] )
- * A is an NHWC bf16 activation; a plain [M,K] matrix is n_img=1, img_h=1, img_w=M, cin=K, taps=1.
+ * A is an NHWC 16-bit activation; a plain [M,K] matrix is n_img=1, img_h=1, img_w=M, cin=K, taps=1.
  * epilogue: + bias[n]  + row_bias[img(m)*row_bias_stride + n]  + residual[m, n]  then optional GEGLU.
  */
 typedef struct {
-    const void* a;          /* bf16 NHWC [n_img, img_h, img_w, cin]; 16-byte aligned; cin % 8 == 0 */
+    const void* a;          /* NHWC [n_img, img_h, img_w, cin] of a_dtype; 16-byte aligned; cin % 8 == 0 */
+    int32_t a_dtype;        /* B200SD_BF16 or B200SD_F16 */
     int32_t n_img, img_h, img_w, cin;
     int32_t taps;           /* 1 or 9 */
-    const void* w;          /* bf16 [n_out, taps*cin], K contiguous, K order = (tap, c)  (KRSC) */
+    const void* w;          /* [n_out, taps*cin] of w_dtype, K contiguous, K order = (tap, c)  (KRSC) */
+    int32_t w_dtype;        /* B200SD_BF16 or B200SD_F16 */
     int32_t n_out;
     const float* bias;      /* fp32 [n_out] (or [M] when bias_along_m), may be NULL */
     int32_t bias_along_m;
     const float* row_bias;  /* fp32, per-image additive row (timestep-embedding projection), may be NULL */
     int64_t row_bias_stride;/* elements between consecutive images; 0 broadcasts one row */
     const void* residual;   /* [M, ld_res] of residual_dtype, may be NULL; may alias `out` */
-    int32_t residual_dtype;
+    int32_t residual_dtype; /* any b200sd_dtype */
     int64_t ld_res;
     void* out;              /* [M, ld_out] of out_dtype (GEGLU: n_out/2 columns are written) */
-    int32_t out_dtype;
+    int32_t out_dtype;      /* any b200sd_dtype */
     int64_t ld_out;
     int32_t geglu;          /* 1: out[m,j] = val_j * gelu_erf(gate_j); weight/bias rows interleaved per block_n
-                               tile by b200sd_pack_geglu_rows (first half of a tile = values, second = gates) */
+                               tile by the host packer, b200sd/layers.py pack_geglu (first half of a tile = values,
+                               second half = gates) */
     int32_t block_n;        /* 0 = choose; else one of 64, 128, 160, 256 */
 } b200sd_gemm_params;
 int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stream);
@@ -89,10 +93,11 @@ int32_t b200sd_gemm_pick_block_n(int32_t n_out, int32_t geglu);
  * (app/run-sd.py:135).  Row r of batch b is q[(b*sq + r)*ld_q + h*64 + d]; same for k/v with skv.
  */
 typedef struct {
-    const void *q, *k, *v;  /* bf16 */
+    const void *q, *k, *v;  /* all of `dtype` */
     int64_t ld_q, ld_k, ld_v;
-    void* out;              /* bf16 [batch*sq, ld_out], head h at columns h*64 */
+    void* out;              /* `dtype` [batch*sq, ld_out], head h at columns h*64 */
     int64_t ld_out;
+    int32_t dtype;          /* B200SD_BF16 or B200SD_F16 (also the format of the probability tile) */
     int32_t batch, heads, head_dim; /* head_dim must be 64 */
     int32_t sq, skv;
     float scale;            /* softmax(scale * q.k) */
@@ -103,7 +108,7 @@ int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_stream_t strea
  * Replaces torch.nn.GroupNorm + F.silu in ResnetBlock2D.norm1/norm2, Transformer2DModel.norm,
  * conv_norm_out, and the torch.cat([h, skip], dim=1) feeding up-block resnets (via pipe.unet /
  * pipe.vae.decoder, app/run-sd.py:110-116,124-128).  Two kernels: deterministic split statistics into
- * `workspace`, then normalise+affine(+SiLU) -> bf16.  `raw` (optional) receives the un-normalised bf16
+ * `workspace`, then normalise+affine(+SiLU) -> 16-bit.  `raw` (optional) receives the un-normalised 16-bit
  * concat, the A operand of the 1x1 conv_shortcut.
  */
 typedef struct {
@@ -111,20 +116,21 @@ typedef struct {
     int32_t c1;
     const void* x2;         /* [n_img, hw, c2] or NULL */
     int32_t c2;
-    int32_t in_dtype;
+    int32_t in_dtype;       /* any b200sd_dtype */
     int32_t n_img, hw, groups;
     float eps;
     const float *gamma, *beta; /* fp32 [c1+c2] */
     int32_t silu;
-    void* y;                /* bf16 [n_img, hw, c1+c2] */
-    void* raw;              /* bf16 [n_img, hw, c1+c2] or NULL */
+    void* y;                /* out_dtype [n_img, hw, c1+c2] */
+    void* raw;              /* out_dtype [n_img, hw, c1+c2] or NULL */
+    int32_t out_dtype;      /* B200SD_BF16 or B200SD_F16 */
     float* workspace;
     int64_t workspace_bytes;
 } b200sd_groupnorm_params;
 int64_t b200sd_groupnorm_workspace_bytes(const b200sd_groupnorm_params* p);
 int32_t b200sd_groupnorm(const b200sd_groupnorm_params* p, b200sd_stream_t stream);
 
-/* ---- LayerNorm over the last dim -> bf16 (BasicTransformerBlock.norm1/2/3) -------------------------- */
+/* ---- LayerNorm over the last dim -> 16-bit (BasicTransformerBlock.norm1/2/3) ---------------------- */
 typedef struct {
     const void* x;          /* [rows, cols] of in_dtype, contiguous */
     int32_t in_dtype;
@@ -132,7 +138,8 @@ typedef struct {
     int32_t cols;
     float eps;
     const float *gamma, *beta;
-    void* y;                /* bf16 [rows, cols] */
+    void* y;                /* out_dtype [rows, cols] */
+    int32_t out_dtype;      /* B200SD_BF16 or B200SD_F16 */
 } b200sd_layernorm_params;
 int32_t b200sd_layernorm(const b200sd_layernorm_params* p, b200sd_stream_t stream);
 
@@ -144,17 +151,19 @@ typedef struct {
     const void* x;          /* NHWC [n_src, in_h, in_w, cin] of in_dtype */
     int32_t in_dtype;
     int32_t n_img, n_src, in_h, in_w, cin, stride;
-    void* out;              /* bf16 [n_img*out_h*out_w, k_pad], k_pad >= 9*cin, k_pad % 8 == 0 */
+    void* out;              /* out_dtype [n_img*out_h*out_w, k_pad], k_pad >= 9*cin, k_pad % 8 == 0 */
+    int32_t out_dtype;      /* B200SD_BF16 or B200SD_F16 */
     int32_t k_pad;
 } b200sd_im2col_params;
 int32_t b200sd_im2col3x3(const b200sd_im2col_params* p, b200sd_stream_t stream);
 
-/* ---- nearest-neighbour 2x upsample NHWC -> bf16 (Upsample2D's F.interpolate) ---------------------- */
+/* ---- nearest-neighbour 2x upsample NHWC -> 16-bit (Upsample2D's F.interpolate) ---------------------- */
 typedef struct {
     const void* x;          /* [n_img, h, w, c] of in_dtype */
     int32_t in_dtype;
     int32_t n_img, h, w, c;
-    void* out;              /* bf16 [n_img, 2h, 2w, c] */
+    void* out;              /* out_dtype [n_img, 2h, 2w, c] */
+    int32_t out_dtype;      /* B200SD_BF16 or B200SD_F16 */
 } b200sd_upsample_params;
 int32_t b200sd_upsample2x(const b200sd_upsample_params* p, b200sd_stream_t stream);
 
@@ -169,7 +178,7 @@ int32_t b200sd_upsample2x(const b200sd_upsample_params* p, b200sd_stream_t strea
  */
 typedef struct {
     const void* eps2;       /* [2*n] of eps_dtype: first n uncond, last n cond */
-    int32_t eps_dtype;
+    int32_t eps_dtype;      /* any b200sd_dtype */
     float* x;               /* fp32 [n], in place */
     float* x0_prev;         /* fp32 [n] or NULL */
     const float* coef;      /* device fp32 [6 * n_steps] */
@@ -179,7 +188,7 @@ typedef struct {
 int32_t b200sd_cfg_sched_step(const b200sd_cfg_sched_params* p, b200sd_stream_t stream);
 
 /* ---- K5: small-M linear for the timestep path -----------------------------------------------------------
- * y[m, n] = act_out( sum_k act_in(x[m,k]) * w[n,k] + b[n] ),  m < 64.  Used for Timesteps (sinusoid, when
+ * y[m, n] = act_out( sum_k act_in(x[m,k]) * w[n,k] + b[n] ),  m <= 64.  Used for Timesteps (sinusoid, when
  * `sinusoid_dim` > 0 x is a device fp32 [rows] vector of timesteps), TimestepEmbedding.linear_1/2 and the 22
  * ResnetBlock2D.time_emb_proj (batched into one weight), all inside pipe.unet (app/run-sd.py:140).
  */
@@ -188,19 +197,21 @@ typedef struct {
     int32_t rows, k, n;
     int32_t sinusoid_dim;   /* 0, or == k: x[m] -> cat(cos, sin)(x[m] * 10000^(-i/(k/2))) */
     int32_t silu_in, silu_out;
-    const void* w;          /* bf16 [n, k] */
+    const void* w;          /* [n, k] of w_dtype */
+    int32_t w_dtype;        /* B200SD_BF16 or B200SD_F16 */
     const float* b;         /* fp32 [n] or NULL */
     float* y;               /* fp32 [rows, n] */
 } b200sd_small_linear_params;
 int32_t b200sd_small_linear(const b200sd_small_linear_params* p, b200sd_stream_t stream);
 
-/* ---- row softmax y = softmax(scale * x) -> bf16 (VAE mid-block attention, 1 head x 512) ------------------
- * x may be fp32 or bf16; y may alias x when x is bf16. */
+/* ---- row softmax y = softmax(scale * x) -> 16-bit (VAE mid-block attention, 1 head x 512) ---------------
+ * y may alias x when both are 16-bit. */
 typedef struct {
     const void* x;          /* [rows, ld_in] of in_dtype, first `cols` of each row are live */
     int32_t in_dtype;
     int64_t ld_in;
-    void* y;                /* bf16 [rows, ld_out] */
+    void* y;                /* out_dtype [rows, ld_out] */
+    int32_t out_dtype;      /* B200SD_BF16 or B200SD_F16 */
     int64_t ld_out;
     int64_t rows;
     int32_t cols;
@@ -218,7 +229,7 @@ typedef struct {
 } b200sd_denorm_u8_params;
 int32_t b200sd_denorm_u8(const b200sd_denorm_u8_params* p, b200sd_stream_t stream);
 
-/* ---- dtype cast fp32 <-> bf16 (boundary tensors) -------------------------------------------------------- */
+/* ---- dtype cast between fp32 / bf16 / fp16 (boundary tensors) --------------------------------------------- */
 typedef struct {
     const void* x;
     int32_t in_dtype;
@@ -228,9 +239,11 @@ typedef struct {
 } b200sd_cast_params;
 int32_t b200sd_cast(const b200sd_cast_params* p, b200sd_stream_t stream);
 
-/* ---- UMMA self-test: one 128 x n x 64k tile product with the B operand K-major or MN-major ---------------
- * no reference counterpart; used by tests to pin the shared-memory descriptor encodings on real hardware. */
-int32_t b200sd_umma_selftest(const void* a_bf16 /*[128,k]*/, const void* b_bf16 /*[n,k] or [k,n]*/,
+/* ---- UMMA self-test: one 128 x n x k tile product with the B operand K-major or MN-major -----------------
+ * no reference counterpart; used by tests to pin the shared-memory / instruction descriptor encodings
+ * (including mixed bf16 x fp16 operands) on real hardware. */
+int32_t b200sd_umma_selftest(const void* a /*[128,k] of a_dtype*/, int32_t a_dtype,
+                             const void* b /*[n,k] or [k,n] of b_dtype*/, int32_t b_dtype,
                              float* d /*[128,n]*/, int32_t n, int32_t k, int32_t b_mn_major,
                              b200sd_stream_t stream);
 

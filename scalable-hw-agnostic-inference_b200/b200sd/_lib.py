@@ -7,44 +7,47 @@ from pathlib import Path
 
 _HERE = Path(__file__).resolve().parent
 LIB_PATH = _HERE / "libb200sd.so"
+ABI_VERSION = 2
 
-BF16, F32 = 1, 2
+BF16, F32, F16 = 1, 2, 3
 
 c_i32, c_i64, c_f32, c_vp = C.c_int32, C.c_int64, C.c_float, C.c_void_p
 
 
 class GemmParams(C.Structure):
-    _fields_ = [("a", c_vp), ("n_img", c_i32), ("img_h", c_i32), ("img_w", c_i32), ("cin", c_i32), ("taps", c_i32),
-                ("w", c_vp), ("n_out", c_i32), ("bias", c_vp), ("bias_along_m", c_i32), ("row_bias", c_vp),
-                ("row_bias_stride", c_i64), ("residual", c_vp), ("residual_dtype", c_i32), ("ld_res", c_i64),
-                ("out", c_vp), ("out_dtype", c_i32), ("ld_out", c_i64), ("geglu", c_i32), ("block_n", c_i32)]
+    _fields_ = [("a", c_vp), ("a_dtype", c_i32), ("n_img", c_i32), ("img_h", c_i32), ("img_w", c_i32),
+                ("cin", c_i32), ("taps", c_i32), ("w", c_vp), ("w_dtype", c_i32), ("n_out", c_i32), ("bias", c_vp),
+                ("bias_along_m", c_i32), ("row_bias", c_vp), ("row_bias_stride", c_i64), ("residual", c_vp),
+                ("residual_dtype", c_i32), ("ld_res", c_i64), ("out", c_vp), ("out_dtype", c_i32), ("ld_out", c_i64),
+                ("geglu", c_i32), ("block_n", c_i32)]
 
 
 class AttentionParams(C.Structure):
     _fields_ = [("q", c_vp), ("k", c_vp), ("v", c_vp), ("ld_q", c_i64), ("ld_k", c_i64), ("ld_v", c_i64),
-                ("out", c_vp), ("ld_out", c_i64), ("batch", c_i32), ("heads", c_i32), ("head_dim", c_i32),
-                ("sq", c_i32), ("skv", c_i32), ("scale", c_f32)]
+                ("out", c_vp), ("ld_out", c_i64), ("dtype", c_i32), ("batch", c_i32), ("heads", c_i32),
+                ("head_dim", c_i32), ("sq", c_i32), ("skv", c_i32), ("scale", c_f32)]
 
 
 class GroupNormParams(C.Structure):
     _fields_ = [("x1", c_vp), ("c1", c_i32), ("x2", c_vp), ("c2", c_i32), ("in_dtype", c_i32), ("n_img", c_i32),
                 ("hw", c_i32), ("groups", c_i32), ("eps", c_f32), ("gamma", c_vp), ("beta", c_vp), ("silu", c_i32),
-                ("y", c_vp), ("raw", c_vp), ("workspace", c_vp), ("workspace_bytes", c_i64)]
+                ("y", c_vp), ("raw", c_vp), ("out_dtype", c_i32), ("workspace", c_vp), ("workspace_bytes", c_i64)]
 
 
 class LayerNormParams(C.Structure):
     _fields_ = [("x", c_vp), ("in_dtype", c_i32), ("rows", c_i64), ("cols", c_i32), ("eps", c_f32), ("gamma", c_vp),
-                ("beta", c_vp), ("y", c_vp)]
+                ("beta", c_vp), ("y", c_vp), ("out_dtype", c_i32)]
 
 
 class Im2colParams(C.Structure):
     _fields_ = [("x", c_vp), ("in_dtype", c_i32), ("n_img", c_i32), ("n_src", c_i32), ("in_h", c_i32),
-                ("in_w", c_i32), ("cin", c_i32), ("stride", c_i32), ("out", c_vp), ("k_pad", c_i32)]
+                ("in_w", c_i32), ("cin", c_i32), ("stride", c_i32), ("out", c_vp), ("out_dtype", c_i32),
+                ("k_pad", c_i32)]
 
 
 class UpsampleParams(C.Structure):
     _fields_ = [("x", c_vp), ("in_dtype", c_i32), ("n_img", c_i32), ("h", c_i32), ("w", c_i32), ("c", c_i32),
-                ("out", c_vp)]
+                ("out", c_vp), ("out_dtype", c_i32)]
 
 
 class CfgSchedParams(C.Structure):
@@ -54,12 +57,12 @@ class CfgSchedParams(C.Structure):
 
 class SmallLinearParams(C.Structure):
     _fields_ = [("x", c_vp), ("rows", c_i32), ("k", c_i32), ("n", c_i32), ("sinusoid_dim", c_i32),
-                ("silu_in", c_i32), ("silu_out", c_i32), ("w", c_vp), ("b", c_vp), ("y", c_vp)]
+                ("silu_in", c_i32), ("silu_out", c_i32), ("w", c_vp), ("w_dtype", c_i32), ("b", c_vp), ("y", c_vp)]
 
 
 class SoftmaxParams(C.Structure):
-    _fields_ = [("x", c_vp), ("in_dtype", c_i32), ("ld_in", c_i64), ("y", c_vp), ("ld_out", c_i64), ("rows", c_i64),
-                ("cols", c_i32), ("scale", c_f32)]
+    _fields_ = [("x", c_vp), ("in_dtype", c_i32), ("ld_in", c_i64), ("y", c_vp), ("out_dtype", c_i32),
+                ("ld_out", c_i64), ("rows", c_i64), ("cols", c_i32), ("scale", c_f32)]
 
 
 class DenormU8Params(C.Structure):
@@ -89,7 +92,7 @@ SYMBOLS = {
     "b200sd_softmax_rows": (c_i32, [C.POINTER(SoftmaxParams), c_vp]),
     "b200sd_denorm_u8": (c_i32, [C.POINTER(DenormU8Params), c_vp]),
     "b200sd_cast": (c_i32, [C.POINTER(CastParams), c_vp]),
-    "b200sd_umma_selftest": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_vp]),
+    "b200sd_umma_selftest": (c_i32, [c_vp, c_i32, c_vp, c_i32, c_vp, c_i32, c_i32, c_i32, c_vp]),
 }
 
 _lib = None
@@ -108,8 +111,8 @@ def load() -> C.CDLL:
     for name, (res, args) in SYMBOLS.items():
         fn = getattr(lib, name)  # AttributeError if the export is missing
         fn.restype, fn.argtypes = res, args
-    if lib.b200sd_abi_version() != 1:
-        raise RuntimeError(f"libb200sd ABI version {lib.b200sd_abi_version()} != 1")
+    if lib.b200sd_abi_version() != ABI_VERSION:
+        raise RuntimeError(f"libb200sd ABI version {lib.b200sd_abi_version()} != {ABI_VERSION} (stale build?)")
     _lib = lib
     return lib
 

@@ -1,62 +1,66 @@
 """Weight packing and the per-layer call helpers shared by B200UNet and B200VAEDecoder.
 
-Layouts: activations NHWC; bf16 for every GEMM operand; the residual trunk in
-`trunk_dtype` (fp32 by default, bf16 optional); conv weights KRSC [Cout, 9*Cin]; linear weights [out, in].
+Layouts: activations NHWC; every tensor-core operand 16-bit in `op_dtype` (fp16 by default,
+bf16 selectable -- see DESIGN.md "operand format"); the residual trunk in `trunk_dtype` (fp32 by default);
+conv weights KRSC [Cout, 9*Cin]; linear weights [out, in].
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, Optional, Tuple
 
 import torch
 
 from . import ops
 
-BF = torch.bfloat16
+_OP_DTYPES = {"fp16": torch.float16, "float16": torch.float16, "bf16": torch.bfloat16, "bfloat16": torch.bfloat16}
+
+
+def default_op_dtype() -> torch.dtype:
+    """16-bit format of tensor-core operands.  fp16 keeps the single-step UNet error vs the fp32 oracle at ~1e-3;
+    bf16 (the reference's storage dtype, app/run-sd.py:39) sits at ~1.1e-2 with identical tensor throughput."""
+    return _OP_DTYPES[os.environ.get("B200SD_OPERAND_DTYPE", "fp16").lower()]
 
 
 # ------------------------------------------------------------------------------------------------ packing
-def pack_conv3x3(w: torch.Tensor) -> torch.Tensor:
-    """[Cout, Cin, 3, 3] -> bf16 [Cout, 9*Cin], K order (ky, kx, c)."""
+def pack_conv3x3(w: torch.Tensor, dtype: torch.dtype = torch.float16) -> torch.Tensor:
+    """[Cout, Cin, 3, 3] -> 16-bit [Cout, 9*Cin], K order (ky, kx, c)."""
     co, ci = w.shape[:2]
-    return w.permute(0, 2, 3, 1).reshape(co, 9 * ci).to(BF).contiguous()
+    return w.permute(0, 2, 3, 1).reshape(co, 9 * ci).to(dtype).contiguous()
 
 
-def pack_conv3x3_im2col(w: torch.Tensor, k_pad: int) -> torch.Tensor:
-    p = pack_conv3x3(w)
+def pack_conv3x3_im2col(w: torch.Tensor, k_pad: int, dtype: torch.dtype = torch.float16) -> torch.Tensor:
+    p = pack_conv3x3(w, dtype)
     if p.shape[1] < k_pad:
         p = torch.cat([p, p.new_zeros(p.shape[0], k_pad - p.shape[1])], dim=1)
     return p.contiguous()
 
 
-def pack_conv1x1(w: torch.Tensor) -> torch.Tensor:
-    return w.reshape(w.shape[0], w.shape[1]).to(BF).contiguous()
+def pack_conv1x1(w: torch.Tensor, dtype: torch.dtype = torch.float16) -> torch.Tensor:
+    return w.reshape(w.shape[0], w.shape[1]).to(dtype).contiguous()
 
 
-def pack_geglu(w: torch.Tensor, b: torch.Tensor, block_n: int) -> Tuple[torch.Tensor, torch.Tensor]:
+def pack_geglu(w: torch.Tensor, b: torch.Tensor, block_n: int,
+               dtype: torch.dtype = torch.float16) -> Tuple[torch.Tensor, torch.Tensor]:
     """[2*inner, K] (values then gates) -> rows interleaved per block_n tile: tile t = values[t*h:(t+1)*h] ++ gates[...]"""
     inner = w.shape[0] // 2
     h = block_n // 2
     assert inner % h == 0
     idx = torch.arange(inner, device=w.device).view(-1, h)
     order = torch.cat([idx, idx + inner], dim=1).reshape(-1)
-    return w[order].to(BF).contiguous(), b[order].float().contiguous()
-
-
-def pad_rows_to(w: torch.Tensor, mult: int) -> torch.Tensor:
-    return w
-
-
-def round_up(a: int, b: int) -> int:
-    return (a + b - 1) // b * b
+    return w[order].to(dtype).contiguous(), b[order].float().contiguous()
 
 
 # ------------------------------------------------------------------------------------------------ call helpers
 class Kernels:
-    """Stateless-ish helper bound to one device: owns the GroupNorm scratch and the dtype policy."""
+    """Helper bound to one device: owns the GroupNorm scratch and the dtype policy."""
 
-    def __init__(self, device: torch.device, trunk_dtype: torch.dtype = torch.float32):
+    def __init__(self, device: torch.device, trunk_dtype: torch.dtype = torch.float32,
+                 op_dtype: Optional[torch.dtype] = None):
         self.device = device
         self.trunk_dtype = trunk_dtype
+        self.op_dtype = op_dtype or default_op_dtype()
+        assert self.op_dtype in (torch.float16, torch.bfloat16)
         self._gn_ws: Optional[torch.Tensor] = None
 
     def gn_workspace(self, n_img: int, hw: int, groups: int) -> torch.Tensor:
@@ -69,19 +73,19 @@ class Kernels:
                   want_raw: bool = False, groups: int = 32):
         n, h, w, c1 = x1.shape
         c = c1 + (x2.shape[-1] if x2 is not None else 0)
-        y = torch.empty(n, h, w, c, device=self.device, dtype=BF)
+        y = torch.empty(n, h, w, c, device=self.device, dtype=self.op_dtype)
         raw = torch.empty_like(y) if want_raw else None
         ops.groupnorm(x1, x2, n, h * w, groups, eps, gamma, beta, silu, y, raw, self.gn_workspace(n, h * w, groups))
         return (y, raw) if want_raw else y
 
     def layernorm(self, x: torch.Tensor, gamma, beta, eps: float = 1e-5) -> torch.Tensor:
-        y = torch.empty(x.shape, device=self.device, dtype=BF)
+        y = torch.empty(x.shape, device=self.device, dtype=self.op_dtype)
         ops.layernorm(x, eps, gamma, beta, y)
         return y
 
     def conv3x3(self, a: torch.Tensor, w: torch.Tensor, bias, *, row_bias=None, residual=None,
                 out_dtype=None) -> torch.Tensor:
-        """a bf16 NHWC, w packed [Cout, 9*Cin]; stride 1, pad 1."""
+        """a 16-bit NHWC, w packed [Cout, 9*Cin]; stride 1, pad 1."""
         n, h, wd, cin = a.shape
         cout = w.shape[0]
         out = torch.empty(n, h, wd, cout, device=self.device, dtype=out_dtype or self.trunk_dtype)
@@ -94,7 +98,7 @@ class Kernels:
 
     def linear(self, a: torch.Tensor, w: torch.Tensor, bias, *, residual=None, out_dtype=None, geglu=False,
                out: Optional[torch.Tensor] = None, bias_along_m: bool = False, block_n: int = 0) -> torch.Tensor:
-        """a bf16 [M, K] (any leading dims), w bf16 [N, K]."""
+        """a 16-bit [M, K] (any leading dims), w 16-bit [N, K]."""
         k = a.shape[-1]
         m = a.numel() // k
         n_cols = w.shape[0] // 2 if geglu else w.shape[0]
@@ -107,18 +111,18 @@ class Kernels:
     def im2col(self, x: torch.Tensor, n_img: int, stride: int, k_pad: int) -> torch.Tensor:
         n_src, h, w, cin = x.shape
         oh, ow = (h - 1) // stride + 1, (w - 1) // stride + 1
-        out = torch.empty(n_img, oh, ow, k_pad, device=self.device, dtype=BF)
+        out = torch.empty(n_img, oh, ow, k_pad, device=self.device, dtype=self.op_dtype)
         ops.im2col3x3(x, n_img, n_src, h, w, cin, stride, out)
         return out
 
     def upsample2x(self, x: torch.Tensor) -> torch.Tensor:
         n, h, w, c = x.shape
-        out = torch.empty(n, 2 * h, 2 * w, c, device=self.device, dtype=BF)
+        out = torch.empty(n, 2 * h, 2 * w, c, device=self.device, dtype=self.op_dtype)
         ops.upsample2x(x, n, h, w, c, out)
         return out
 
     def attention(self, q, k, v, batch: int, heads: int, sq: int, skv: int, scale: float) -> torch.Tensor:
-        out = torch.empty(batch * sq, heads * 64, device=self.device, dtype=BF)
+        out = torch.empty(batch * sq, heads * 64, device=self.device, dtype=q.dtype)
         ops.attention(q, k, v, out, batch, heads, sq, skv, scale)
         return out
 
@@ -126,18 +130,19 @@ class Kernels:
 class ResnetParams:
     """packed weights of one ResnetBlock2D (keys: diffusers `...resnets.j.*`)."""
 
-    def __init__(self, sd: Dict[str, torch.Tensor], prefix: str, dev, temb_slice: Optional[Tuple[int, int]] = None):
+    def __init__(self, sd: Dict[str, torch.Tensor], prefix: str, dev, dtype: torch.dtype,
+                 temb_slice: Optional[Tuple[int, int]] = None):
         g = lambda k: sd[prefix + k].to(dev)
         self.n1_g, self.n1_b = g("norm1.weight").float().contiguous(), g("norm1.bias").float().contiguous()
         self.n2_g, self.n2_b = g("norm2.weight").float().contiguous(), g("norm2.bias").float().contiguous()
-        self.w1 = pack_conv3x3(g("conv1.weight"))
+        self.w1 = pack_conv3x3(g("conv1.weight"), dtype)
         self.b1 = g("conv1.bias").float().contiguous()
-        self.w2 = pack_conv3x3(g("conv2.weight"))
+        self.w2 = pack_conv3x3(g("conv2.weight"), dtype)
         self.b2 = g("conv2.bias").float().contiguous()
         self.cout = self.w1.shape[0]
         self.has_shortcut = (prefix + "conv_shortcut.weight") in sd
         if self.has_shortcut:
-            self.ws = pack_conv1x1(g("conv_shortcut.weight"))
+            self.ws = pack_conv1x1(g("conv_shortcut.weight"), dtype)
             self.bs = g("conv_shortcut.bias").float().contiguous()
         self.temb_slice = temb_slice  # columns of the per-step timestep table (conv1 bias folded in)
 
@@ -152,9 +157,9 @@ def run_resnet(K: Kernels, P: ResnetParams, x: torch.Tensor, skip: Optional[torc
         a, raw = K.groupnorm(x, None, P.n1_g, P.n1_b, eps, True), None
     if temb_table is not None:
         lo, hi = P.temb_slice
-        h1 = K.conv3x3(a, P.w1, None, row_bias=temb_table[:, lo:hi], out_dtype=BF)
+        h1 = K.conv3x3(a, P.w1, None, row_bias=temb_table[:, lo:hi], out_dtype=K.op_dtype)
     else:
-        h1 = K.conv3x3(a, P.w1, P.b1, out_dtype=BF)
+        h1 = K.conv3x3(a, P.w1, P.b1, out_dtype=K.op_dtype)
     b = K.groupnorm(h1, None, P.n2_g, P.n2_b, eps, True)
     if P.has_shortcut:
         res = K.linear(raw, P.ws, P.bs)  # 1x1 conv == linear over pixels

@@ -2,6 +2,7 @@
 
 Every op is an out-variant: the caller (torch) owns all device memory, the library only launches kernels
 on torch's current CUDA stream.  CUDA only -- there is deliberately no CPU implementation.
+Output element types are taken from the output tensors (bf16 / fp16 / fp32).
 """
 from __future__ import annotations
 
@@ -12,7 +13,7 @@ import torch
 
 from . import _lib as L
 
-_DT = {torch.bfloat16: L.BF16, torch.float32: L.F32}
+_DT = {torch.bfloat16: L.BF16, torch.float32: L.F32, torch.float16: L.F16}
 
 
 def _dt(t: torch.Tensor) -> int:
@@ -46,13 +47,52 @@ def pick_block_n(n_out: int, geglu: bool) -> int:
     return int(L.load().b200sd_gemm_pick_block_n(n_out, int(geglu)))
 
 
+# ------------------------------------------------------------------------------------------------ profiling
+# bench.py brackets every launch with CUDA events on the launching stream to get per-kernel-class time and the
+# algorithmic work (FLOPs for tensor-core kernels, bytes for HBM-bound ones) each launch did.
+_prof = None
+
+
+def profile_begin() -> None:
+    global _prof
+    _prof = []
+
+
+def profile_end():
+    """-> {kind: {"launches", "ms", "work"}}; work = algorithmic FLOPs (gemm, attention) or bytes (the rest)."""
+    global _prof
+    recs, _prof = _prof or [], None
+    torch.cuda.synchronize()
+    out = {}
+    for kind, work, s, e in recs:
+        d = out.setdefault(kind, {"launches": 0, "ms": 0.0, "work": 0.0})
+        d["launches"] += 1
+        d["ms"] += s.elapsed_time(e)
+        d["work"] += work
+    return out
+
+
+def _run(kind: str, work: float, fn, p) -> None:
+    if _prof is None:
+        L.check(fn(C.byref(p), _stream()), kind)
+        return
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    L.check(fn(C.byref(p), _stream()), kind)
+    e.record()
+    _prof.append((kind, work, s, e))
+
+
+def _nbytes(*ts) -> float:
+    return float(sum(t.numel() * t.element_size() for t in ts if t is not None))
+
+
 # ------------------------------------------------------------------------------------------------ impls
 def _gemm(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, row_bias_stride, residual, out,
           geglu, block_n):
-    assert a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
     p = L.GemmParams()
-    p.a, p.n_img, p.img_h, p.img_w, p.cin, p.taps = _ptr(a), n_img, img_h, img_w, cin, taps
-    p.w, p.n_out = _ptr(w), w.shape[0]
+    p.a, p.a_dtype, p.n_img, p.img_h, p.img_w, p.cin, p.taps = _ptr(a), _dt(a), n_img, img_h, img_w, cin, taps
+    p.w, p.w_dtype, p.n_out = _ptr(w), _dt(w), w.shape[0]
     assert w.shape[1] == taps * cin, (tuple(w.shape), taps, cin)
     p.bias, p.bias_along_m = _ptr(bias), int(bias_along_m)
     p.row_bias, p.row_bias_stride = _ptr(row_bias), row_bias_stride
@@ -60,27 +100,17 @@ def _gemm(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, ro
         p.residual, p.residual_dtype, p.ld_res = _ptr(residual), _dt(residual), residual.stride(-2)
     p.out, p.out_dtype, p.ld_out = _ptr(out), _dt(out), out.stride(-2)
     p.geglu, p.block_n = int(geglu), block_n
-    L.check(L.load().b200sd_gemm(C.byref(p), _stream()), "gemm")
+    m = n_img * img_h * img_w
+    _run("gemm", 2.0 * m * w.shape[0] * taps * cin, L.load().b200sd_gemm, p)
 
 
 def _attention(q, k, v, out, batch, heads, sq, skv, scale):
+    assert q.dtype == k.dtype == v.dtype == out.dtype
     p = L.AttentionParams()
     p.q, p.k, p.v, p.out = _ptr(q), _ptr(k), _ptr(v), _ptr(out)
     p.ld_q, p.ld_k, p.ld_v, p.ld_out = q.stride(-2), k.stride(-2), v.stride(-2), out.stride(-2)
-    p.batch, p.heads, p.head_dim, p.sq, p.skv, p.scale = batch, heads, 64, sq, skv, scale
-    L.check(L.load().b200sd_attention(C.byref(p), _stream()), "attention")
-
-
-def _gn_params(x1, x2, n_img, hw, groups, eps, gamma, beta, silu, y, raw, workspace):
-    p = L.GroupNormParams()
-    p.x1, p.c1 = _ptr(x1), x1.shape[-1]
-    p.x2, p.c2 = (_ptr(x2), x2.shape[-1]) if x2 is not None else (None, 0)
-    p.in_dtype, p.n_img, p.hw, p.groups, p.eps = _dt(x1), n_img, hw, groups, eps
-    p.gamma, p.beta, p.silu = _ptr(gamma), _ptr(beta), int(silu)
-    p.y, p.raw = _ptr(y), _ptr(raw)
-    if workspace is not None:
-        p.workspace, p.workspace_bytes = _ptr(workspace), workspace.numel() * workspace.element_size()
-    return p
+    p.dtype, p.batch, p.heads, p.head_dim, p.sq, p.skv, p.scale = _dt(q), batch, heads, 64, sq, skv, scale
+    _run("attention", 4.0 * batch * heads * sq * skv * 64, L.load().b200sd_attention, p)
 
 
 def groupnorm_workspace_bytes(n_img: int, hw: int, groups: int = 32) -> int:
@@ -92,28 +122,38 @@ def groupnorm_workspace_bytes(n_img: int, hw: int, groups: int = 32) -> int:
 def _groupnorm(x1, x2, n_img, hw, groups, eps, gamma, beta, silu, y, raw, workspace):
     if x2 is not None:
         assert x2.dtype == x1.dtype
-    p = _gn_params(x1, x2, n_img, hw, groups, eps, gamma, beta, silu, y, raw, workspace)
-    L.check(L.load().b200sd_groupnorm(C.byref(p), _stream()), "groupnorm")
+    if raw is not None:
+        assert raw.dtype == y.dtype
+    p = L.GroupNormParams()
+    p.x1, p.c1 = _ptr(x1), x1.shape[-1]
+    p.x2, p.c2 = (_ptr(x2), x2.shape[-1]) if x2 is not None else (None, 0)
+    p.in_dtype, p.n_img, p.hw, p.groups, p.eps = _dt(x1), n_img, hw, groups, eps
+    p.gamma, p.beta, p.silu = _ptr(gamma), _ptr(beta), int(silu)
+    p.y, p.raw, p.out_dtype = _ptr(y), _ptr(raw), _dt(y)
+    p.workspace, p.workspace_bytes = _ptr(workspace), workspace.numel() * workspace.element_size()
+    # algorithmic bytes: inputs read once for statistics and once to normalise, outputs written once
+    _run("groupnorm", 2 * _nbytes(x1, x2) + _nbytes(y, raw), L.load().b200sd_groupnorm, p)
 
 
 def _layernorm(x, eps, gamma, beta, y):
     p = L.LayerNormParams()
     p.x, p.in_dtype, p.rows, p.cols, p.eps = _ptr(x), _dt(x), x.numel() // x.shape[-1], x.shape[-1], eps
-    p.gamma, p.beta, p.y = _ptr(gamma), _ptr(beta), _ptr(y)
-    L.check(L.load().b200sd_layernorm(C.byref(p), _stream()), "layernorm")
+    p.gamma, p.beta, p.y, p.out_dtype = _ptr(gamma), _ptr(beta), _ptr(y), _dt(y)
+    _run("layernorm", _nbytes(x, y), L.load().b200sd_layernorm, p)
 
 
 def _im2col3x3(x, n_img, n_src, in_h, in_w, cin, stride, out):
     p = L.Im2colParams()
-    p.x, p.in_dtype, p.n_img, p.n_src, p.in_h, p.in_w, p.cin, p.stride = _ptr(x), _dt(x), n_img, n_src, in_h, in_w, cin, stride
-    p.out, p.k_pad = _ptr(out), out.shape[-1]
-    L.check(L.load().b200sd_im2col3x3(C.byref(p), _stream()), "im2col3x3")
+    p.x, p.in_dtype, p.n_img, p.n_src, p.in_h, p.in_w, p.cin, p.stride = (_ptr(x), _dt(x), n_img, n_src, in_h, in_w,
+                                                                         cin, stride)
+    p.out, p.out_dtype, p.k_pad = _ptr(out), _dt(out), out.shape[-1]
+    _run("im2col3x3", _nbytes(x, out), L.load().b200sd_im2col3x3, p)
 
 
 def _upsample2x(x, n_img, h, w, c, out):
     p = L.UpsampleParams()
-    p.x, p.in_dtype, p.n_img, p.h, p.w, p.c, p.out = _ptr(x), _dt(x), n_img, h, w, c, _ptr(out)
-    L.check(L.load().b200sd_upsample2x(C.byref(p), _stream()), "upsample2x")
+    p.x, p.in_dtype, p.n_img, p.h, p.w, p.c, p.out, p.out_dtype = _ptr(x), _dt(x), n_img, h, w, c, _ptr(out), _dt(out)
+    _run("upsample2x", _nbytes(x, out), L.load().b200sd_upsample2x, p)
 
 
 def _cfg_sched_step(eps2, x, x0_prev, coef, step_index):
@@ -122,37 +162,37 @@ def _cfg_sched_step(eps2, x, x0_prev, coef, step_index):
     p.coef, p.step_index, p.n = _ptr(coef), _ptr(step_index), x.numel()
     assert eps2.numel() == 2 * x.numel() and x.dtype == torch.float32 and coef.dtype == torch.float32
     assert step_index is None or step_index.dtype == torch.int32
-    L.check(L.load().b200sd_cfg_sched_step(C.byref(p), _stream()), "cfg_sched_step")
+    _run("cfg_sched_step", _nbytes(eps2, x, x, x0_prev, x0_prev), L.load().b200sd_cfg_sched_step, p)
 
 
 def _small_linear(x, rows, k, sinusoid_dim, silu_in, silu_out, w, b, y):
     p = L.SmallLinearParams()
     p.x, p.rows, p.k, p.n = _ptr(x), rows, k, w.shape[0]
     p.sinusoid_dim, p.silu_in, p.silu_out = sinusoid_dim, int(silu_in), int(silu_out)
-    p.w, p.b, p.y = _ptr(w), _ptr(b), _ptr(y)
-    assert x.dtype == torch.float32 and w.dtype == torch.bfloat16 and y.dtype == torch.float32 and w.shape[1] == k
-    L.check(L.load().b200sd_small_linear(C.byref(p), _stream()), "small_linear")
+    p.w, p.w_dtype, p.b, p.y = _ptr(w), _dt(w), _ptr(b), _ptr(y)
+    assert x.dtype == torch.float32 and y.dtype == torch.float32 and w.shape[1] == k
+    _run("small_linear", _nbytes(w, y), L.load().b200sd_small_linear, p)
 
 
 def _softmax_rows(x, y, rows, cols, scale):
     p = L.SoftmaxParams()
-    p.x, p.in_dtype, p.ld_in, p.y, p.ld_out = _ptr(x), _dt(x), x.stride(-2), _ptr(y), y.stride(-2)
+    p.x, p.in_dtype, p.ld_in = _ptr(x), _dt(x), x.stride(-2)
+    p.y, p.out_dtype, p.ld_out = _ptr(y), _dt(y), y.stride(-2)
     p.rows, p.cols, p.scale = rows, cols, scale
-    assert y.dtype == torch.bfloat16
-    L.check(L.load().b200sd_softmax_rows(C.byref(p), _stream()), "softmax_rows")
+    _run("softmax_rows", float(rows) * cols * (x.element_size() + 2), L.load().b200sd_softmax_rows, p)
 
 
 def _denorm_u8(x, out):
     p = L.DenormU8Params()
     p.x, p.in_dtype, p.out, p.n = _ptr(x), _dt(x), _ptr(out), x.numel()
     assert out.dtype == torch.uint8 and out.numel() == x.numel()
-    L.check(L.load().b200sd_denorm_u8(C.byref(p), _stream()), "denorm_u8")
+    _run("denorm_u8", _nbytes(x, out), L.load().b200sd_denorm_u8, p)
 
 
 def _cast(x, y):
     p = L.CastParams()
     p.x, p.in_dtype, p.y, p.out_dtype, p.n = _ptr(x), _dt(x), _ptr(y), _dt(y), x.numel()
-    L.check(L.load().b200sd_cast(C.byref(p), _stream()), "cast")
+    _run("cast", _nbytes(x, y), L.load().b200sd_cast, p)
 
 
 def umma_selftest(a: torch.Tensor, b: torch.Tensor, b_mn_major: bool) -> torch.Tensor:
@@ -160,7 +200,8 @@ def umma_selftest(a: torch.Tensor, b: torch.Tensor, b_mn_major: bool) -> torch.T
     k = a.shape[1]
     n = b.shape[1] if b_mn_major else b.shape[0]
     d = torch.empty(128, n, device=a.device, dtype=torch.float32)
-    L.check(L.load().b200sd_umma_selftest(_ptr(a), _ptr(b), _ptr(d), n, k, int(b_mn_major), _stream()), "umma_selftest")
+    L.check(L.load().b200sd_umma_selftest(_ptr(a), _dt(a), _ptr(b), _dt(b), _ptr(d), n, k, int(b_mn_major),
+                                          _stream()), "umma_selftest")
     return d
 
 

@@ -80,7 +80,7 @@ class B200Pipeline:
                   "x0_prev": torch.zeros(B, h, w, 4, device=dev, dtype=torch.float32) if sch.needs_x0_prev else None,
                   "t": torch.zeros(1, device=dev, dtype=torch.float32),
                   "step_idx": torch.zeros(1, device=dev, dtype=torch.int32),
-                  "ctx2": torch.zeros(ctx2.shape, device=dev, dtype=torch.bfloat16)}
+                  "ctx2": torch.zeros(ctx2.shape, device=dev, dtype=self.unet.K.op_dtype)}
             self._static, self._graph, self._graph_key = st, None, key
         st = self._static
         st["t_table"] = sch.timesteps.to(torch.float32)
@@ -188,7 +188,7 @@ class B200Pipeline:
         dev = self.device
         lat = latents.to(dev, torch.float32, non_blocking=True).permute(0, 2, 3, 1).contiguous()
         ctx2 = torch.cat([negative_prompt_embeds.to(dev, non_blocking=True),
-                          prompt_embeds.to(dev, non_blocking=True)]).to(torch.bfloat16)
+                          prompt_embeds.to(dev, non_blocking=True)]).to(self.unet.K.op_dtype)
         final = self.denoise(lat, ctx2, num_inference_steps, guidance_scale)
         if output_type == "latent":
             images = final.permute(0, 3, 1, 2).clone()

@@ -1,0 +1,221 @@
+"""Serving host for the SD2.1 path: the reference's FastAPI surface (app/run-sd.py:153-203) and environment
+contract (app/run-sd.py:15-21) on top of B200Pipeline, one engine per GPU.
+
+Kept from the reference: env names APP, POD_NAME, NODEPOOL, MODEL_ID, DEVICE, COMPILED_MODEL_ID, NUM_OF_RUNS_INF;
+routes GET /, GET /load/{n_runs}/infer/{n_inf}, POST /genimage, GET /health, GET /readiness, gradio at /serve (only
+if gradio is importable); response shapes; the three metric names `<APP>-counter`, `<NODEPOOL>`, `<APP>-latency`
+(app/run-sd.py:166-173); the nearest-rank percentile rule of LatencyCollector (app/run-sd.py:84-102).
+Added: DEVICE=b200, POST /generate {prompt, num_inference_steps[, height, width]}, a lock around the engine (the
+reference shares one stateful pipeline between threadpool handlers without one, app/run-sd.py:137-142).
+"""
+from __future__ import annotations
+
+import base64
+import io
+import json
+import math
+import os
+import threading
+import time
+from typing import Callable, Dict, List, Optional
+
+ENV_KEYS = ("APP", "POD_NAME", "NODEPOOL", "MODEL_ID", "DEVICE", "COMPILED_MODEL_ID", "NUM_OF_RUNS_INF")
+CW_NAMESPACE = "hw-agnostic-infer"
+WARMUP_PROMPT = "portrait photo of a old warrior chief"
+LOAD_PROMPT = "a photo of an astronaut riding a horse on mars"
+
+
+def read_env(env=os.environ) -> Dict[str, str]:
+    """All seven variables are required, as in the reference (KeyError at import if one is unset)."""
+    cfg = {k: env[k] for k in ENV_KEYS}
+    cfg["NUM_OF_RUNS_INF"] = int(cfg["NUM_OF_RUNS_INF"])
+    return cfg
+
+
+# ---------------------------------------------------------------------------------------------------- metrics
+class MetricSink:
+    """`put_metric_data` stand-in: boto3/CloudWatch when importable and enabled, else JSON lines on stdout."""
+
+    def __init__(self, namespace: str = CW_NAMESPACE, region: str = "us-west-2", use_cloudwatch: Optional[bool] = None):
+        self.namespace = namespace
+        self.records: List[dict] = []
+        self._cw = None
+        want = os.environ.get("B200SD_CLOUDWATCH", "0") == "1" if use_cloudwatch is None else use_cloudwatch
+        if want:
+            try:
+                import boto3  # type: ignore
+                self._cw = boto3.client("cloudwatch", region_name=region)
+            except Exception:  # boto3 is absent on this box
+                self._cw = None
+
+    def publish(self, name: str, value: float, unit: str) -> dict:
+        rec = {"Namespace": self.namespace, "MetricName": name, "Value": value, "Unit": unit}
+        self.records.append(rec)
+        if self._cw is not None:
+            return self._cw.put_metric_data(Namespace=self.namespace,
+                                            MetricData=[{"MetricName": name, "Value": value, "Unit": unit}])
+        print(json.dumps({"metric": rec}), flush=True)
+        return rec
+
+
+# ---------------------------------------------------------------------------------------------------- latency
+class LatencyCollector:
+    """Wall-clock samples with the reference's percentile rule: position p% of the way into the sorted list,
+    rounded up only when the fractional part exceeds one half (app/run-sd.py:94-102)."""
+
+    def __init__(self):
+        self.start: Optional[float] = None
+        self.latency_list: List[float] = []
+
+    def pre_hook(self, *_):
+        self.start = time.time()
+
+    def hook(self, *_):
+        self.latency_list.append(time.time() - self.start)
+
+    def percentile(self, percent: float) -> float:
+        ordered = sorted(self.latency_list)
+        last = len(ordered) - 1
+        pos = len(ordered) * percent / 100
+        lo, hi = min(math.floor(pos), last), min(math.ceil(pos), last)
+        return ordered[hi] if pos - lo > 0.5 else ordered[lo]
+
+
+def benchmark(n_runs: int, test_name: str, model: Callable, model_inputs: dict, pod_name: str = "") -> str:
+    """n_runs timed calls, no warm-up; report string in the reference's format (app/run-sd.py:49-82)."""
+    lc = LatencyCollector()
+    for _ in range(n_runs):
+        lc.pre_hook()
+        model(**model_inputs)
+        lc.hook()
+    parts = [f"Latency P{p}={lc.percentile(p) * 1000:.1f}" for p in (0, 50, 90, 95, 99, 100)]
+    report = f"RESULT FOR {test_name} on {pod_name}: " + " ".join(parts)
+    print(report, flush=True)
+    return report
+
+
+def serialize_image(image) -> str:
+    """PIL image -> base64 PNG (app/run-sd.py:177-181)."""
+    buf = io.BytesIO()
+    image.save(buf, format="PNG")
+    return base64.b64encode(buf.getvalue()).decode("utf-8")
+
+
+# ---------------------------------------------------------------------------------------------------- engine
+class Engine:
+    """One pipeline on one GPU behind a lock; `text2img` mirrors app/run-sd.py:137-142."""
+
+    def __init__(self, pipe, default_steps: int):
+        self.pipe, self.default_steps = pipe, default_steps
+        self._lock = threading.Lock()
+
+    def __call__(self, **model_args):
+        with self._lock:
+            return self.pipe(**model_args)
+
+    def text2img(self, prompt: str, steps: Optional[int] = None):
+        t0 = time.time()
+        image = self(prompt=prompt, num_inference_steps=steps or self.default_steps).images[0]
+        return image, str(time.time() - t0)
+
+
+def build_random_init_pipeline(model_id: str, device: str = "cuda:0", seed: int = 0):
+    """There are no checkpoints on this box (no network): builds the SD2.1 architecture named by `model_id`
+    (`...-base` = 512^2 epsilon-prediction, otherwise 768^2 v-prediction) with seeded random weights.
+    With real weights, pass a diffusers-layout state_dict to B200UNet / B200VAEDecoder instead."""
+    import torch
+    import torch.nn as nn
+
+    from . import B200Pipeline, B200Scheduler, B200UNet, B200VAEDecoder, UNetConfig, VAEConfig
+    from ._randinit import random_state_dicts
+
+    base = model_id.rstrip("/").endswith("-base")
+    ucfg = UNetConfig(sample_size=64 if base else 96, prediction_type="epsilon" if base else "v_prediction")
+    usd, vsd = random_state_dicts(ucfg, VAEConfig(), seed)
+    dev = torch.device(device)
+    unet, vae = B200UNet(usd, ucfg, dev), B200VAEDecoder(vsd, VAEConfig(), dev)
+    return B200Pipeline(unet, vae, B200Scheduler("ddim", ucfg.prediction_type, dev))
+
+
+def create_app(engine: Engine, cfg: Dict[str, str], sink: Optional[MetricSink] = None):
+    """FastAPI app with the reference's routes and payloads."""
+    from fastapi import FastAPI
+
+    sink = sink or MetricSink()
+    app = FastAPI()
+    model_id, pod, device = cfg["MODEL_ID"], cfg["POD_NAME"], cfg["DEVICE"]
+
+    @app.get("/")
+    def read_main():
+        return {"message": "This is" + model_id + " pod " + pod + " in AWS EC2 " + device +
+                           " instance; try /load/{n_runs}/infer/{n_inf}; /genimage http post with user prompt "}
+
+    @app.get("/load/{n_runs}/infer/{n_inf}")
+    def load(n_runs: int, n_inf: int):
+        t0 = time.time()
+        report = benchmark(n_runs, "stable_diffusion_512", engine,
+                           {"prompt": LOAD_PROMPT, "num_inference_steps": n_inf}, pod)
+        total = time.time() - t0
+        sink.publish(cfg["APP"] + "-counter", 1, "Count")
+        sink.publish(cfg["NODEPOOL"], 1, "Count")
+        sink.publish(cfg["APP"] + "-latency", total, "Seconds")
+        return {"message": "benchmark report:" + report}
+
+    @app.post("/genimage")
+    def generate_image_post(request: dict):
+        prompt = request.get("prompt")
+        image, latency = engine.text2img(prompt)
+        return {"prompt": prompt, "response": serialize_image(image), "latency": latency}
+
+    @app.post("/generate")
+    def generate(request: dict):
+        """superset endpoint in the shape of the reference's Flux model-API (app/flux_model_api.py:331-360)"""
+        prompt = request.get("prompt")
+        args = {"prompt": prompt, "num_inference_steps": int(request.get("num_inference_steps", engine.default_steps))}
+        for k in ("height", "width"):
+            if request.get(k) is not None:
+                args[k] = int(request[k])
+        t0 = time.time()
+        image = engine(**args).images[0]
+        return {"image": serialize_image(image), "execution_time": time.time() - t0}
+
+    @app.get("/health")
+    def healthy():
+        return {"message": pod + "is healthy"}
+
+    @app.get("/readiness")
+    def ready():
+        return {"message": pod + "is ready"}
+
+    try:  # gradio is optional (absent on this box)
+        import gradio as gr  # type: ignore
+
+        io_ = gr.Interface(fn=engine.text2img, inputs=["text"], outputs=[gr.Image(height=512, width=512), "text"],
+                           title=model_id + " on " + device + "; pod name " + pod)
+        app = gr.mount_gradio_app(app, io_, path="/serve")
+    except Exception:
+        pass
+    return app
+
+
+def create_app_from_env():
+    """`uvicorn b200sd.serving:create_app_from_env --factory` -- the analogue of `uvicorn run-sd:app`
+    (app/run-sd.sh:14).  Builds the pipeline, runs the reference's warm-up inference, then serves."""
+    cfg = read_env()
+    if cfg["DEVICE"] not in ("b200", "cuda"):
+        raise RuntimeError(f"DEVICE={cfg['DEVICE']!r}: this host serves DEVICE=b200 (sm_100a) only")
+    pipe = build_random_init_pipeline(cfg["MODEL_ID"], os.environ.get("B200SD_CUDA_DEVICE", "cuda:0"))
+    pipe.enable_attention_slicing()
+    engine = Engine(pipe, cfg["NUM_OF_RUNS_INF"])
+    engine(prompt=WARMUP_PROMPT, num_inference_steps=cfg["NUM_OF_RUNS_INF"])  # readiness only after warm-up
+    return create_app(engine, cfg)
+
+
+# ---------------------------------------------------------------------------------------------------- sharding
+def shard_range(n_items: int, rank: int, world: int) -> range:
+    """Data-parallel serving: independent prompts are split contiguously across replicas (one per GPU), the
+    in-box analogue of the reference's N pods behind ALB round-robin (sd21-equal-routing-ing.yaml:33).
+    No collective on the data path."""
+    base, extra = divmod(n_items, world)
+    start = rank * base + min(rank, extra)
+    return range(start, start + base + (1 if rank < extra else 0))

@@ -12,11 +12,11 @@ import torch
 
 from . import ops
 from .config import UNetConfig
-from .layers import BF, Kernels, ResnetParams, pack_conv3x3, pack_conv3x3_im2col, pack_geglu, run_resnet
+from .layers import Kernels, ResnetParams, pack_conv3x3, pack_conv3x3_im2col, pack_geglu, run_resnet
 
 
 class _TransformerParams:
-    def __init__(self, sd, prefix: str, dev, dim: int, heads: int):
+    def __init__(self, sd, prefix: str, dev, dim: int, heads: int, BF: torch.dtype):
         g = lambda k: sd[prefix + k].to(dev)
         f = lambda k: g(k).float().contiguous()
         b = lambda k: g(k).to(BF).contiguous()
@@ -34,13 +34,13 @@ class _TransformerParams:
         self.o2_w, self.o2_b = b(t + "attn2.to_out.0.weight"), f(t + "attn2.to_out.0.bias")
         w1, b1 = g(t + "ff.net.0.proj.weight"), g(t + "ff.net.0.proj.bias")
         self.ff_block_n = ops.pick_block_n(w1.shape[0], True)
-        self.ff1_w, self.ff1_b = pack_geglu(w1, b1, self.ff_block_n)
+        self.ff1_w, self.ff1_b = pack_geglu(w1, b1, self.ff_block_n, BF)
         self.ff2_w, self.ff2_b = b(t + "ff.net.2.weight"), f(t + "ff.net.2.bias")
 
 
 class B200UNet(torch.nn.Module):
     def __init__(self, state_dict: Dict[str, torch.Tensor], config=None, device="cuda",
-                 trunk_dtype: torch.dtype = torch.float32):
+                 trunk_dtype: torch.dtype = torch.float32, op_dtype: Optional[torch.dtype] = None):
         super().__init__()
         self.config = UNetConfig.from_any(config if config is not None else UNetConfig())
         cfg = self.config
@@ -48,7 +48,8 @@ class B200UNet(torch.nn.Module):
         if self._device.type != "cuda":
             raise RuntimeError("B200UNet needs a CUDA device (there is no CPU path)")
         ops.check_device(self._device.index or 0)
-        self.K = Kernels(self._device, trunk_dtype)
+        self.K = Kernels(self._device, trunk_dtype, op_dtype)
+        BF = self.K.op_dtype
         self._dtype = BF
         dev, sd = self._device, state_dict
         boc, L = cfg.block_out_channels, cfg.layers_per_block
@@ -69,22 +70,22 @@ class B200UNet(torch.nn.Module):
             self._temb_off += w.shape[0]
             self._temb_w.append(w.to(BF))
             self._temb_b.append(bias)
-            return ResnetParams(sd, prefix, dev, (lo, self._temb_off))
+            return ResnetParams(sd, prefix, dev, BF, (lo, self._temb_off))
 
-        self.conv_in_w = pack_conv3x3_im2col(sd["conv_in.weight"].to(dev), 64)
+        self.conv_in_w = pack_conv3x3_im2col(sd["conv_in.weight"].to(dev), 64, BF)
         self.conv_in_b = f("conv_in.bias")
         self.down = []
         for i, co in enumerate(boc):
             blk = {"res": [resnet(f"down_blocks.{i}.resnets.{j}.") for j in range(L)], "attn": None, "down": None}
             if cfg.down_has_attn[i]:
                 blk["attn"] = [_TransformerParams(sd, f"down_blocks.{i}.attentions.{j}.", dev, co,
-                                                  cfg.attention_head_dim[i]) for j in range(L)]
+                                                  cfg.attention_head_dim[i], BF) for j in range(L)]
             if i < nb - 1:
                 p = f"down_blocks.{i}.downsamplers.0.conv."
-                blk["down"] = (pack_conv3x3(sd[p + "weight"].to(dev)), f(p + "bias"))
+                blk["down"] = (pack_conv3x3(sd[p + "weight"].to(dev), BF), f(p + "bias"))
             self.down.append(blk)
         self.mid_res = [resnet(f"mid_block.resnets.{j}.") for j in range(2)]
-        self.mid_attn = _TransformerParams(sd, "mid_block.attentions.0.", dev, boc[-1], cfg.attention_head_dim[-1])
+        self.mid_attn = _TransformerParams(sd, "mid_block.attentions.0.", dev, boc[-1], cfg.attention_head_dim[-1], BF)
         self.up = []
         rev = list(reversed(boc))
         rev_heads = list(reversed(cfg.attention_head_dim))
@@ -92,14 +93,14 @@ class B200UNet(torch.nn.Module):
         for i, co in enumerate(rev):
             blk = {"res": [resnet(f"up_blocks.{i}.resnets.{j}.") for j in range(L + 1)], "attn": None, "up": None}
             if rev_attn[i]:
-                blk["attn"] = [_TransformerParams(sd, f"up_blocks.{i}.attentions.{j}.", dev, co, rev_heads[i])
+                blk["attn"] = [_TransformerParams(sd, f"up_blocks.{i}.attentions.{j}.", dev, co, rev_heads[i], BF)
                                for j in range(L + 1)]
             if i < nb - 1:
                 p = f"up_blocks.{i}.upsamplers.0.conv."
-                blk["up"] = (pack_conv3x3(sd[p + "weight"].to(dev)), f(p + "bias"))
+                blk["up"] = (pack_conv3x3(sd[p + "weight"].to(dev), BF), f(p + "bias"))
             self.up.append(blk)
         self.out_g, self.out_b = f("conv_norm_out.weight"), f("conv_norm_out.bias")
-        self.conv_out_w = pack_conv3x3(sd["conv_out.weight"].to(dev))
+        self.conv_out_w = pack_conv3x3(sd["conv_out.weight"].to(dev), BF)
         self.conv_out_b = f("conv_out.bias")
         self.temb_all_w = torch.cat(self._temb_w).contiguous()
         self.temb_all_b = torch.cat(self._temb_b).contiguous()
@@ -132,6 +133,7 @@ class B200UNet(torch.nn.Module):
     # ---- pieces ---------------------------------------------------------------------------------------
     def project_context(self, ctx: torch.Tensor) -> List[torch.Tensor]:
         """cross-attention K/V of every transformer for a prompt batch; step-invariant, so computed once."""
+        BF = self.K.op_dtype
         ctx_bf = ctx.to(device=self._device, dtype=BF).contiguous()
         n, s, d = ctx_bf.shape
         flat = ctx_bf.view(n * s, d)
@@ -152,6 +154,7 @@ class B200UNet(torch.nn.Module):
 
     def _transformer(self, T: _TransformerParams, x: torch.Tensor, kv: torch.Tensor, ctx_len: int) -> torch.Tensor:
         K = self.K
+        BF = K.op_dtype
         n, h, w, c = x.shape
         s = h * w
         m = n * s

@@ -14,7 +14,7 @@ import torch
 
 from . import ops
 from .config import VAEConfig
-from .layers import BF, Kernels, ResnetParams, pack_conv3x3, run_resnet
+from .layers import Kernels, ResnetParams, pack_conv3x3, run_resnet
 
 
 class B200PostQuantConv(torch.nn.Module):
@@ -26,7 +26,7 @@ class B200PostQuantConv(torch.nn.Module):
 
 class B200VAEDecoder(torch.nn.Module):
     def __init__(self, state_dict: Dict[str, torch.Tensor], config=None, device="cuda",
-                 trunk_dtype: torch.dtype = torch.float32, max_images_per_pass: int = 4):
+                 trunk_dtype: torch.dtype = torch.float32, op_dtype=None, max_images_per_pass: int = 4):
         super().__init__()
         self.config = VAEConfig.from_any(config if config is not None else VAEConfig())
         cfg = self.config
@@ -34,7 +34,8 @@ class B200VAEDecoder(torch.nn.Module):
         if self._device.type != "cuda":
             raise RuntimeError("B200VAEDecoder needs a CUDA device (there is no CPU path)")
         ops.check_device(self._device.index or 0)
-        self.K = Kernels(self._device, trunk_dtype)
+        self.K = Kernels(self._device, trunk_dtype, op_dtype)
+        BF = self.K.op_dtype
         self.max_images_per_pass = max_images_per_pass
         dev, sd = self._device, state_dict
         f = lambda k: sd[k].to(dev).float().contiguous()
@@ -52,7 +53,7 @@ class B200VAEDecoder(torch.nn.Module):
         self.conv_in_w = torch.cat([folded, folded.new_zeros(rev[0], 64 - folded.shape[1])], 1).to(BF).contiguous()
         self.conv_in_b = f("decoder.conv_in.bias")
 
-        self.mid_res = [ResnetParams(sd, f"decoder.mid_block.resnets.{j}.", dev) for j in range(2)]
+        self.mid_res = [ResnetParams(sd, f"decoder.mid_block.resnets.{j}.", dev, BF) for j in range(2)]
         a = "decoder.mid_block.attentions.0."
         self.at_g, self.at_b = f(a + "group_norm.weight"), f(a + "group_norm.bias")
         self.wq, self.bq = b(a + "to_q.weight"), f(a + "to_q.bias")
@@ -61,19 +62,19 @@ class B200VAEDecoder(torch.nn.Module):
         self.wo, self.bo = b(a + "to_out.0.weight"), f(a + "to_out.0.bias")
         self.up = []
         for i, co in enumerate(rev):
-            blk = {"res": [ResnetParams(sd, f"decoder.up_blocks.{i}.resnets.{j}.", dev)
+            blk = {"res": [ResnetParams(sd, f"decoder.up_blocks.{i}.resnets.{j}.", dev, BF)
                            for j in range(cfg.layers_per_block + 1)], "up": None}
             if i < len(rev) - 1:
                 p = f"decoder.up_blocks.{i}.upsamplers.0.conv."
-                blk["up"] = (pack_conv3x3(sd[p + "weight"].to(dev)), f(p + "bias"))
+                blk["up"] = (pack_conv3x3(sd[p + "weight"].to(dev), BF), f(p + "bias"))
             self.up.append(blk)
         self.out_g, self.out_b = f("decoder.conv_norm_out.weight"), f("decoder.conv_norm_out.bias")
-        self.conv_out_w = pack_conv3x3(sd["decoder.conv_out.weight"].to(dev))
+        self.conv_out_w = pack_conv3x3(sd["decoder.conv_out.weight"].to(dev), BF)
         self.conv_out_b = f("decoder.conv_out.bias")
 
     @property
     def dtype(self):
-        return BF
+        return self.K.op_dtype
 
     @property
     def device(self):
@@ -81,6 +82,7 @@ class B200VAEDecoder(torch.nn.Module):
 
     def _mid_attention(self, h: torch.Tensor) -> torch.Tensor:
         K = self.K
+        BF = K.op_dtype
         n, hh, ww, c = h.shape
         s = hh * ww
         a = K.groupnorm(h, None, self.at_g, self.at_b, 1e-6, False).view(n, s, c)

@@ -26,8 +26,9 @@ constexpr uint32_t ATT_TMEM_S0 = 0, ATT_TMEM_S1 = 128, ATT_TMEM_O = 256;
 struct AttnKernelParams {
     int sq, skv, n_kv_tiles;
     float scale_log2;  // scale * log2(e)
-    __nv_bfloat16* out;
+    uint16_t* out;
     long long ld_out;
+    int is_f16;        // q/k/v/P/out are fp16 (1) or bf16 (0)
 };
 
 __global__ void __launch_bounds__(ATT_THREADS, 1)
@@ -94,8 +95,9 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
         __syncwarp();
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc_qk = umma_idesc_bf16(128, ATT_BN, 0, 0);
-            constexpr uint32_t idesc_pv = umma_idesc_bf16(128, ATT_D, 0, 1);  // V is MN-major
+            const uint32_t bf = p.is_f16 ? 0u : 1u;
+            const uint32_t idesc_qk = umma_idesc(128, ATT_BN, bf, bf, 0, 0);
+            const uint32_t idesc_pv = umma_idesc(128, ATT_D, bf, bf, 0, 1);  // V is MN-major
             const uint32_t q_addr = smem_u32(sQ);
             auto issue_qk = [&](int j, int stage) {
                 const uint32_t k_addr = smem_u32(sKV + stage * 2 * ATT_TILE);
@@ -143,6 +145,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
         const int quad = warp & 3;
         const int row = quad * 32 + lane;
         const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
+        const bool f16 = p.is_f16 != 0;
         float m_used = 0.f, l = 0.f;
         for (int j = 0; j < n_tiles; ++j) {
             mbar_wait(&s_full[j & 1], (j >> 1) & 1);
@@ -211,8 +214,8 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                     const int chunk = col0 >> 6;             // which 64-wide kv chunk
                     const int cc = (col0 & 63) >> 3;         // 16-byte chunk inside the 128-byte row
                     *reinterpret_cast<uint4*>(prow + chunk * ATT_TILE + ((cc ^ (row & 7)) << 4)) =
-                        make_uint4(pack_bf16x2(e[0], e[1]), pack_bf16x2(e[2], e[3]), pack_bf16x2(e[4], e[5]),
-                                   pack_bf16x2(e[6], e[7]));
+                        make_uint4(pack_h2(e[0], e[1], f16), pack_h2(e[2], e[3], f16), pack_h2(e[4], e[5], f16),
+                                   pack_h2(e[6], e[7], f16));
                 }
             }
             l += lsum;
@@ -227,21 +230,21 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
         tc_fence_after();
         const float inv = 1.0f / l;
         const int qrow = q0 + row;
-        __nv_bfloat16* orow = p.out + ((long long)b * p.sq + qrow) * p.ld_out + head * ATT_D;
+        uint16_t* orow = p.out + ((long long)b * p.sq + qrow) * p.ld_out + head * ATT_D;
 #pragma unroll
         for (int c = 0; c < ATT_D / 16; ++c) {
             uint32_t o[16];
             tmem_ld_x16(tmem_base + ATT_TMEM_O + lane_off + c * 16, o);
             tmem_ld_wait();
             if (qrow < p.sq) {
-                uint4 v0 = make_uint4(pack_bf16x2(__uint_as_float(o[0]) * inv, __uint_as_float(o[1]) * inv),
-                                      pack_bf16x2(__uint_as_float(o[2]) * inv, __uint_as_float(o[3]) * inv),
-                                      pack_bf16x2(__uint_as_float(o[4]) * inv, __uint_as_float(o[5]) * inv),
-                                      pack_bf16x2(__uint_as_float(o[6]) * inv, __uint_as_float(o[7]) * inv));
-                uint4 v1 = make_uint4(pack_bf16x2(__uint_as_float(o[8]) * inv, __uint_as_float(o[9]) * inv),
-                                      pack_bf16x2(__uint_as_float(o[10]) * inv, __uint_as_float(o[11]) * inv),
-                                      pack_bf16x2(__uint_as_float(o[12]) * inv, __uint_as_float(o[13]) * inv),
-                                      pack_bf16x2(__uint_as_float(o[14]) * inv, __uint_as_float(o[15]) * inv));
+                uint4 v0 = make_uint4(pack_h2(__uint_as_float(o[0]) * inv, __uint_as_float(o[1]) * inv, f16),
+                                      pack_h2(__uint_as_float(o[2]) * inv, __uint_as_float(o[3]) * inv, f16),
+                                      pack_h2(__uint_as_float(o[4]) * inv, __uint_as_float(o[5]) * inv, f16),
+                                      pack_h2(__uint_as_float(o[6]) * inv, __uint_as_float(o[7]) * inv, f16));
+                uint4 v1 = make_uint4(pack_h2(__uint_as_float(o[8]) * inv, __uint_as_float(o[9]) * inv, f16),
+                                      pack_h2(__uint_as_float(o[10]) * inv, __uint_as_float(o[11]) * inv, f16),
+                                      pack_h2(__uint_as_float(o[12]) * inv, __uint_as_float(o[13]) * inv, f16),
+                                      pack_h2(__uint_as_float(o[14]) * inv, __uint_as_float(o[15]) * inv, f16));
                 *reinterpret_cast<uint4*>(orow + c * 16) = v0;
                 *reinterpret_cast<uint4*>(orow + c * 16 + 8) = v1;
             }
@@ -260,6 +263,7 @@ extern "C" int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_str
     B200SD_CHECK_ARG(p && p->q && p->k && p->v && p->out, "attention: null pointer");
     if (p->head_dim != 64) return set_error(B200SD_ERR_UNSUPPORTED, "attention: head_dim %d (only 64)", p->head_dim);
     B200SD_CHECK_ARG(p->batch > 0 && p->heads > 0 && p->sq > 0 && p->skv > 0, "attention: bad shape");
+    B200SD_CHECK_ARG(p->dtype == B200SD_BF16 || p->dtype == B200SD_F16, "attention: dtype must be bf16 or fp16");
     B200SD_CHECK_ARG(p->ld_q % 8 == 0 && p->ld_k % 8 == 0 && p->ld_v % 8 == 0 && p->ld_out % 8 == 0,
                      "attention: leading dimensions must be multiples of 8");
     B200SD_CHECK_ARG(((reinterpret_cast<uintptr_t>(p->q) | reinterpret_cast<uintptr_t>(p->k) |
@@ -296,8 +300,9 @@ extern "C" int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_str
     kp.sq = p->sq, kp.skv = p->skv;
     kp.n_kv_tiles = (p->skv + ATT_BN - 1) / ATT_BN;
     kp.scale_log2 = p->scale * 1.4426950408889634f;
-    kp.out = static_cast<__nv_bfloat16*>(p->out);
+    kp.out = static_cast<uint16_t*>(p->out);
     kp.ld_out = p->ld_out;
+    kp.is_f16 = p->dtype == B200SD_F16;
     dim3 grid((p->sq + ATT_BM - 1) / ATT_BM, p->heads, p->batch);
     attention_kernel<<<grid, ATT_THREADS, ATT_SMEM, as_stream(stream)>>>(tmQ, tmK, tmV, kp);
     count_launch();

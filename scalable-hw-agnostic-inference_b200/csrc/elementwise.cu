@@ -2,6 +2,7 @@
 // cannot tile, nearest 2x upsample, CFG + scheduler step (K4), the timestep-embedding small-M linears (K5),
 // row softmax for the VAE's single-head attention, uint8 post-process (K7), casts.
 // All are coalesced, 8/16-byte vectorised, grid sized in multiples of the SM count where the shape allows.
+// Element types are selected at run time by a dtype code (warp-uniform branch; these kernels are bandwidth-bound).
 // Algorithmic bytes per element are listed per kernel in DESIGN.md section 4.
 #include "common.h"
 #include "ptx.cuh"
@@ -11,34 +12,39 @@ using namespace ptx;
 
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)); }
 
-// ---- 4-wide loads/stores over fp32 or bf16 ---------------------------------------------------------------
-template <typename T>
-__device__ __forceinline__ float4 load4(const T* p);
-template <>
-__device__ __forceinline__ float4 load4<float>(const float* p) {
-    return *reinterpret_cast<const float4*>(p);
+// ---- 4-wide loads/stores; idx counts elements ---------------------------------------------------------------
+__device__ __forceinline__ float4 load4(const void* base, size_t idx, int dt) {
+    if (dt == B200SD_F32) return *reinterpret_cast<const float4*>(static_cast<const float*>(base) + idx);
+    const uint2 v = *reinterpret_cast<const uint2*>(static_cast<const uint16_t*>(base) + idx);
+    const bool f16 = dt == B200SD_F16;
+    return make_float4(h_lo(v.x, f16), h_hi(v.x, f16), h_lo(v.y, f16), h_hi(v.y, f16));
 }
-template <>
-__device__ __forceinline__ float4 load4<__nv_bfloat16>(const __nv_bfloat16* p) {
-    uint2 v = *reinterpret_cast<const uint2*>(p);
-    return make_float4(bf16_lo(v.x), bf16_hi(v.x), bf16_lo(v.y), bf16_hi(v.y));
+__device__ __forceinline__ float load1(const void* base, size_t idx, int dt) {
+    if (dt == B200SD_F32) return static_cast<const float*>(base)[idx];
+    if (dt == B200SD_F16) return __half2float(static_cast<const __half*>(base)[idx]);
+    return __bfloat162float(static_cast<const __nv_bfloat16*>(base)[idx]);
 }
-__device__ __forceinline__ void store4_bf16(__nv_bfloat16* p, float4 v) {
-    *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+__device__ __forceinline__ void store4_h(void* base, size_t idx, float4 v, bool f16) {
+    *reinterpret_cast<uint2*>(static_cast<uint16_t*>(base) + idx) =
+        make_uint2(pack_h2(v.x, v.y, f16), pack_h2(v.z, v.w, f16));
+}
+__device__ __forceinline__ void store8_h(void* base, size_t idx, const float (&v)[8], bool f16) {
+    *reinterpret_cast<uint4*>(static_cast<uint16_t*>(base) + idx) =
+        make_uint4(pack_h2(v[0], v[1], f16), pack_h2(v[2], v[3], f16), pack_h2(v[4], v[5], f16),
+                   pack_h2(v[6], v[7], f16));
 }
 
 // =============================================================================================== GroupNorm
 // Pass 1: per (image, pixel-split) partial sums per group, written (not accumulated) to scratch so the result
 // is deterministic.  Pass 2 reduces the splits in a fixed order, then normalises.
 // Thread layout: blockDim = vpp * lanes, vpp = C/4 vectors per pixel; thread -> fixed 4 channels.
-template <typename T>
-__global__ void gn_stats_kernel(const T* __restrict__ x1, int c1, const T* __restrict__ x2, int c2, int hw,
-                                int groups, int splits, float* __restrict__ partial) {
+__global__ void gn_stats_kernel(const void* __restrict__ x1, int c1, const void* __restrict__ x2, int c2, int dt,
+                                int hw, int groups, int splits, float* __restrict__ partial) {
     extern __shared__ float sm[];  // [lanes][C] sums, then [lanes][C] sums of squares
     const int C = c1 + c2;
     const int vpp = C >> 2;
     const int lanes = blockDim.x / vpp;
-    const int pl = threadIdx.x / vpp;   // pixel lane
+    const int pl = threadIdx.x / vpp;  // pixel lane
     const int vec = threadIdx.x - pl * vpp;
     const int ch = vec << 2;
     const int n = blockIdx.y, split = blockIdx.x;
@@ -46,20 +52,19 @@ __global__ void gn_stats_kernel(const T* __restrict__ x1, int c1, const T* __res
     const int p0 = split * per;
     const int p1 = min(hw, p0 + per);
     const bool second = ch >= c1;
-    const T* base = second ? x2 + (size_t)n * hw * c2 + (ch - c1) : x1 + (size_t)n * hw * c1 + ch;
+    const void* src = second ? x2 : x1;
     const int cs = second ? c2 : c1;
+    const size_t off = (size_t)n * hw * cs + (second ? ch - c1 : ch);
     float s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
-    if (pl < lanes) {
-        for (int p = p0 + pl; p < p1; p += lanes) {
-            float4 v = load4<T>(base + (size_t)p * cs);
-            s[0] += v.x, s[1] += v.y, s[2] += v.z, s[3] += v.w;
-            q[0] += v.x * v.x, q[1] += v.y * v.y, q[2] += v.z * v.z, q[3] += v.w * v.w;
-        }
-        float* ss = sm + pl * C + ch;
-        float* qq = sm + lanes * C + pl * C + ch;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) ss[j] = s[j], qq[j] = q[j];
+    for (int p = p0 + pl; p < p1; p += lanes) {
+        const float4 v = load4(src, off + (size_t)p * cs, dt);
+        s[0] += v.x, s[1] += v.y, s[2] += v.z, s[3] += v.w;
+        q[0] += v.x * v.x, q[1] += v.y * v.y, q[2] += v.z * v.z, q[3] += v.w * v.w;
     }
+    float* ss = sm + pl * C + ch;
+    float* qq = sm + lanes * C + pl * C + ch;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) ss[j] = s[j], qq[j] = q[j];
     __syncthreads();
     const int cpg = C / groups;
     for (int g = threadIdx.x; g < groups; g += blockDim.x) {
@@ -71,11 +76,10 @@ __global__ void gn_stats_kernel(const T* __restrict__ x1, int c1, const T* __res
     }
 }
 
-template <typename T>
-__global__ void gn_apply_kernel(const T* __restrict__ x1, int c1, const T* __restrict__ x2, int c2, int hw,
-                                int groups, int splits, const float* __restrict__ partial, float eps,
+__global__ void gn_apply_kernel(const void* __restrict__ x1, int c1, const void* __restrict__ x2, int c2, int dt,
+                                int hw, int groups, int splits, const float* __restrict__ partial, float eps,
                                 const float* __restrict__ gamma, const float* __restrict__ beta, int silu,
-                                __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ raw, int chunks) {
+                                void* __restrict__ y, void* __restrict__ raw, int out_f16, int chunks) {
     __shared__ float s_mean[64], s_rstd[64];
     const int C = c1 + c2;
     const int vpp = C >> 2;
@@ -97,7 +101,6 @@ __global__ void gn_apply_kernel(const T* __restrict__ x1, int c1, const T* __res
         s_mean[g] = mean, s_rstd[g] = rsqrtf(var + eps);
     }
     __syncthreads();
-    if (pl >= lanes) return;
     float sc[4], sh[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -106,18 +109,20 @@ __global__ void gn_apply_kernel(const T* __restrict__ x1, int c1, const T* __res
         sc[j] = w, sh[j] = beta[ch + j] - s_mean[g] * w;
     }
     const bool second = ch >= c1;
-    const T* base = second ? x2 + (size_t)n * hw * c2 + (ch - c1) : x1 + (size_t)n * hw * c1 + ch;
+    const void* src = second ? x2 : x1;
     const int cs = second ? c2 : c1;
+    const size_t off = (size_t)n * hw * cs + (second ? ch - c1 : ch);
     const int per = (hw + chunks - 1) / chunks;
     const int p0 = blockIdx.x * per;
     const int p1 = min(hw, p0 + per);
+    const bool f16 = out_f16 != 0;
     for (int p = p0 + pl; p < p1; p += lanes) {
-        float4 v = load4<T>(base + (size_t)p * cs);
+        const float4 v = load4(src, off + (size_t)p * cs, dt);
         const size_t o = ((size_t)n * hw + p) * C + ch;
-        if (raw) store4_bf16(raw + o, v);
+        if (raw) store4_h(raw, o, v, f16);
         float4 r = make_float4(v.x * sc[0] + sh[0], v.y * sc[1] + sh[1], v.z * sc[2] + sh[2], v.w * sc[3] + sh[3]);
         if (silu) r = make_float4(silu_f(r.x), silu_f(r.y), silu_f(r.z), silu_f(r.w));
-        store4_bf16(y + o, r);
+        store4_h(y, o, r, f16);
     }
 }
 
@@ -132,23 +137,22 @@ static int gn_splits(int n_img, int hw) {
 
 // =============================================================================================== LayerNorm
 // one warp per row, whole row held in registers (cols <= 1536): exact two-pass mean / variance.
-template <typename T>
-__global__ void layernorm_kernel(const T* __restrict__ x, long long rows, int cols, float eps,
+__global__ void layernorm_kernel(const void* __restrict__ x, int dt, long long rows, int cols, float eps,
                                  const float* __restrict__ gamma, const float* __restrict__ beta,
-                                 __nv_bfloat16* __restrict__ y) {
+                                 void* __restrict__ y, int out_f16) {
     constexpr int MAXV = 12;
     const int lane = threadIdx.x & 31;
     const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= rows) return;
     const int nvec = cols >> 2;
-    const T* xr = x + row * cols;
+    const size_t base = (size_t)row * cols;
     float4 v[MAXV];
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
         const int idx = lane + i * 32;
         if (idx < nvec) {
-            v[i] = load4<T>(xr + idx * 4);
+            v[i] = load4(x, base + idx * 4, dt);
             s += v[i].x + v[i].y + v[i].z + v[i].w;
         }
     }
@@ -167,7 +171,6 @@ __global__ void layernorm_kernel(const T* __restrict__ x, long long rows, int co
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
     const float rstd = rsqrtf(q / (float)cols + eps);
-    __nv_bfloat16* yr = y + row * cols;
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
         const int idx = lane + i * 32;
@@ -176,16 +179,16 @@ __global__ void layernorm_kernel(const T* __restrict__ x, long long rows, int co
             float4 b = *reinterpret_cast<const float4*>(beta + idx * 4);
             float4 r = make_float4((v[i].x - mean) * rstd * g.x + b.x, (v[i].y - mean) * rstd * g.y + b.y,
                                    (v[i].z - mean) * rstd * g.z + b.z, (v[i].w - mean) * rstd * g.w + b.w);
-            store4_bf16(yr + idx * 4, r);
+            store4_h(y, base + idx * 4, r, out_f16 != 0);
         }
     }
 }
 
 // =============================================================================================== im2col 3x3
 // one thread per 8 consecutive k of one output pixel
-template <typename T>
-__global__ void im2col3x3_kernel(const T* __restrict__ x, int n_img, int n_src, int in_h, int in_w, int cin,
-                                 int stride, int out_h, int out_w, int k_pad, __nv_bfloat16* __restrict__ out) {
+__global__ void im2col3x3_kernel(const void* __restrict__ x, int dt, int n_img, int n_src, int in_h, int in_w,
+                                 int cin, int stride, int out_h, int out_w, int k_pad, void* __restrict__ out,
+                                 int out_f16) {
     const int kchunks = k_pad >> 3;
     const long long total = (long long)n_img * out_h * out_w * kchunks;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -195,15 +198,15 @@ __global__ void im2col3x3_kernel(const T* __restrict__ x, int n_img, int n_src, 
         const int ox = (int)(m % out_w);
         const int oy = (int)((m / out_w) % out_h);
         const int n = (int)(m / ((long long)out_w * out_h));
-        const T* src = x + (size_t)(n % n_src) * in_h * in_w * cin;
+        const size_t src = (size_t)(n % n_src) * in_h * in_w * cin;
         float v[8];
         const int k0 = kc << 3;
         if ((cin & 7) == 0) {
             const int tap = k0 / cin, c = k0 - tap * cin;
             const int iy = oy * stride + tap / 3 - 1, ix = ox * stride + tap % 3 - 1;
             if (tap < 9 && iy >= 0 && iy < in_h && ix >= 0 && ix < in_w) {
-                const T* p = src + ((size_t)iy * in_w + ix) * cin + c;
-                float4 a = load4<T>(p), b = load4<T>(p + 4);
+                const size_t p = src + ((size_t)iy * in_w + ix) * cin + c;
+                const float4 a = load4(x, p, dt), b = load4(x, p + 4, dt);
                 v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w, v[4] = b.x, v[5] = b.y, v[6] = b.z, v[7] = b.w;
             } else {
 #pragma unroll
@@ -217,20 +220,17 @@ __global__ void im2col3x3_kernel(const T* __restrict__ x, int n_img, int n_src, 
                 const int iy = oy * stride + tap / 3 - 1, ix = ox * stride + tap % 3 - 1;
                 float t = 0.f;
                 if (tap < 9 && iy >= 0 && iy < in_h && ix >= 0 && ix < in_w)
-                    t = (float)src[((size_t)iy * in_w + ix) * cin + c];
+                    t = load1(x, src + ((size_t)iy * in_w + ix) * cin + c, dt);
                 v[j] = t;
             }
         }
-        *reinterpret_cast<uint4*>(out + m * k_pad + k0) =
-            make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
-                       pack_bf16x2(v[6], v[7]));
+        store8_h(out, (size_t)m * k_pad + k0, v, out_f16 != 0);
     }
 }
 
 // =============================================================================================== upsample 2x
-template <typename T>
-__global__ void upsample2x_kernel(const T* __restrict__ x, int n_img, int h, int w, int c,
-                                  __nv_bfloat16* __restrict__ out) {
+__global__ void upsample2x_kernel(const void* __restrict__ x, int dt, int n_img, int h, int w, int c,
+                                  void* __restrict__ out, int out_f16) {
     const int cv = c >> 3;
     const long long total = (long long)n_img * (2 * h) * (2 * w) * cv;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -240,32 +240,32 @@ __global__ void upsample2x_kernel(const T* __restrict__ x, int n_img, int h, int
         const int ox = (int)(pix % (2 * w));
         const int oy = (int)((pix / (2 * w)) % (2 * h));
         const int n = (int)(pix / ((long long)4 * w * h));
-        const T* p = x + (((size_t)n * h + (oy >> 1)) * w + (ox >> 1)) * c + v8 * 8;
-        float4 a = load4<T>(p), b = load4<T>(p + 4);
-        *reinterpret_cast<uint4*>(out + pix * c + v8 * 8) =
-            make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+        const size_t p = (((size_t)n * h + (oy >> 1)) * w + (ox >> 1)) * c + v8 * 8;
+        const float4 a = load4(x, p, dt), b = load4(x, p + 4, dt);
+        const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        store8_h(out, (size_t)pix * c + v8 * 8, v, out_f16 != 0);
     }
 }
 
 // =============================================================================================== K4
-template <typename T>
-__global__ void cfg_sched_kernel(const T* __restrict__ eps2, float* __restrict__ x, float* __restrict__ x0_prev,
-                                 const float* __restrict__ coef, const int* __restrict__ step_index, long long n) {
+__global__ void cfg_sched_kernel(const void* __restrict__ eps2, int dt, float* __restrict__ x,
+                                 float* __restrict__ x0_prev, const float* __restrict__ coef,
+                                 const int* __restrict__ step_index, long long n) {
     const int step = step_index ? *step_index : 0;
     const float g = coef[step * 6 + 0], cx = coef[step * 6 + 1], cm = coef[step * 6 + 2], cp = coef[step * 6 + 3],
                 ax = coef[step * 6 + 4], am = coef[step * 6 + 5];
     const long long nv = n >> 2;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
          i += (long long)gridDim.x * blockDim.x) {
-        float4 u = load4<T>(eps2 + i * 4);
-        float4 c = load4<T>(eps2 + n + i * 4);
-        float4 xv = *reinterpret_cast<const float4*>(x + i * 4);
-        float4 m = make_float4(u.x + g * (c.x - u.x), u.y + g * (c.y - u.y), u.z + g * (c.z - u.z),
-                               u.w + g * (c.w - u.w));
+        const float4 u = load4(eps2, (size_t)i * 4, dt);
+        const float4 c = load4(eps2, (size_t)(n + i * 4), dt);
+        const float4 xv = *reinterpret_cast<const float4*>(x + i * 4);
+        const float4 m = make_float4(u.x + g * (c.x - u.x), u.y + g * (c.y - u.y), u.z + g * (c.z - u.z),
+                                     u.w + g * (c.w - u.w));
         float4 o = make_float4(cx * xv.x + cm * m.x, cx * xv.y + cm * m.y, cx * xv.z + cm * m.z,
                                cx * xv.w + cm * m.w);
         if (x0_prev) {
-            float4 pv = *reinterpret_cast<const float4*>(x0_prev + i * 4);
+            const float4 pv = *reinterpret_cast<const float4*>(x0_prev + i * 4);
             o.x += cp * pv.x, o.y += cp * pv.y, o.z += cp * pv.z, o.w += cp * pv.w;
             *reinterpret_cast<float4*>(x0_prev + i * 4) =
                 make_float4(ax * xv.x + am * m.x, ax * xv.y + am * m.y, ax * xv.z + am * m.z, ax * xv.w + am * m.w);
@@ -277,11 +277,12 @@ __global__ void cfg_sched_kernel(const T* __restrict__ eps2, float* __restrict__
 // =============================================================================================== K5
 // one warp per output column, rows processed 8 at a time from shared memory
 __global__ void small_linear_kernel(const float* __restrict__ x, int rows, int k, int n, int sinusoid_dim,
-                                    int silu_in, int silu_out, const __nv_bfloat16* __restrict__ w,
+                                    int silu_in, int silu_out, const uint16_t* __restrict__ w, int w_f16,
                                     const float* __restrict__ b, float* __restrict__ y) {
     extern __shared__ float xs[];  // [8][k]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int col = blockIdx.x * (blockDim.x >> 5) + warp;
+    const bool f16 = w_f16 != 0;
     for (int r0 = 0; r0 < rows; r0 += 8) {
         const int nr = min(8, rows - r0);
         __syncthreads();
@@ -302,11 +303,11 @@ __global__ void small_linear_kernel(const float* __restrict__ x, int rows, int k
         __syncthreads();
         if (col < n) {
             float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-            const __nv_bfloat16* wr = w + (size_t)col * k;
+            const uint16_t* wr = w + (size_t)col * k;
             for (int kk = lane * 8; kk < k; kk += 256) {
-                uint4 wv = *reinterpret_cast<const uint4*>(wr + kk);
-                float wf[8] = {bf16_lo(wv.x), bf16_hi(wv.x), bf16_lo(wv.y), bf16_hi(wv.y),
-                               bf16_lo(wv.z), bf16_hi(wv.z), bf16_lo(wv.w), bf16_hi(wv.w)};
+                const uint4 wv = *reinterpret_cast<const uint4*>(wr + kk);
+                const float wf[8] = {h_lo(wv.x, f16), h_hi(wv.x, f16), h_lo(wv.y, f16), h_hi(wv.y, f16),
+                                     h_lo(wv.z, f16), h_hi(wv.z, f16), h_lo(wv.w, f16), h_hi(wv.w, f16)};
                 for (int r = 0; r < nr; ++r) {
                     const float* xr = xs + r * k + kk;
 #pragma unroll
@@ -327,17 +328,15 @@ __global__ void small_linear_kernel(const float* __restrict__ x, int rows, int k
 }
 
 // =============================================================================================== row softmax
-template <typename T>
-__global__ void softmax_rows_kernel(const T* __restrict__ x, long long ld_in, __nv_bfloat16* __restrict__ y,
-                                    long long ld_out, int cols, float scale) {
+__global__ void softmax_rows_kernel(const void* __restrict__ x, int dt, long long ld_in, void* __restrict__ y,
+                                    int out_f16, long long ld_out, int cols, float scale) {
     extern __shared__ float row[];
     __shared__ float red[32];
-    const T* p = x + (long long)blockIdx.x * ld_in;
-    __nv_bfloat16* q = y + (long long)blockIdx.x * ld_out;
+    const size_t in0 = (size_t)blockIdx.x * ld_in, out0 = (size_t)blockIdx.x * ld_out;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
     float mx = -INFINITY;
     for (int i = tid * 4; i < cols; i += blockDim.x * 4) {
-        float4 v = load4<T>(p + i);
+        float4 v = load4(x, in0 + i, dt);
         v.x *= scale, v.y *= scale, v.z *= scale, v.w *= scale;
         *reinterpret_cast<float4*>(row + i) = v;
         mx = fmaxf(fmaxf(mx, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
@@ -363,18 +362,17 @@ __global__ void softmax_rows_kernel(const T* __restrict__ x, long long ld_in, __
     for (int i = 0; i < nw; ++i) sum += red[i];
     const float inv = 1.0f / sum;
     for (int i = tid * 4; i < cols; i += blockDim.x * 4) {
-        float4 v = *reinterpret_cast<const float4*>(row + i);
-        store4_bf16(q + i, make_float4(v.x * inv, v.y * inv, v.z * inv, v.w * inv));
+        const float4 v = *reinterpret_cast<const float4*>(row + i);
+        store4_h(y, out0 + i, make_float4(v.x * inv, v.y * inv, v.z * inv, v.w * inv), out_f16 != 0);
     }
 }
 
 // =============================================================================================== K7 / cast
-template <typename T>
-__global__ void denorm_u8_kernel(const T* __restrict__ x, uint8_t* __restrict__ out, long long n) {
+__global__ void denorm_u8_kernel(const void* __restrict__ x, int dt, uint8_t* __restrict__ out, long long n) {
     const long long nv = n >> 2;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
          i += (long long)gridDim.x * blockDim.x) {
-        float4 v = load4<T>(x + i * 4);
+        const float4 v = load4(x, (size_t)i * 4, dt);
         uchar4 o;
         o.x = (unsigned char)rintf(fminf(fmaxf(v.x * 0.5f + 0.5f, 0.f), 1.f) * 255.f);
         o.y = (unsigned char)rintf(fminf(fmaxf(v.y * 0.5f + 0.5f, 0.f), 1.f) * 255.f);
@@ -384,16 +382,15 @@ __global__ void denorm_u8_kernel(const T* __restrict__ x, uint8_t* __restrict__ 
     }
 }
 
-template <typename TI, typename TO>
-__global__ void cast_kernel(const TI* __restrict__ x, TO* __restrict__ y, long long n) {
+__global__ void cast_kernel(const void* __restrict__ x, int dt_in, void* __restrict__ y, int dt_out, long long n) {
     const long long nv = n >> 2;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
          i += (long long)gridDim.x * blockDim.x) {
-        float4 v = load4<TI>(x + i * 4);
-        if constexpr (sizeof(TO) == 4)
-            *reinterpret_cast<float4*>(y + i * 4) = v;
+        const float4 v = load4(x, (size_t)i * 4, dt_in);
+        if (dt_out == B200SD_F32)
+            *reinterpret_cast<float4*>(static_cast<float*>(y) + i * 4) = v;
         else
-            store4_bf16(reinterpret_cast<__nv_bfloat16*>(y) + i * 4, v);
+            store4_h(y, (size_t)i * 4, v, dt_out == B200SD_F16);
     }
 }
 
@@ -410,6 +407,8 @@ static int ew_grid(long long work_items, int block) {
 using namespace b200sd;
 
 #define ALIGNED16(p) ((reinterpret_cast<uintptr_t>(p) & 15) == 0)
+#define ANY_DTYPE(d) ((d) == B200SD_BF16 || (d) == B200SD_F32 || (d) == B200SD_F16)
+#define H_DTYPE(d) ((d) == B200SD_BF16 || (d) == B200SD_F16)
 
 extern "C" int64_t b200sd_groupnorm_workspace_bytes(const b200sd_groupnorm_params* p) {
     if (!p || p->n_img <= 0 || p->hw <= 0 || p->groups <= 0) return 0;
@@ -418,13 +417,15 @@ extern "C" int64_t b200sd_groupnorm_workspace_bytes(const b200sd_groupnorm_param
 
 extern "C" int32_t b200sd_groupnorm(const b200sd_groupnorm_params* p, b200sd_stream_t stream) {
     B200SD_CHECK_ARG(p && p->x1 && p->y && p->gamma && p->beta && p->workspace, "groupnorm: null pointer");
-    const int C = p->c1 + (p->x2 ? p->c2 : 0);
     const int c2 = p->x2 ? p->c2 : 0;
+    const int C = p->c1 + c2;
     B200SD_CHECK_ARG(p->groups > 0 && p->groups <= 64 && C % p->groups == 0, "groupnorm: C=%d groups=%d", C,
                      p->groups);
-    B200SD_CHECK_ARG(p->c1 % 4 == 0 && c2 % 4 == 0 && C / 4 <= 1024, "groupnorm: channels must be multiples of 4, C<=4096");
-    B200SD_CHECK_ARG(p->in_dtype == B200SD_F32 || p->in_dtype == B200SD_BF16, "groupnorm: bad in_dtype");
-    B200SD_CHECK_ARG(ALIGNED16(p->x1) && (!p->x2 || ALIGNED16(p->x2)) && ALIGNED16(p->y) && (!p->raw || ALIGNED16(p->raw)),
+    B200SD_CHECK_ARG(p->c1 % 4 == 0 && c2 % 4 == 0 && C / 4 <= 1024,
+                     "groupnorm: channels must be multiples of 4, C<=4096");
+    B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype) && H_DTYPE(p->out_dtype), "groupnorm: bad in_dtype / out_dtype");
+    B200SD_CHECK_ARG(ALIGNED16(p->x1) && (!p->x2 || ALIGNED16(p->x2)) && ALIGNED16(p->y) &&
+                         (!p->raw || ALIGNED16(p->raw)),
                      "groupnorm: pointers must be 16-byte aligned");
     const int splits = gn_splits(p->n_img, p->hw);
     const int64_t need = (int64_t)p->n_img * splits * p->groups * 2 * sizeof(float);
@@ -437,22 +438,13 @@ extern "C" int32_t b200sd_groupnorm(const b200sd_groupnorm_params* p, b200sd_str
     const int threads = vpp * lanes;
     const size_t smem = (size_t)2 * lanes * C * sizeof(float);
     cudaStream_t s = as_stream(stream);
-    const int chunks = gn_splits(p->n_img, p->hw) * 2;
+    const int chunks = splits * 2;
     dim3 g1(splits, p->n_img), g2(chunks, p->n_img);
-    if (p->in_dtype == B200SD_F32) {
-        gn_stats_kernel<float><<<g1, threads, smem, s>>>((const float*)p->x1, p->c1, (const float*)p->x2, c2, p->hw,
-                                                         p->groups, splits, p->workspace);
-        gn_apply_kernel<float><<<g2, threads, 0, s>>>((const float*)p->x1, p->c1, (const float*)p->x2, c2, p->hw,
-                                                      p->groups, splits, p->workspace, p->eps, p->gamma, p->beta,
-                                                      p->silu, (__nv_bfloat16*)p->y, (__nv_bfloat16*)p->raw, chunks);
-    } else {
-        gn_stats_kernel<__nv_bfloat16><<<g1, threads, smem, s>>>((const __nv_bfloat16*)p->x1, p->c1,
-                                                                 (const __nv_bfloat16*)p->x2, c2, p->hw, p->groups,
-                                                                 splits, p->workspace);
-        gn_apply_kernel<__nv_bfloat16><<<g2, threads, 0, s>>>(
-            (const __nv_bfloat16*)p->x1, p->c1, (const __nv_bfloat16*)p->x2, c2, p->hw, p->groups, splits,
-            p->workspace, p->eps, p->gamma, p->beta, p->silu, (__nv_bfloat16*)p->y, (__nv_bfloat16*)p->raw, chunks);
-    }
+    gn_stats_kernel<<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits,
+                                              p->workspace);
+    gn_apply_kernel<<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits,
+                                           p->workspace, p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
+                                           p->out_dtype == B200SD_F16, chunks);
     count_launch(2);
     B200SD_CHECK_LAUNCH("groupnorm");
     return B200SD_OK;
@@ -462,20 +454,14 @@ extern "C" int32_t b200sd_layernorm(const b200sd_layernorm_params* p, b200sd_str
     B200SD_CHECK_ARG(p && p->x && p->y && p->gamma && p->beta, "layernorm: null pointer");
     B200SD_CHECK_ARG(p->cols % 4 == 0 && p->cols <= 1536 && p->cols > 0, "layernorm: cols=%d (need %%4==0, <=1536)",
                      p->cols);
+    B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype) && H_DTYPE(p->out_dtype), "layernorm: bad in_dtype / out_dtype");
     B200SD_CHECK_ARG(ALIGNED16(p->x) && ALIGNED16(p->y) && ALIGNED16(p->gamma) && ALIGNED16(p->beta),
                      "layernorm: pointers must be 16-byte aligned");
     if (p->rows <= 0) return B200SD_OK;
     const int wpb = 8;
     const unsigned grid = (unsigned)((p->rows + wpb - 1) / wpb);
-    cudaStream_t s = as_stream(stream);
-    if (p->in_dtype == B200SD_F32)
-        layernorm_kernel<float><<<grid, wpb * 32, 0, s>>>((const float*)p->x, p->rows, p->cols, p->eps, p->gamma,
-                                                          p->beta, (__nv_bfloat16*)p->y);
-    else if (p->in_dtype == B200SD_BF16)
-        layernorm_kernel<__nv_bfloat16><<<grid, wpb * 32, 0, s>>>((const __nv_bfloat16*)p->x, p->rows, p->cols,
-                                                                  p->eps, p->gamma, p->beta, (__nv_bfloat16*)p->y);
-    else
-        return set_error(B200SD_ERR_BAD_ARG, "layernorm: bad in_dtype");
+    layernorm_kernel<<<grid, wpb * 32, 0, as_stream(stream)>>>(p->x, p->in_dtype, p->rows, p->cols, p->eps, p->gamma,
+                                                              p->beta, p->y, p->out_dtype == B200SD_F16);
     count_launch();
     B200SD_CHECK_LAUNCH("layernorm");
     return B200SD_OK;
@@ -486,20 +472,13 @@ extern "C" int32_t b200sd_im2col3x3(const b200sd_im2col_params* p, b200sd_stream
     B200SD_CHECK_ARG(p->stride == 1 || p->stride == 2, "im2col: stride must be 1 or 2");
     B200SD_CHECK_ARG(p->k_pad % 8 == 0 && p->k_pad >= 9 * p->cin, "im2col: k_pad=%d cin=%d", p->k_pad, p->cin);
     B200SD_CHECK_ARG(p->n_src > 0 && p->n_img > 0, "im2col: bad batch");
+    B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype) && H_DTYPE(p->out_dtype), "im2col: bad in_dtype / out_dtype");
     B200SD_CHECK_ARG(ALIGNED16(p->x) && ALIGNED16(p->out), "im2col: pointers must be 16-byte aligned");
     const int out_h = (p->in_h + 2 - 3) / p->stride + 1, out_w = (p->in_w + 2 - 3) / p->stride + 1;
     const long long total = (long long)p->n_img * out_h * out_w * (p->k_pad / 8);
-    const int grid = ew_grid(total, 256);
-    cudaStream_t s = as_stream(stream);
-    if (p->in_dtype == B200SD_F32)
-        im2col3x3_kernel<float><<<grid, 256, 0, s>>>((const float*)p->x, p->n_img, p->n_src, p->in_h, p->in_w, p->cin,
-                                                     p->stride, out_h, out_w, p->k_pad, (__nv_bfloat16*)p->out);
-    else if (p->in_dtype == B200SD_BF16)
-        im2col3x3_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)p->x, p->n_img, p->n_src, p->in_h,
-                                                             p->in_w, p->cin, p->stride, out_h, out_w, p->k_pad,
-                                                             (__nv_bfloat16*)p->out);
-    else
-        return set_error(B200SD_ERR_BAD_ARG, "im2col: bad in_dtype");
+    im2col3x3_kernel<<<ew_grid(total, 256), 256, 0, as_stream(stream)>>>(
+        p->x, p->in_dtype, p->n_img, p->n_src, p->in_h, p->in_w, p->cin, p->stride, out_h, out_w, p->k_pad, p->out,
+        p->out_dtype == B200SD_F16);
     count_launch();
     B200SD_CHECK_LAUNCH("im2col3x3");
     return B200SD_OK;
@@ -508,18 +487,11 @@ extern "C" int32_t b200sd_im2col3x3(const b200sd_im2col_params* p, b200sd_stream
 extern "C" int32_t b200sd_upsample2x(const b200sd_upsample_params* p, b200sd_stream_t stream) {
     B200SD_CHECK_ARG(p && p->x && p->out, "upsample2x: null pointer");
     B200SD_CHECK_ARG(p->c % 8 == 0, "upsample2x: c must be a multiple of 8");
+    B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype) && H_DTYPE(p->out_dtype), "upsample2x: bad in_dtype / out_dtype");
     B200SD_CHECK_ARG(ALIGNED16(p->x) && ALIGNED16(p->out), "upsample2x: pointers must be 16-byte aligned");
     const long long total = (long long)p->n_img * 4 * p->h * p->w * (p->c / 8);
-    const int grid = ew_grid(total, 256);
-    cudaStream_t s = as_stream(stream);
-    if (p->in_dtype == B200SD_F32)
-        upsample2x_kernel<float><<<grid, 256, 0, s>>>((const float*)p->x, p->n_img, p->h, p->w, p->c,
-                                                      (__nv_bfloat16*)p->out);
-    else if (p->in_dtype == B200SD_BF16)
-        upsample2x_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)p->x, p->n_img, p->h, p->w, p->c,
-                                                              (__nv_bfloat16*)p->out);
-    else
-        return set_error(B200SD_ERR_BAD_ARG, "upsample2x: bad in_dtype");
+    upsample2x_kernel<<<ew_grid(total, 256), 256, 0, as_stream(stream)>>>(p->x, p->in_dtype, p->n_img, p->h, p->w,
+                                                                         p->c, p->out, p->out_dtype == B200SD_F16);
     count_launch();
     B200SD_CHECK_LAUNCH("upsample2x");
     return B200SD_OK;
@@ -528,19 +500,12 @@ extern "C" int32_t b200sd_upsample2x(const b200sd_upsample_params* p, b200sd_str
 extern "C" int32_t b200sd_cfg_sched_step(const b200sd_cfg_sched_params* p, b200sd_stream_t stream) {
     B200SD_CHECK_ARG(p && p->eps2 && p->x && p->coef, "cfg_sched_step: null pointer");
     B200SD_CHECK_ARG(p->n > 0 && p->n % 4 == 0, "cfg_sched_step: n must be a positive multiple of 4");
+    B200SD_CHECK_ARG(ANY_DTYPE(p->eps_dtype), "cfg_sched_step: bad eps_dtype");
     B200SD_CHECK_ARG(ALIGNED16(p->eps2) && ALIGNED16(p->x) && (!p->x0_prev || ALIGNED16(p->x0_prev)) &&
-                         (p->eps_dtype != B200SD_BF16 || (p->n % 8 == 0)),
-                     "cfg_sched_step: pointers must be 16-byte aligned (bf16: n %% 8 == 0)");
-    const int grid = ew_grid(p->n / 4, 256);
-    cudaStream_t s = as_stream(stream);
-    if (p->eps_dtype == B200SD_F32)
-        cfg_sched_kernel<float><<<grid, 256, 0, s>>>((const float*)p->eps2, p->x, p->x0_prev, p->coef, p->step_index,
-                                                     p->n);
-    else if (p->eps_dtype == B200SD_BF16)
-        cfg_sched_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)p->eps2, p->x, p->x0_prev, p->coef,
-                                                             p->step_index, p->n);
-    else
-        return set_error(B200SD_ERR_BAD_ARG, "cfg_sched_step: bad eps_dtype");
+                         (p->eps_dtype == B200SD_F32 || (p->n % 8 == 0)),
+                     "cfg_sched_step: pointers must be 16-byte aligned (16-bit eps: n %% 8 == 0)");
+    cfg_sched_kernel<<<ew_grid(p->n / 4, 256), 256, 0, as_stream(stream)>>>(p->eps2, p->eps_dtype, p->x, p->x0_prev,
+                                                                           p->coef, p->step_index, p->n);
     count_launch();
     B200SD_CHECK_LAUNCH("cfg_sched_step");
     return B200SD_OK;
@@ -551,7 +516,7 @@ extern "C" int32_t b200sd_small_linear(const b200sd_small_linear_params* p, b200
     B200SD_CHECK_ARG(p->rows > 0 && p->rows <= 64 && p->k % 8 == 0 && p->k > 0 && p->k <= 4096 && p->n > 0,
                      "small_linear: rows=%d k=%d n=%d", p->rows, p->k, p->n);
     B200SD_CHECK_ARG(p->sinusoid_dim == 0 || p->sinusoid_dim == p->k, "small_linear: sinusoid_dim must be 0 or k");
-    B200SD_CHECK_ARG(ALIGNED16(p->w), "small_linear: w must be 16-byte aligned");
+    B200SD_CHECK_ARG(H_DTYPE(p->w_dtype) && ALIGNED16(p->w), "small_linear: w must be bf16/fp16, 16-byte aligned");
     const int wpb = 8;
     const int grid = (p->n + wpb - 1) / wpb;
     const size_t smem = (size_t)8 * p->k * sizeof(float);
@@ -560,9 +525,9 @@ extern "C" int32_t b200sd_small_linear(const b200sd_small_linear_params* p, b200
         cudaFuncSetAttribute(small_linear_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4096 * 4);
         attr_set = true;
     }
-    small_linear_kernel<<<grid, wpb * 32, smem, as_stream(stream)>>>(p->x, p->rows, p->k, p->n, p->sinusoid_dim,
-                                                                    p->silu_in, p->silu_out,
-                                                                    (const __nv_bfloat16*)p->w, p->b, p->y);
+    small_linear_kernel<<<grid, wpb * 32, smem, as_stream(stream)>>>(
+        p->x, p->rows, p->k, p->n, p->sinusoid_dim, p->silu_in, p->silu_out, (const uint16_t*)p->w,
+        p->w_dtype == B200SD_F16, p->b, p->y);
     count_launch();
     B200SD_CHECK_LAUNCH("small_linear");
     return B200SD_OK;
@@ -570,6 +535,7 @@ extern "C" int32_t b200sd_small_linear(const b200sd_small_linear_params* p, b200
 
 extern "C" int32_t b200sd_softmax_rows(const b200sd_softmax_params* p, b200sd_stream_t stream) {
     B200SD_CHECK_ARG(p && p->x && p->y, "softmax_rows: null pointer");
+    B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype) && H_DTYPE(p->out_dtype), "softmax_rows: bad in_dtype / out_dtype");
     B200SD_CHECK_ARG(p->cols > 0 && p->cols % 4 == 0 && p->ld_in % 4 == 0 && p->ld_out % 4 == 0 && p->cols <= 49152 &&
                          ALIGNED16(p->x) && (reinterpret_cast<uintptr_t>(p->y) & 7) == 0,
                      "softmax_rows: cols=%d ld_in=%lld ld_out=%lld (need %%4==0, cols<=49152, aligned)", p->cols,
@@ -578,21 +544,11 @@ extern "C" int32_t b200sd_softmax_rows(const b200sd_softmax_params* p, b200sd_st
     const size_t smem = (size_t)p->cols * sizeof(float);
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(softmax_rows_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 49152 * 4);
-        cudaFuncSetAttribute(softmax_rows_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             49152 * 4);
+        cudaFuncSetAttribute(softmax_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 49152 * 4);
         attr_set = true;
     }
-    cudaStream_t s = as_stream(stream);
-    if (p->in_dtype == B200SD_F32)
-        softmax_rows_kernel<float><<<(unsigned)p->rows, 256, smem, s>>>((const float*)p->x, p->ld_in,
-                                                                        (__nv_bfloat16*)p->y, p->ld_out, p->cols,
-                                                                        p->scale);
-    else if (p->in_dtype == B200SD_BF16)
-        softmax_rows_kernel<__nv_bfloat16><<<(unsigned)p->rows, 256, smem, s>>>(
-            (const __nv_bfloat16*)p->x, p->ld_in, (__nv_bfloat16*)p->y, p->ld_out, p->cols, p->scale);
-    else
-        return set_error(B200SD_ERR_BAD_ARG, "softmax_rows: bad in_dtype");
+    softmax_rows_kernel<<<(unsigned)p->rows, 256, smem, as_stream(stream)>>>(
+        p->x, p->in_dtype, p->ld_in, p->y, p->out_dtype == B200SD_F16, p->ld_out, p->cols, p->scale);
     count_launch();
     B200SD_CHECK_LAUNCH("softmax_rows");
     return B200SD_OK;
@@ -600,15 +556,10 @@ extern "C" int32_t b200sd_softmax_rows(const b200sd_softmax_params* p, b200sd_st
 
 extern "C" int32_t b200sd_denorm_u8(const b200sd_denorm_u8_params* p, b200sd_stream_t stream) {
     B200SD_CHECK_ARG(p && p->x && p->out, "denorm_u8: null pointer");
+    B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype), "denorm_u8: bad in_dtype");
     B200SD_CHECK_ARG(p->n > 0 && p->n % 4 == 0 && ALIGNED16(p->x) && (reinterpret_cast<uintptr_t>(p->out) & 3) == 0,
                      "denorm_u8: n %% 4 == 0 and aligned pointers required");
-    const int grid = ew_grid(p->n / 4, 256);
-    if (p->in_dtype == B200SD_F32)
-        denorm_u8_kernel<float><<<grid, 256, 0, as_stream(stream)>>>((const float*)p->x, p->out, p->n);
-    else if (p->in_dtype == B200SD_BF16)
-        denorm_u8_kernel<__nv_bfloat16><<<grid, 256, 0, as_stream(stream)>>>((const __nv_bfloat16*)p->x, p->out, p->n);
-    else
-        return set_error(B200SD_ERR_BAD_ARG, "denorm_u8: bad in_dtype");
+    denorm_u8_kernel<<<ew_grid(p->n / 4, 256), 256, 0, as_stream(stream)>>>(p->x, p->in_dtype, p->out, p->n);
     count_launch();
     B200SD_CHECK_LAUNCH("denorm_u8");
     return B200SD_OK;
@@ -616,15 +567,9 @@ extern "C" int32_t b200sd_denorm_u8(const b200sd_denorm_u8_params* p, b200sd_str
 
 extern "C" int32_t b200sd_cast(const b200sd_cast_params* p, b200sd_stream_t stream) {
     B200SD_CHECK_ARG(p && p->x && p->y, "cast: null pointer");
+    B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype) && ANY_DTYPE(p->out_dtype), "cast: bad dtype");
     B200SD_CHECK_ARG(p->n > 0 && p->n % 4 == 0 && ALIGNED16(p->x) && ALIGNED16(p->y), "cast: n %% 4 == 0, aligned");
-    const int grid = ew_grid(p->n / 4, 256);
-    cudaStream_t s = as_stream(stream);
-    if (p->in_dtype == B200SD_F32 && p->out_dtype == B200SD_BF16)
-        cast_kernel<float, __nv_bfloat16><<<grid, 256, 0, s>>>((const float*)p->x, (__nv_bfloat16*)p->y, p->n);
-    else if (p->in_dtype == B200SD_BF16 && p->out_dtype == B200SD_F32)
-        cast_kernel<__nv_bfloat16, float><<<grid, 256, 0, s>>>((const __nv_bfloat16*)p->x, (float*)p->y, p->n);
-    else
-        return set_error(B200SD_ERR_BAD_ARG, "cast: only f32<->bf16");
+    cast_kernel<<<ew_grid(p->n / 4, 256), 256, 0, as_stream(stream)>>>(p->x, p->in_dtype, p->y, p->out_dtype, p->n);
     count_launch();
     B200SD_CHECK_LAUNCH("cast");
     return B200SD_OK;

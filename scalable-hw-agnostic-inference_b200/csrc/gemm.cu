@@ -22,6 +22,7 @@ constexpr int GEMM_THREADS = 192;
 
 struct GemmKernelParams {
     int n_img, img_h, img_w, cin, taps;
+    int a_bf16, b_bf16;  // operand formats for the instruction descriptor (0 = fp16, 1 = bf16)
     int bw, bh, bn;
     int tiles_x, tiles_y, m_tiles, n_tiles, kb_per_tap;
     int n_out, n_cols;  // n_cols = columns actually written (n_out, or n_out/2 for GEGLU)
@@ -64,15 +65,16 @@ __device__ __forceinline__ void epilogue_store32(const GemmKernelParams& p, floa
                     v[4 * j + 0] += t.x, v[4 * j + 1] += t.y, v[4 * j + 2] += t.z, v[4 * j + 3] += t.w;
                 }
             } else {
-                const uint4* r = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) +
+                const bool f16 = p.res_dtype == B200SD_F16;
+                const uint4* r = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.residual) +
                                                                 m * p.ld_res + col0);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     uint4 t = r[j];
-                    v[8 * j + 0] += bf16_lo(t.x), v[8 * j + 1] += bf16_hi(t.x);
-                    v[8 * j + 2] += bf16_lo(t.y), v[8 * j + 3] += bf16_hi(t.y);
-                    v[8 * j + 4] += bf16_lo(t.z), v[8 * j + 5] += bf16_hi(t.z);
-                    v[8 * j + 6] += bf16_lo(t.w), v[8 * j + 7] += bf16_hi(t.w);
+                    v[8 * j + 0] += h_lo(t.x, f16), v[8 * j + 1] += h_hi(t.x, f16);
+                    v[8 * j + 2] += h_lo(t.y, f16), v[8 * j + 3] += h_hi(t.y, f16);
+                    v[8 * j + 4] += h_lo(t.z, f16), v[8 * j + 5] += h_hi(t.z, f16);
+                    v[8 * j + 6] += h_lo(t.w, f16), v[8 * j + 7] += h_hi(t.w, f16);
                 }
             }
         }
@@ -81,11 +83,12 @@ __device__ __forceinline__ void epilogue_store32(const GemmKernelParams& p, floa
 #pragma unroll
             for (int j = 0; j < 8; ++j) o[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
         } else {
-            uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + m * p.ld_out + col0);
+            const bool f16 = p.out_dtype == B200SD_F16;
+            uint4* o = reinterpret_cast<uint4*>(static_cast<uint16_t*>(p.out) + m * p.ld_out + col0);
 #pragma unroll
             for (int j = 0; j < 4; ++j)
-                o[j] = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
-                                  pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+                o[j] = make_uint4(pack_h2(v[8 * j], v[8 * j + 1], f16), pack_h2(v[8 * j + 2], v[8 * j + 3], f16),
+                                  pack_h2(v[8 * j + 4], v[8 * j + 5], f16), pack_h2(v[8 * j + 6], v[8 * j + 7], f16));
         }
     } else {
         for (int j = 0; j < 32; ++j) {
@@ -95,11 +98,15 @@ __device__ __forceinline__ void epilogue_store32(const GemmKernelParams& p, floa
             if (p.residual) {
                 if (p.res_dtype == B200SD_F32)
                     x += static_cast<const float*>(p.residual)[m * p.ld_res + col];
+                else if (p.res_dtype == B200SD_F16)
+                    x += __half2float(static_cast<const __half*>(p.residual)[m * p.ld_res + col]);
                 else
                     x += __bfloat162float(static_cast<const __nv_bfloat16*>(p.residual)[m * p.ld_res + col]);
             }
             if (p.out_dtype == B200SD_F32)
                 static_cast<float*>(p.out)[m * p.ld_out + col] = x;
+            else if (p.out_dtype == B200SD_F16)
+                static_cast<__half*>(p.out)[m * p.ld_out + col] = __float2half_rn(x);
             else
                 static_cast<__nv_bfloat16*>(p.out)[m * p.ld_out + col] = __float2bfloat16(x);
         }
@@ -220,7 +227,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     } else if (warp == 1) {
         // ------------------------------------------------------------------ UMMA issuer
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BLOCK_N);
+            const uint32_t idesc = umma_idesc(BLOCK_M, BLOCK_N, (uint32_t)p.a_bf16, (uint32_t)p.b_bf16);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
@@ -412,9 +419,16 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
     B200SD_CHECK_ARG(p->cin % 8 == 0, "gemm: cin (%d) must be a multiple of 8", p->cin);
     B200SD_CHECK_ARG((reinterpret_cast<uintptr_t>(p->a) & 15) == 0 && (reinterpret_cast<uintptr_t>(p->w) & 15) == 0,
                      "gemm: a / w must be 16-byte aligned");
-    B200SD_CHECK_ARG(p->out_dtype == B200SD_BF16 || p->out_dtype == B200SD_F32, "gemm: bad out_dtype");
-    B200SD_CHECK_ARG(!p->residual || p->residual_dtype == B200SD_BF16 || p->residual_dtype == B200SD_F32,
+    B200SD_CHECK_ARG(p->out_dtype >= B200SD_BF16 && p->out_dtype <= B200SD_F16, "gemm: bad out_dtype");
+    B200SD_CHECK_ARG(!p->residual || (p->residual_dtype >= B200SD_BF16 && p->residual_dtype <= B200SD_F16),
                      "gemm: bad residual_dtype");
+    B200SD_CHECK_ARG((p->a_dtype == B200SD_BF16 || p->a_dtype == B200SD_F16) &&
+                         (p->w_dtype == B200SD_BF16 || p->w_dtype == B200SD_F16),
+                     "gemm: a_dtype / w_dtype must be bf16 or fp16");
+    // measured on B200: tcgen05.mma kind::f16 with A and B in different 16-bit formats traps (illegal instruction)
+    if (p->a_dtype != p->w_dtype)
+        return set_error(B200SD_ERR_UNSUPPORTED, "gemm: a_dtype (%d) and w_dtype (%d) must be equal", p->a_dtype,
+                         p->w_dtype);
     const int n_cols = p->geglu ? p->n_out / 2 : p->n_out;
     if (n_cols >= 32) {
         // vector path requirements
@@ -435,6 +449,7 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
 
     GemmKernelParams kp{};
     kp.n_img = p->n_img, kp.img_h = p->img_h, kp.img_w = p->img_w, kp.cin = p->cin, kp.taps = p->taps;
+    kp.a_bf16 = p->a_dtype == B200SD_BF16, kp.b_bf16 = p->w_dtype == B200SD_BF16;
     choose_box(p->n_img, p->img_h, p->img_w, &kp.bw, &kp.bh, &kp.bn);
     kp.tiles_x = (p->img_w + kp.bw - 1) / kp.bw;
     kp.tiles_y = (p->img_h + kp.bh - 1) / kp.bh;
@@ -491,8 +506,8 @@ namespace b200sd {
 // Single CTA, 128 threads.  Operands are written to shared memory by ordinary stores in the SWIZZLE_128B
 // pattern (16-byte chunk c of 128-byte row r lives at chunk c ^ (r & 7)), then consumed by tcgen05.mma.
 __global__ void __launch_bounds__(128, 1)
-    umma_selftest_kernel(const __nv_bfloat16* __restrict__ A, const __nv_bfloat16* __restrict__ B,
-                         float* __restrict__ D, int n, int k, int b_mn_major) {
+    umma_selftest_kernel(const uint16_t* __restrict__ A, const uint16_t* __restrict__ B, float* __restrict__ D,
+                         int n, int k, int b_mn_major, int a_bf16, int b_bf16) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -537,7 +552,7 @@ __global__ void __launch_bounds__(128, 1)
     const uint32_t tmem_base = tmem_slot;
 
     if (tid == 0) {
-        const uint32_t idesc = umma_idesc_bf16(128, (uint32_t)n, 0, b_mn_major ? 1u : 0u);
+        const uint32_t idesc = umma_idesc(128, (uint32_t)n, (uint32_t)a_bf16, (uint32_t)b_bf16, 0, b_mn_major ? 1u : 0u);
         for (int kk = 0; kk < k / 16; ++kk) {
             const uint32_t a_addr = smem_u32(sA) + (kk / 4) * 16384 + (kk % 4) * 32;
             uint64_t adesc = umma_desc_sw128(a_addr);
@@ -566,9 +581,13 @@ __global__ void __launch_bounds__(128, 1)
 
 }  // namespace b200sd
 
-extern "C" int32_t b200sd_umma_selftest(const void* a, const void* b, float* d, int32_t n, int32_t k,
-                                        int32_t b_mn_major, b200sd_stream_t stream) {
+extern "C" int32_t b200sd_umma_selftest(const void* a, int32_t a_dtype, const void* b, int32_t b_dtype, float* d,
+                                        int32_t n, int32_t k, int32_t b_mn_major, b200sd_stream_t stream) {
     B200SD_CHECK_ARG(a && b && d, "umma_selftest: null pointer");
+    B200SD_CHECK_ARG((a_dtype == B200SD_BF16 || a_dtype == B200SD_F16) && (b_dtype == B200SD_BF16 || b_dtype == B200SD_F16),
+                     "umma_selftest: operands must be bf16 or fp16");
+    if (a_dtype != b_dtype)
+        return set_error(B200SD_ERR_UNSUPPORTED, "umma_selftest: mixed bf16 x fp16 operands trap on sm_100a");
     B200SD_CHECK_ARG(n >= 16 && n <= 256 && n % 16 == 0 && k >= 64 && k <= 256 && k % 64 == 0,
                      "umma_selftest: need 16<=n<=256 (n%%16==0), 64<=k<=256 (k%%64==0)");
     B200SD_CHECK_ARG(!b_mn_major || n % 64 == 0, "umma_selftest: MN-major B needs n %% 64 == 0");
@@ -576,9 +595,9 @@ extern "C" int32_t b200sd_umma_selftest(const void* a, const void* b, float* d, 
     cudaError_t e =
         cudaFuncSetAttribute(umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "umma_selftest attr: %s", cudaGetErrorString(e));
-    umma_selftest_kernel<<<1, 128, smem, as_stream(stream)>>>(static_cast<const __nv_bfloat16*>(a),
-                                                              static_cast<const __nv_bfloat16*>(b), d, n, k,
-                                                              b_mn_major);
+    umma_selftest_kernel<<<1, 128, smem, as_stream(stream)>>>(static_cast<const uint16_t*>(a),
+                                                              static_cast<const uint16_t*>(b), d, n, k, b_mn_major,
+                                                              a_dtype == B200SD_BF16, b_dtype == B200SD_BF16);
     count_launch();
     B200SD_CHECK_LAUNCH("umma_selftest_kernel");
     return B200SD_OK;

@@ -4,6 +4,7 @@
 #include <cstdint>
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 namespace b200sd {
 namespace ptx {
@@ -118,13 +119,13 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr, uint32_t
     d |= static_cast<uint64_t>(2) << 61;
     return d;
 }
-// Instruction descriptor, kind::f16, bf16 x bf16 -> fp32, M=128.
-//   [4,6) D fmt (1=f32)  [7,10) A fmt (1=bf16)  [10,13) B fmt (1=bf16)  [15] A major  [16] B major (1 = MN-major)
+// Instruction descriptor, kind::f16, {bf16|fp16} x {bf16|fp16} -> fp32.
+//   [4,6) D fmt (1=f32)  [7,10) A fmt (0=f16, 1=bf16)  [10,13) B fmt  [15] A major  [16] B major (1 = MN-major)
 //   [17,23) N>>3  [24,29) M>>4
-__host__ __device__ constexpr uint32_t umma_idesc_bf16(uint32_t M, uint32_t N, uint32_t a_mn_major = 0,
-                                                       uint32_t b_mn_major = 0) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | (a_mn_major << 15) | (b_mn_major << 16) | ((N >> 3) << 17) |
-           ((M >> 4) << 24);
+__host__ __device__ constexpr uint32_t umma_idesc(uint32_t M, uint32_t N, uint32_t a_is_bf16, uint32_t b_is_bf16,
+                                                  uint32_t a_mn_major = 0, uint32_t b_mn_major = 0) {
+    return (1u << 4) | (a_is_bf16 << 7) | (b_is_bf16 << 10) | (a_mn_major << 15) | (b_mn_major << 16) |
+           ((N >> 3) << 17) | ((M >> 4) << 24);
 }
 // D[tmem] (+)= A[smem] * B[smem]; one thread issues for the whole CTA.
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
@@ -185,6 +186,24 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 }
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xFFFF0000u); }
+// fp16 pair with saturation to +-65504 instead of inf
+__device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+__device__ __forceinline__ float f16_lo(uint32_t v) {
+    return __half2float(__ushort_as_half(static_cast<unsigned short>(v & 0xFFFFu)));
+}
+__device__ __forceinline__ float f16_hi(uint32_t v) {
+    return __half2float(__ushort_as_half(static_cast<unsigned short>(v >> 16)));
+}
+// 16-bit pair in the format selected at run time (is_f16 is warp-uniform everywhere it is used)
+__device__ __forceinline__ uint32_t pack_h2(float lo, float hi, bool is_f16) {
+    return is_f16 ? pack_f16x2(lo, hi) : pack_bf16x2(lo, hi);
+}
+__device__ __forceinline__ float h_lo(uint32_t v, bool is_f16) { return is_f16 ? f16_lo(v) : bf16_lo(v); }
+__device__ __forceinline__ float h_hi(uint32_t v, bool is_f16) { return is_f16 ? f16_hi(v) : bf16_hi(v); }
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }

@@ -53,6 +53,25 @@ def test_tiny_unet_per_sample_timesteps_and_bf16_trunk(tiny, cuda):
     assert err <= 3e-2  # the bf16 residual trunk is an optional mode; the fp32 trunk is the parity path
 
 
+def test_tiny_unet_bf16_operands_floor(tiny, cuda):
+    """bf16 tensor-core operands (the reference's storage dtype) are a supported mode.  Their error floor against the
+    fp32 oracle is set by bf16's 8-bit significand, not by the kernels: emulating bf16 rounding of weights and
+    activations in the fp32 oracle itself gives 1.08e-2 on the real SD2.1 widths (tools/precision_probe.py), which is
+    why fp16 operands (same tensor throughput, 11-bit significand) are the default parity path."""
+    import b200sd
+    ou, _, _, _ = tiny
+    lat, ctx = O.seeded_inputs(2, 16, 128)
+    x2 = torch.cat([lat, lat])
+    with torch.no_grad():
+        ref = ou(x2, 961.0, ctx)
+    gb = b200sd.B200UNet(ou.state_dict(), ou.cfg, cuda, op_dtype=torch.bfloat16)
+    with torch.no_grad():
+        out = gb(x2.to(cuda), 961.0, ctx.to(cuda)).sample
+    err = O.rel_l2(out.float().cpu(), ref)
+    print(f"bf16-operand rel L2 {err:.3e}")
+    assert err <= 2e-2
+
+
 def test_tiny_vae_decode(tiny, cuda):
     _, ov, _, gv = tiny
     lat, _ = O.seeded_inputs(2, 16, 128)

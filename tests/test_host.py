@@ -1,0 +1,186 @@
+"""CPU: the C ABI loads and exports everything include/b200sd.h declares (no compute without a GPU), ctypes struct
+layouts equal the C compiler's, and the host logic (scheduler coefficients, shape tables, packers, serving app,
+latency percentile rule) agrees with the oracle / the reference's documented behaviour."""
+import ctypes
+import math
+import re
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+
+from oracle import sd21 as O
+
+ROOT = Path(__file__).resolve().parent.parent
+HEADER = ROOT / "include" / "b200sd.h"
+
+
+def test_library_exports_every_declared_symbol(lib_built):
+    from b200sd import _lib
+    declared = set(re.findall(r"\b(b200sd_[a-z0-9_]+)\s*\(", HEADER.read_text()))
+    assert declared and declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
+    lib = ctypes.CDLL(str(lib_built))
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert _lib.load().b200sd_abi_version() == _lib.ABI_VERSION == 2
+
+
+def test_ctypes_struct_layout_matches_c(lib_built, tmp_path):
+    """sizeof / offsetof from gcc on include/b200sd.h == the ctypes mirror in b200sd/_lib.py"""
+    from b200sd import _lib
+    pairs = {"b200sd_gemm_params": _lib.GemmParams, "b200sd_attention_params": _lib.AttentionParams,
+             "b200sd_groupnorm_params": _lib.GroupNormParams, "b200sd_layernorm_params": _lib.LayerNormParams,
+             "b200sd_im2col_params": _lib.Im2colParams, "b200sd_upsample_params": _lib.UpsampleParams,
+             "b200sd_cfg_sched_params": _lib.CfgSchedParams, "b200sd_small_linear_params": _lib.SmallLinearParams,
+             "b200sd_softmax_params": _lib.SoftmaxParams, "b200sd_denorm_u8_params": _lib.DenormU8Params,
+             "b200sd_cast_params": _lib.CastParams}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', f'#include "{HEADER}"', "int main(void){"]
+    for cname, cls in pairs.items():
+        lines.append(f'printf("{cname} %zu\\n", sizeof({cname}));')
+        for fname, _ in cls._fields_:
+            lines.append(f'printf("{cname}.{fname} %zu\\n", offsetof({cname}, {fname}));')
+    lines.append("return 0;}")
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", str(src), "-o", str(exe)], check=True)
+    got = dict(l.split() for l in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines())
+    for cname, cls in pairs.items():
+        assert int(got[cname]) == ctypes.sizeof(cls), cname
+        for fname, _ in cls._fields_:
+            assert int(got[f"{cname}.{fname}"]) == getattr(cls, fname).offset, f"{cname}.{fname}"
+
+
+def test_ops_refuse_cpu_tensors(lib_built):
+    """no CPU fallback: a CPU tensor must raise, not silently compute"""
+    from b200sd import ops
+    x = torch.zeros(8)
+    with pytest.raises(Exception):
+        ops.cast(x, torch.zeros(8, dtype=torch.bfloat16))
+    with pytest.raises(RuntimeError, match="CUDA-only"):
+        ops._cast(x, torch.zeros(8, dtype=torch.bfloat16))
+
+
+def test_argument_validation_without_gpu(lib_built):
+    from b200sd import _lib as L
+    lib = L.load()
+    p = L.GemmParams()
+    assert lib.b200sd_gemm(ctypes.byref(p), None) == -1 and b"null pointer" in lib.b200sd_last_error()
+    a = L.AttentionParams()
+    a.q = a.k = a.v = a.out = 16
+    a.head_dim = 512
+    assert lib.b200sd_attention(ctypes.byref(a), None) == -2  # unsupported head_dim, rejected before any launch
+    assert lib.b200sd_gemm_pick_block_n(2560, 1) == 256 and lib.b200sd_gemm_pick_block_n(320, 0) == 160
+
+
+@pytest.mark.parametrize("kind", ["ddim", "dpm++2m", "euler"])
+@pytest.mark.parametrize("pred", ["v_prediction", "epsilon"])
+@pytest.mark.parametrize("steps", [4, 20, 25])
+def test_scheduler_coefficients_match_oracle(lib_built, kind, pred, steps):
+    from b200sd import B200Scheduler
+    s = B200Scheduler(kind, pred, "cpu")
+    s.set_timesteps(steps)
+    o = O.SCHEDULERS[kind](pred)
+    o.set_timesteps(steps)
+    assert s._ts == o.timesteps
+    assert math.isclose(s.init_noise_sigma, o.init_noise_sigma, rel_tol=1e-12)
+    for i in range(steps):
+        c = o.coef(i)
+        for got, want in zip(s._rows[i], (c.cx, c.cm, c.cp, c.ax, c.am)):
+            assert math.isclose(got, want, rel_tol=1e-10, abs_tol=1e-12), (kind, pred, i)
+        assert math.isclose(s.in_scale(i), o.in_scale(i), rel_tol=1e-12)
+    assert torch.allclose(torch.tensor(s.acp, dtype=torch.float64), o.alphas_cumprod, rtol=1e-6)  # oracle betas are fp32-linspace^2 in fp64
+
+
+def test_shape_tables_match_oracle_modules(lib_built):
+    from b200sd import UNetConfig, VAEConfig
+    from b200sd._randinit import random_state_dicts, unet_param_shapes, vae_decoder_param_shapes
+    for ocfg in (O.tiny_unet_config(), O.sd21_unet_config()):
+        want = {k: tuple(v.shape) for k, v in O.UNet2DCondition(ocfg).state_dict().items()}
+        assert unet_param_shapes(UNetConfig.from_any(ocfg)) == want
+    for vcfg in (O.tiny_vae_config(), O.VAEConfig()):
+        want = {k: tuple(v.shape) for k, v in O.VAEDecoder(vcfg).state_dict().items()}
+        assert vae_decoder_param_shapes(VAEConfig.from_any(vcfg)) == want
+    usd, vsd = random_state_dicts(UNetConfig.from_any(O.tiny_unet_config()), VAEConfig.from_any(O.tiny_vae_config()))
+    O.UNet2DCondition(O.tiny_unet_config()).load_state_dict(usd)  # strict: same keys, same shapes
+    O.VAEDecoder(O.tiny_vae_config()).load_state_dict(vsd)
+    assert abs(float(usd["conv_norm_out.weight"].mean()) - 1.0) < 0.1
+
+
+def test_weight_packers(lib_built):
+    from b200sd.layers import pack_conv3x3, pack_geglu
+    w = torch.arange(2 * 3 * 9, dtype=torch.float32).view(2, 3, 3, 3)
+    p = pack_conv3x3(w)
+    assert p.shape == (2, 27) and float(p[1, (1 * 3 + 2) * 3 + 1]) == float(w[1, 1, 1, 2])  # K order (ky, kx, c)
+    w, b = torch.arange(16.0).view(16, 1).repeat(1, 8), torch.arange(16.0)
+    wp, bp = pack_geglu(w, b, 8)  # inner = 8, tiles of 4 values + 4 gates
+    assert bp.tolist() == [0, 1, 2, 3, 8, 9, 10, 11, 4, 5, 6, 7, 12, 13, 14, 15]
+    assert wp[:, 0].float().tolist() == bp.tolist()
+
+
+def test_latency_collector_percentile_rule(lib_built):
+    from b200sd.serving import LatencyCollector
+    lc = LatencyCollector()
+    lc.latency_list = [0.5, 0.1, 0.4, 0.2, 0.3]
+    # n=5: P0 -> idx0, P50 -> pos 2.5 (frac .5 not > .5 -> floor 2), P90 -> 4.5 -> floor 4, P95 -> 4.75 -> ceil capped 4
+    assert [lc.percentile(p) for p in (0, 50, 90, 95, 99, 100)] == [0.1, 0.3, 0.5, 0.5, 0.5, 0.5]
+    lc.latency_list = [float(i) for i in range(10)]
+    assert lc.percentile(55) == 5.0 and lc.percentile(56) == 6.0 and lc.percentile(100) == 9.0
+
+
+def test_shard_range_partitions_prompts(lib_built):
+    from b200sd.serving import shard_range
+    for n, w in [(16, 8), (17, 4), (3, 8), (128, 8)]:
+        parts = [list(shard_range(n, r, w)) for r in range(w)]
+        assert sum(parts, []) == list(range(n))
+        assert max(map(len, parts)) - min(map(len, parts)) <= 1
+
+
+def test_serving_app_routes_and_payloads(lib_built):
+    """the reference's HTTP surface (app/run-sd.py:153-203) with a fake engine -- no GPU involved"""
+    from types import SimpleNamespace
+
+    from fastapi.testclient import TestClient
+    from PIL import Image
+
+    from b200sd import serving
+
+    calls = []
+
+    def fake_pipe(**kw):
+        calls.append(kw)
+        return SimpleNamespace(images=[Image.new("RGB", (8, 8), (1, 2, 3))])
+
+    env = {"APP": "sd21", "POD_NAME": "pod0", "NODEPOOL": "b200-pool", "MODEL_ID": "stabilityai/stable-diffusion-2-1",
+           "DEVICE": "b200", "COMPILED_MODEL_ID": "none", "NUM_OF_RUNS_INF": "7"}
+    cfg = serving.read_env(env)
+    with pytest.raises(KeyError):
+        serving.read_env({k: v for k, v in env.items() if k != "NODEPOOL"})
+    sink = serving.MetricSink(use_cloudwatch=False)
+    client = TestClient(serving.create_app(serving.Engine(fake_pipe, cfg["NUM_OF_RUNS_INF"]), cfg, sink))
+    assert "pod0" in client.get("/").json()["message"]
+    assert client.get("/health").json() == {"message": "pod0is healthy"}
+    assert client.get("/readiness").json() == {"message": "pod0is ready"}
+    r = client.post("/genimage", json={"prompt": "a cat"}).json()
+    assert set(r) == {"prompt", "response", "latency"} and r["prompt"] == "a cat" and float(r["latency"]) >= 0
+    assert calls[-1] == {"prompt": "a cat", "num_inference_steps": 7}
+    import base64, io
+    assert Image.open(io.BytesIO(base64.b64decode(r["response"]))).size == (8, 8)
+    r = client.get("/load/3/infer/5").json()
+    assert r["message"].startswith("benchmark report:RESULT FOR stable_diffusion_512 on pod0:")
+    assert all(f"Latency P{p}=" in r["message"] for p in (0, 50, 90, 95, 99, 100))
+    assert len(calls) == 1 + 3 and calls[-1]["num_inference_steps"] == 5
+    assert [m["MetricName"] for m in sink.records] == ["sd21-counter", "b200-pool", "sd21-latency"]
+    assert [m["Unit"] for m in sink.records] == ["Count", "Count", "Seconds"]
+    r = client.post("/generate", json={"prompt": "x", "num_inference_steps": 3, "height": 512, "width": 512}).json()
+    assert set(r) == {"image", "execution_time"}
+    assert calls[-1] == {"prompt": "x", "num_inference_steps": 3, "height": 512, "width": 512}
+
+
+def test_stand_in_text_encoder_is_deterministic(lib_built):
+    from b200sd import StandInTextEncoder
+    te = StandInTextEncoder(1024)
+    a, b = te(["a cat", ""]), te(["a cat"])
+    assert a.shape == (2, 77, 1024) and torch.equal(a[0], b[0]) and not torch.equal(a[0], a[1])
