@@ -129,6 +129,21 @@ typedef struct {
 } b200sd_groupnorm_params;
 int64_t b200sd_groupnorm_workspace_bytes(const b200sd_groupnorm_params* p);
 int32_t b200sd_groupnorm(const b200sd_groupnorm_params* p, b200sd_stream_t stream);
+/* GroupNorm for hosts that cannot supply scratch memory -- it has no counterpart in the reference.
+ * Who needs it: an FFI front end (cgo, JNI, ctypes) that is handed device pointers for its tensors by some other
+ * component and links no CUDA runtime of its own, so it has nothing to allocate a workspace with; and a server whose
+ * whole device budget went to a tensor arena at start-up, leaving no memory to carve a workspace from.
+ * Same params and result as b200sd_groupnorm, but `workspace` / `workspace_bytes` are ignored: the split statistics
+ * go to a 256 KiB array built into the library (held by every GPU that loads it, until process exit).
+ *   - allocates nothing (no cudaMalloc / cudaFree or allocating library call);
+ *   - limit: n_img * splits * groups * 2 floats <= 65536, splits as in b200sd_groupnorm_workspace_bytes; beyond that
+ *     it returns B200SD_ERR_WORKSPACE and the message says to use b200sd_groupnorm;
+ *   - the first call on a device looks up the array's device address; issue that first call before any stream
+ *     capture on that device;
+ *   - every call on a device shares the array, which keeps the previous call's contents; nothing needs clearing
+ *     (the statistics kernel overwrites every slot that is read), but calls whose kernels overlap on the GPU race
+ *     on it -- keep them ordered on one stream or by events. */
+int32_t b200sd_groupnorm_static_scratch(const b200sd_groupnorm_params* p, b200sd_stream_t stream);
 
 /* ---- LayerNorm over the last dim -> 16-bit (BasicTransformerBlock.norm1/2/3) ---------------------- */
 typedef struct {

@@ -84,6 +84,7 @@ SYMBOLS = {
     "b200sd_attention": (c_i32, [C.POINTER(AttentionParams), c_vp]),
     "b200sd_groupnorm_workspace_bytes": (c_i64, [C.POINTER(GroupNormParams)]),
     "b200sd_groupnorm": (c_i32, [C.POINTER(GroupNormParams), c_vp]),
+    "b200sd_groupnorm_static_scratch": (c_i32, [C.POINTER(GroupNormParams), c_vp]),
     "b200sd_layernorm": (c_i32, [C.POINTER(LayerNormParams), c_vp]),
     "b200sd_im2col3x3": (c_i32, [C.POINTER(Im2colParams), c_vp]),
     "b200sd_upsample2x": (c_i32, [C.POINTER(UpsampleParams), c_vp]),

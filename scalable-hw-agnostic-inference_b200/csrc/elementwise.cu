@@ -574,3 +574,88 @@ extern "C" int32_t b200sd_cast(const b200sd_cast_params* p, b200sd_stream_t stre
     B200SD_CHECK_LAUNCH("cast");
     return B200SD_OK;
 }
+
+// =============================================================================================== GroupNorm, no-allocation variant
+// Some hosts that bind this library cannot hand it scratch memory.  A cgo / JNI / ctypes front end that only
+// receives device pointers for its tensors from another component has no CUDA runtime of its own to allocate
+// with, and a serving process that gave its whole device budget to a tensor arena at start-up has nothing left to
+// carve a workspace from.  For them the split statistics of GroupNorm live in this array, which is part of the
+// library image: every GPU that loads libb200sd.so holds these 256 KiB until the process exits.
+#include <mutex>
+
+namespace b200sd {
+
+constexpr long long GN_STATIC_SCRATCH_FLOATS = 65536;  // 256 KiB; n_img * splits * groups * 2 must fit
+static __device__ __align__(256) float g_gn_static_scratch[GN_STATIC_SCRATCH_FLOATS];
+
+// In host code `g_gn_static_scratch` is only a handle for the symbol, not an address a kernel may dereference.
+// The real device address is looked up once per device (with that device current) and cached.
+static int32_t gn_static_scratch_address(float** out) {
+    static std::mutex mu;
+    static float* cached[64] = {nullptr};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "groupnorm_static_scratch: cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= 64) return set_error(B200SD_ERR_DEVICE, "groupnorm_static_scratch: device index %d not in [0, 64)", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (cached[dev] == nullptr) {
+        float* p = nullptr;
+        e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_gn_static_scratch);
+        if (e != cudaSuccess || p == nullptr)
+            return set_error(B200SD_ERR_CUDA, "groupnorm_static_scratch: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        cached[dev] = p;
+    }
+    *out = cached[dev];
+    return B200SD_OK;
+}
+
+}  // namespace b200sd
+
+// Same computation and same two kernels as b200sd_groupnorm; `workspace` / `workspace_bytes` of the params are ignored.
+//  * Allocates nothing: no cudaMalloc / cudaFree, no allocating library call.
+//  * Limit: n_img * splits * groups * 2 floats <= 65536 (256 KiB), splits as chosen by b200sd_groupnorm_workspace_bytes;
+//    larger problems are refused with B200SD_ERR_WORKSPACE.  With 32 groups that is n_img * splits <= 1024, which covers
+//    the whole SD2.1 UNet at CFG batch 32 and the VAE at 768^2.
+//  * The first call on each device resolves the array's device address (cudaGetSymbolAddress); make that first call
+//    before starting any stream capture on that device.
+//  * All calls on a device share the one array and it keeps whatever the previous call left there.  Nothing has to be
+//    cleared: the statistics kernel overwrites every slot the normalising kernel later reads.  Two calls whose
+//    kernels overlap on the GPU (different streams, no dependency between them) race on it -- serialise them.
+extern "C" int32_t b200sd_groupnorm_static_scratch(const b200sd_groupnorm_params* p, b200sd_stream_t stream) {
+    B200SD_CHECK_ARG(p && p->x1 && p->y && p->gamma && p->beta, "groupnorm_static_scratch: null pointer");
+    const int c2 = p->x2 ? p->c2 : 0;
+    const int C = p->c1 + c2;
+    B200SD_CHECK_ARG(p->n_img > 0 && p->hw > 0, "groupnorm_static_scratch: bad shape");
+    B200SD_CHECK_ARG(p->groups > 0 && p->groups <= 64 && C % p->groups == 0, "groupnorm_static_scratch: C=%d groups=%d",
+                     C, p->groups);
+    B200SD_CHECK_ARG(p->c1 % 4 == 0 && c2 % 4 == 0 && C / 4 <= 1024,
+                     "groupnorm_static_scratch: channels must be multiples of 4, C<=4096");
+    B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype) && H_DTYPE(p->out_dtype), "groupnorm_static_scratch: bad in_dtype / out_dtype");
+    B200SD_CHECK_ARG(ALIGNED16(p->x1) && (!p->x2 || ALIGNED16(p->x2)) && ALIGNED16(p->y) && (!p->raw || ALIGNED16(p->raw)),
+                     "groupnorm_static_scratch: pointers must be 16-byte aligned");
+    const int splits = gn_splits(p->n_img, p->hw);
+    const long long need = (long long)p->n_img * splits * p->groups * 2;
+    if (need > GN_STATIC_SCRATCH_FLOATS)
+        return set_error(B200SD_ERR_WORKSPACE,
+                         "groupnorm_static_scratch: needs %lld floats of scratch (n_img=%d x splits=%d x groups=%d x 2) but the "
+                         "built-in array holds %lld; use b200sd_groupnorm with a caller-owned workspace",
+                         need, p->n_img, splits, p->groups, GN_STATIC_SCRATCH_FLOATS);
+    float* scratch = nullptr;
+    const int32_t rc = gn_static_scratch_address(&scratch);
+    if (rc != B200SD_OK) return rc;
+    const int vpp = C / 4;
+    int lanes = 256 / vpp;
+    if (lanes < 1) lanes = 1;
+    const int threads = vpp * lanes;
+    const size_t smem = (size_t)2 * lanes * C * sizeof(float);
+    cudaStream_t s = as_stream(stream);
+    const int chunks = splits * 2;
+    dim3 g1(splits, p->n_img), g2(chunks, p->n_img);
+    gn_stats_kernel<<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch);
+    gn_apply_kernel<<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch,
+                                           p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
+                                           p->out_dtype == B200SD_F16, chunks);
+    count_launch(2);
+    B200SD_CHECK_LAUNCH("groupnorm_static_scratch");
+    return B200SD_OK;
+}
