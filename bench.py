@@ -47,6 +47,7 @@ def parse():
     ap.add_argument("--operand-dtype", default=None, choices=[None, "fp16", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-only", action="store_true", help="one eager profiled pass, no timing (for ncu runs)")
+    ap.add_argument("--shape-profile", action="store_true", help="per-(kernel, shape) CUDA-event times of one eager pass")
     return ap.parse_args()
 
 
@@ -225,6 +226,19 @@ def run_b200(args):
         pipe.use_cuda_graph = False
         one_pass_device()
         torch.cuda.synchronize()
+        return
+    if args.shape_profile:
+        pipe.use_cuda_graph = False
+        one_pass_device()
+        ops.profile_begin()
+        one_pass_device()
+        prof = ops.profile_end(by_shape=True)
+        tot = sum(d["ms"] for d in prof.values())
+        print(f"total {tot:.2f} ms over {sum(d['launches'] for d in prof.values())} launches")
+        for k, d in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])[:60]:
+            rate = d["work"] / (d["ms"] * 1e-3) / 1e12
+            print(f"{d['ms']:9.3f} ms {100 * d['ms'] / tot:5.1f}%  n={d['launches']:4d}  avg {1000 * d['ms'] / d['launches']:8.1f} us  "
+                  f"{rate:8.2f} T(FLOP|B)/s  {k}")
         return
 
     for _ in range(max(args.warmup, 1)):

@@ -58,21 +58,22 @@ def profile_begin() -> None:
     _prof = []
 
 
-def profile_end():
-    """-> {kind: {"launches", "ms", "work"}}; work = algorithmic FLOPs (gemm, attention) or bytes (the rest)."""
+def profile_end(by_shape: bool = False):
+    """-> {kind: {"launches", "ms", "work"}}; work = algorithmic FLOPs (gemm, attention) or bytes (the rest).
+    by_shape=True keys the result by "kind shape" instead."""
     global _prof
     recs, _prof = _prof or [], None
     torch.cuda.synchronize()
     out = {}
-    for kind, work, s, e in recs:
-        d = out.setdefault(kind, {"launches": 0, "ms": 0.0, "work": 0.0})
+    for kind, work, s, e, tag in recs:
+        d = out.setdefault(f"{kind} {tag}" if by_shape else kind, {"launches": 0, "ms": 0.0, "work": 0.0})
         d["launches"] += 1
         d["ms"] += s.elapsed_time(e)
         d["work"] += work
     return out
 
 
-def _run(kind: str, work: float, fn, p) -> None:
+def _run(kind: str, work: float, fn, p, tag: str = "") -> None:
     if _prof is None:
         L.check(fn(C.byref(p), _stream()), kind)
         return
@@ -80,7 +81,7 @@ def _run(kind: str, work: float, fn, p) -> None:
     s.record()
     L.check(fn(C.byref(p), _stream()), kind)
     e.record()
-    _prof.append((kind, work, s, e))
+    _prof.append((kind, work, s, e, tag))
 
 
 def _nbytes(*ts) -> float:
@@ -101,7 +102,8 @@ def _gemm(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, ro
     p.out, p.out_dtype, p.ld_out = _ptr(out), _dt(out), out.stride(-2)
     p.geglu, p.block_n = int(geglu), block_n
     m = n_img * img_h * img_w
-    _run("gemm", 2.0 * m * w.shape[0] * taps * cin, L.load().b200sd_gemm, p)
+    _run("gemm", 2.0 * m * w.shape[0] * taps * cin, L.load().b200sd_gemm, p,
+         f"M{m} N{w.shape[0]} K{taps * cin} taps{taps} img{n_img}x{img_h}x{img_w}{' geglu' if geglu else ''}")
 
 
 def _attention(q, k, v, out, batch, heads, sq, skv, scale):
@@ -110,7 +112,8 @@ def _attention(q, k, v, out, batch, heads, sq, skv, scale):
     p.q, p.k, p.v, p.out = _ptr(q), _ptr(k), _ptr(v), _ptr(out)
     p.ld_q, p.ld_k, p.ld_v, p.ld_out = q.stride(-2), k.stride(-2), v.stride(-2), out.stride(-2)
     p.dtype, p.batch, p.heads, p.head_dim, p.sq, p.skv, p.scale = _dt(q), batch, heads, 64, sq, skv, scale
-    _run("attention", 4.0 * batch * heads * sq * skv * 64, L.load().b200sd_attention, p)
+    _run("attention", 4.0 * batch * heads * sq * skv * 64, L.load().b200sd_attention, p,
+         f"b{batch} h{heads} sq{sq} skv{skv}")
 
 
 def groupnorm_workspace_bytes(n_img: int, hw: int, groups: int = 32) -> int:
@@ -132,14 +135,15 @@ def _groupnorm(x1, x2, n_img, hw, groups, eps, gamma, beta, silu, y, raw, worksp
     p.y, p.raw, p.out_dtype = _ptr(y), _ptr(raw), _dt(y)
     p.workspace, p.workspace_bytes = _ptr(workspace), workspace.numel() * workspace.element_size()
     # algorithmic bytes: inputs read once for statistics and once to normalise, outputs written once
-    _run("groupnorm", 2 * _nbytes(x1, x2) + _nbytes(y, raw), L.load().b200sd_groupnorm, p)
+    _run("groupnorm", 2 * _nbytes(x1, x2) + _nbytes(y, raw), L.load().b200sd_groupnorm, p,
+         f"n{n_img} hw{hw} C{p.c1 + p.c2} {x1.dtype}")
 
 
 def _layernorm(x, eps, gamma, beta, y):
     p = L.LayerNormParams()
     p.x, p.in_dtype, p.rows, p.cols, p.eps = _ptr(x), _dt(x), x.numel() // x.shape[-1], x.shape[-1], eps
     p.gamma, p.beta, p.y, p.out_dtype = _ptr(gamma), _ptr(beta), _ptr(y), _dt(y)
-    _run("layernorm", _nbytes(x, y), L.load().b200sd_layernorm, p)
+    _run("layernorm", _nbytes(x, y), L.load().b200sd_layernorm, p, f"rows{p.rows} cols{p.cols}")
 
 
 def _im2col3x3(x, n_img, n_src, in_h, in_w, cin, stride, out):

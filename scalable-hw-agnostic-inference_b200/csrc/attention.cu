@@ -1,27 +1,33 @@
 // K3: fused flash attention for head_dim 64 on sm_100a (self- and cross-attention of BasicTransformerBlock).
 //
-//   warp 0      TMA producer : Q tile once, then K/V tiles (128 kv rows x 64) through a 3-stage ring
-//   warp 1      UMMA issuer  : S = Q K^T (128x128x64) into a double-buffered TMEM tile,
-//                              O += P V (128x64x128) with P from shared memory and V as an MN-major operand
-//   warps 2..5  softmax      : one query row per thread (tcgen05.ld 32x32b => no cross-lane reductions),
-//                              exp2 with the scale folded in, lazy rescale of O (only when the running max
-//                              grows by more than 2^8), P written as bf16 into the SWIZZLE_128B layout
-//
-// The S x S score matrix never leaves the SM.  FLOPs per launch: 4 * batch * heads * sq * skv * 64.
+// One CTA owns 256 query rows = two 128-row tiles (A, B) that share every K/V tile:
+//   warp 0        TMA producer : both Q tiles once, then K/V tiles (128 kv rows x 64) through a 3-stage ring
+//   warp 1        UMMA issuer  : S_t = Q_t K^T (128x128x64) into TMEM, O_t += P_t V (128x64x128) with P_t from
+//                                shared memory and V as an MN-major operand (no transpose of V anywhere)
+//   warps 2..5    softmax A    } one query row per thread (tcgen05.ld 32x32b => no cross-lane reductions), the whole
+//   warps 6..9    softmax B    } score row held in registers so S_t is released to the next QK^T at once; exp2 with the
+//                                scale folded in; lazy rescale of O (only when the running max grows by more than 2^8);
+//                                P written as 16-bit into the SWIZZLE_128B layout UMMA reads
+// Two softmax groups per SM give every scheduler two resident warps, and the tensor pipe always has the other
+// tile's GEMM to run while one group is in its exponentials.  The S x S score matrix never leaves the SM.
+// FLOPs per launch: 4 * batch * heads * sq * skv * 64.
 #include "common.h"
 #include "ptx.cuh"
 
 namespace b200sd {
 using namespace ptx;
 
-constexpr int ATT_BM = 128;
-constexpr int ATT_BN = 128;
+constexpr int ATT_BM = 128;          // rows per Q tile
+constexpr int ATT_QT = 2;            // Q tiles per CTA
+constexpr int ATT_BN = 128;          // kv rows per tile
 constexpr int ATT_D = 64;
 constexpr int ATT_STAGES = 3;
-constexpr int ATT_TILE = 128 * 128;  // bytes of a [128 x 64] bf16 tile
-constexpr int ATT_THREADS = 192;
-constexpr int ATT_SMEM = ATT_TILE /*Q*/ + ATT_STAGES * 2 * ATT_TILE /*K,V*/ + 2 * 2 * ATT_TILE /*P x2*/ + 1024 + 256;
-constexpr uint32_t ATT_TMEM_S0 = 0, ATT_TMEM_S1 = 128, ATT_TMEM_O = 256;
+constexpr int ATT_TILE = 128 * 128;  // bytes of a [128 x 64] 16-bit tile
+constexpr int ATT_THREADS = 32 * (2 + 4 * ATT_QT);
+constexpr int ATT_SMEM = ATT_QT * ATT_TILE /*Q*/ + ATT_STAGES * 2 * ATT_TILE /*K,V*/ + ATT_QT * 2 * ATT_TILE /*P*/ +
+                         1024 + 256;
+// TMEM columns: S_A 0..127, S_B 128..255, O_A 256..319, O_B 320..383
+constexpr uint32_t ATT_TMEM_S = 0, ATT_TMEM_O = 256;
 
 struct AttnKernelParams {
     int sq, skv, n_kv_tiles;
@@ -37,23 +43,24 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
-    uint8_t* sQ = smem;
-    uint8_t* sKV = sQ + ATT_TILE;                       // stage s: K at s*2*TILE, V at s*2*TILE + TILE
-    uint8_t* sP = sKV + ATT_STAGES * 2 * ATT_TILE;      // buffer b at b*2*TILE; two 64-wide kv chunks each
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * 2 * ATT_TILE);
+    uint8_t* sQ = smem;                                  // tile t at t*TILE
+    uint8_t* sKV = sQ + ATT_QT * ATT_TILE;               // stage s: K at s*2*TILE, V at s*2*TILE + TILE
+    uint8_t* sP = sKV + ATT_STAGES * 2 * ATT_TILE;       // tile t at t*2*TILE; two 64-wide kv chunks each
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + ATT_QT * 2 * ATT_TILE);
     uint64_t* q_full = bars;
     uint64_t* kv_full = bars + 1;
     uint64_t* kv_empty = kv_full + ATT_STAGES;
-    uint64_t* s_full = kv_empty + ATT_STAGES;  // [2] UMMA -> softmax : S tile ready
-    uint64_t* s_free = s_full + 2;             // [2] softmax -> UMMA : S tile read out
-    uint64_t* p_full = s_free + 2;             // [2] softmax -> UMMA : P tile written (and O rescaled)
-    uint64_t* pv_done = p_full + 2;            // [2] UMMA -> softmax : O += P V finished
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 2);
+    uint64_t* s_full = kv_empty + ATT_STAGES;  // [QT] UMMA -> softmax : S tile ready
+    uint64_t* s_free = s_full + ATT_QT;        // [QT] softmax -> UMMA : S tile copied to registers
+    uint64_t* p_full = s_free + ATT_QT;        // [QT] softmax -> UMMA : P tile written (and O rescaled)
+    uint64_t* pv_done = p_full + ATT_QT;       // [QT] UMMA -> softmax : O += P V finished (P buffer free, O current)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + ATT_QT);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int q0 = blockIdx.x * ATT_BM;
+    const int q0 = blockIdx.x * (ATT_BM * ATT_QT);
     const int head = blockIdx.y, b = blockIdx.z;
     const int n_tiles = p.n_kv_tiles;
+    const bool has_b = q0 + ATT_BM < p.sq;  // second Q tile holds at least one live row
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmQ);
@@ -63,11 +70,11 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
     if (warp == 1 && lane == 0) {
         mbar_init(q_full, 1);
         for (int s = 0; s < ATT_STAGES; ++s) mbar_init(&kv_full[s], 1), mbar_init(&kv_empty[s], 1);
-        for (int s = 0; s < 2; ++s) {
-            mbar_init(&s_full[s], 1);
-            mbar_init(&s_free[s], 4);
-            mbar_init(&p_full[s], 4);
-            mbar_init(&pv_done[s], 1);
+        for (int t = 0; t < ATT_QT; ++t) {
+            mbar_init(&s_full[t], 1);
+            mbar_init(&s_free[t], 4);
+            mbar_init(&p_full[t], 4);
+            mbar_init(&pv_done[t], 1);
         }
         fence_barrier_init();
     }
@@ -79,8 +86,9 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
 
     if (warp == 0) {
         if (lane == 0) {
-            mbar_expect_tx(q_full, ATT_TILE);
+            mbar_expect_tx(q_full, (has_b ? 2 : 1) * ATT_TILE);
             tma_load_2d(sQ, &tmQ, q_full, head * ATT_D, b * p.sq + q0);
+            if (has_b) tma_load_2d(sQ + ATT_TILE, &tmQ, q_full, head * ATT_D, b * p.sq + q0 + ATT_BM);
             int stage = 0;
             uint32_t phase = 0;
             for (int j = 0; j < n_tiles; ++j) {
@@ -98,155 +106,170 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
             const uint32_t bf = p.is_f16 ? 0u : 1u;
             const uint32_t idesc_qk = umma_idesc(128, ATT_BN, bf, bf, 0, 0);
             const uint32_t idesc_pv = umma_idesc(128, ATT_D, bf, bf, 0, 1);  // V is MN-major
-            const uint32_t q_addr = smem_u32(sQ);
-            auto issue_qk = [&](int j, int stage) {
+            const int nq = has_b ? 2 : 1;
+            auto issue_qk = [&](int t, int stage) {
+                const uint32_t q_addr = smem_u32(sQ + t * ATT_TILE);
                 const uint32_t k_addr = smem_u32(sKV + stage * 2 * ATT_TILE);
-                const uint32_t d = tmem_base + ((j & 1) ? ATT_TMEM_S1 : ATT_TMEM_S0);
+                const uint32_t d = tmem_base + ATT_TMEM_S + t * 128;
 #pragma unroll
                 for (int ks = 0; ks < ATT_D / 16; ++ks)
                     umma_bf16(d, umma_desc_sw128(q_addr + ks * 32), umma_desc_sw128(k_addr + ks * 32), idesc_qk,
                               ks != 0);
-                umma_commit(&s_full[j & 1]);
+                umma_commit(&s_full[t]);
             };
             mbar_wait(q_full, 0);
             mbar_wait(&kv_full[0], 0);
             tc_fence_after();
-            issue_qk(0, 0);
-            int stage = 0;       // stage of tile j
-            uint32_t phase = 0;  // phase of tile j's stage
+            for (int t = 0; t < nq; ++t) issue_qk(t, 0);
+            int stage = 0;       // stage of kv tile j
+            uint32_t phase = 0;  // phase of that stage
             for (int j = 0; j < n_tiles; ++j) {
                 int nstage = stage + 1;
                 uint32_t nphase = phase;
                 if (nstage == ATT_STAGES) nstage = 0, nphase ^= 1;
                 if (j + 1 < n_tiles) {
                     mbar_wait(&kv_full[nstage], nphase);
-                    if (j + 1 >= 2) mbar_wait(&s_free[(j + 1) & 1], (((j + 1) >> 1) - 1) & 1);
-                    tc_fence_after();
-                    issue_qk(j + 1, nstage);
+                    for (int t = 0; t < nq; ++t) {
+                        mbar_wait(&s_free[t], j & 1);  // softmax t has S_t(j) in registers
+                        tc_fence_after();
+                        issue_qk(t, nstage);
+                    }
                 }
-                mbar_wait(&p_full[j & 1], (j >> 1) & 1);
-                tc_fence_after();
-                const uint32_t p_addr = smem_u32(sP + (j & 1) * 2 * ATT_TILE);
                 const uint32_t v_addr = smem_u32(sKV + stage * 2 * ATT_TILE + ATT_TILE);
+                for (int t = 0; t < nq; ++t) {
+                    mbar_wait(&p_full[t], j & 1);
+                    tc_fence_after();
+                    const uint32_t p_addr = smem_u32(sP + t * 2 * ATT_TILE);
 #pragma unroll
-                for (int ks = 0; ks < ATT_BN / 16; ++ks) {
-                    const uint64_t adesc = umma_desc_sw128(p_addr + (ks >> 2) * ATT_TILE + (ks & 3) * 32);
-                    const uint64_t bdesc = umma_desc_sw128(v_addr + ks * 2048, /*lbo*/ 128 * 128, /*sbo*/ 1024);
-                    umma_bf16(tmem_base + ATT_TMEM_O, adesc, bdesc, idesc_pv, (j | ks) != 0);
+                    for (int ks = 0; ks < ATT_BN / 16; ++ks) {
+                        const uint64_t adesc = umma_desc_sw128(p_addr + (ks >> 2) * ATT_TILE + (ks & 3) * 32);
+                        const uint64_t bdesc = umma_desc_sw128(v_addr + ks * 2048, /*lbo*/ 128 * 128, /*sbo*/ 1024);
+                        umma_bf16(tmem_base + ATT_TMEM_O + t * ATT_D, adesc, bdesc, idesc_pv, (j | ks) != 0);
+                    }
+                    umma_commit(&pv_done[t]);
                 }
                 umma_commit(&kv_empty[stage]);
-                umma_commit(&pv_done[j & 1]);
                 stage = nstage, phase = nphase;
             }
         }
         __syncwarp();
     } else {
-        // ---------------------------------------------------------------- softmax + output (128 threads)
-        const int quad = warp & 3;
-        const int row = quad * 32 + lane;
-        const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
-        const bool f16 = p.is_f16 != 0;
-        float m_used = 0.f, l = 0.f;
-        for (int j = 0; j < n_tiles; ++j) {
-            mbar_wait(&s_full[j & 1], (j >> 1) & 1);
-            tc_fence_after();
-            uint32_t s[4][32];
-            const uint32_t s_addr = tmem_base + ((j & 1) ? ATT_TMEM_S1 : ATT_TMEM_S0) + lane_off;
-#pragma unroll
-            for (int c = 0; c < 4; ++c) tmem_ld_x32(s_addr + c * 32, s[c]);
-            tmem_ld_wait();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&s_free[j & 1]);
-
-            const int valid = min(ATT_BN, p.skv - j * ATT_BN);  // live kv columns of this tile
-            float mx = -INFINITY;
-#pragma unroll
-            for (int c = 0; c < 4; ++c)
-#pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const float v = (c * 32 + i < valid) ? __uint_as_float(s[c][i]) : -INFINITY;
-                    mx = fmaxf(mx, v);
-                }
-            const float m_new = mx * p.scale_log2;
-            float alpha = 1.f;
-            bool need = false;
-            if (j == 0) {
-                m_used = m_new;
-            } else if (m_new > m_used + 8.0f) {
-                alpha = exp2f(m_used - m_new);
-                m_used = m_new;
-                need = true;
-            }
-            if (__any_sync(0xffffffffu, need)) {
-                // O holds tiles 0..j-1 once PV(j-1) has completed
-                mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);
+        // ---------------------------------------------------------------- softmax + output, group t = (warp-2)/4
+        const int t = (warp - 2) >> 2;
+        if (t == 0 || has_b) {
+            const int quad = warp & 3;
+            const int row = quad * 32 + lane;
+            const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
+            const uint32_t s_addr = tmem_base + ATT_TMEM_S + t * 128 + lane_off;
+            const uint32_t o_addr = tmem_base + ATT_TMEM_O + t * ATT_D + lane_off;
+            uint8_t* prow = sP + t * 2 * ATT_TILE + row * 128;
+            const bool f16 = p.is_f16 != 0;
+            const float sc = p.scale_log2;
+            float m_used = 0.f, l = 0.f;
+            for (int j = 0; j < n_tiles; ++j) {
+                mbar_wait(&s_full[t], j & 1);
                 tc_fence_after();
-                l *= alpha;
+                uint32_t s[4][32];
 #pragma unroll
-                for (int c = 0; c < ATT_D / 16; ++c) {
-                    uint32_t o[16];
-                    tmem_ld_x16(tmem_base + ATT_TMEM_O + lane_off + c * 16, o);
-                    tmem_ld_wait();
+                for (int c = 0; c < 4; ++c) tmem_ld_x32(s_addr + c * 32, s[c]);
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s_free[t]);
+
+                const int valid = p.skv - j * ATT_BN;  // live kv columns of this tile (>= 128: all)
+                float mx = -INFINITY;
+                if (valid >= ATT_BN) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-                    tmem_st_x16(tmem_base + ATT_TMEM_O + lane_off + c * 16, o);
+                    for (int c = 0; c < 4; ++c)
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(s[c][i]));
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c)
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (c * 32 + i < valid) mx = fmaxf(mx, __uint_as_float(s[c][i]));
                 }
-                tmem_st_wait();
-            }
-            // P buffer (j&1) was last read by PV(j-2)
-            if (j >= 2) mbar_wait(&pv_done[j & 1], ((j >> 1) - 1) & 1);
-            uint8_t* prow = sP + (j & 1) * 2 * ATT_TILE + row * 128;
-            float lsum = 0.f;
+                const float m_new = mx * sc;
+                float alpha = 1.f;
+                bool need = false;
+                if (j == 0) {
+                    m_used = m_new;
+                } else if (m_new > m_used + 8.0f) {
+                    alpha = exp2f(m_used - m_new);
+                    m_used = m_new;
+                    need = true;
+                }
+                // PV(j-1) must be complete before P_t is overwritten or O_t rescaled
+                if (j > 0) {
+                    mbar_wait(&pv_done[t], (j - 1) & 1);
+                    tc_fence_after();
+                }
+                if (__any_sync(0xffffffffu, need)) {
+                    l *= alpha;
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+                    for (int c = 0; c < ATT_D / 16; ++c) {
+                        uint32_t o[16];
+                        tmem_ld_x16(o_addr + c * 16, o);
+                        tmem_ld_wait();
 #pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    float e[8];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int col = c * 32 + g * 8 + i;
-                        const float v = exp2f(__uint_as_float(s[c][g * 8 + i]) * p.scale_log2 - m_used);
-                        e[i] = (col < valid) ? v : 0.f;
-                        lsum += e[i];
+                        for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                        tmem_st_x16(o_addr + c * 16, o);
                     }
-                    const int col0 = c * 32 + g * 8;
-                    const int chunk = col0 >> 6;             // which 64-wide kv chunk
-                    const int cc = (col0 & 63) >> 3;         // 16-byte chunk inside the 128-byte row
-                    *reinterpret_cast<uint4*>(prow + chunk * ATT_TILE + ((cc ^ (row & 7)) << 4)) =
-                        make_uint4(pack_h2(e[0], e[1], f16), pack_h2(e[2], e[3], f16), pack_h2(e[4], e[5], f16),
-                                   pack_h2(e[6], e[7], f16));
+                    tmem_st_wait();
                 }
-            }
-            l += lsum;
-            fence_proxy_async_smem();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&p_full[j & 1]);
-        }
-        // ---- epilogue: O / l -> bf16
-        const int last = n_tiles - 1;
-        mbar_wait(&pv_done[last & 1], (last >> 1) & 1);
-        tc_fence_after();
-        const float inv = 1.0f / l;
-        const int qrow = q0 + row;
-        uint16_t* orow = p.out + ((long long)b * p.sq + qrow) * p.ld_out + head * ATT_D;
+                float lsum = 0.f;
+                const float neg_m = -m_used;
 #pragma unroll
-        for (int c = 0; c < ATT_D / 16; ++c) {
-            uint32_t o[16];
-            tmem_ld_x16(tmem_base + ATT_TMEM_O + lane_off + c * 16, o);
-            tmem_ld_wait();
-            if (qrow < p.sq) {
-                uint4 v0 = make_uint4(pack_h2(__uint_as_float(o[0]) * inv, __uint_as_float(o[1]) * inv, f16),
-                                      pack_h2(__uint_as_float(o[2]) * inv, __uint_as_float(o[3]) * inv, f16),
-                                      pack_h2(__uint_as_float(o[4]) * inv, __uint_as_float(o[5]) * inv, f16),
-                                      pack_h2(__uint_as_float(o[6]) * inv, __uint_as_float(o[7]) * inv, f16));
-                uint4 v1 = make_uint4(pack_h2(__uint_as_float(o[8]) * inv, __uint_as_float(o[9]) * inv, f16),
-                                      pack_h2(__uint_as_float(o[10]) * inv, __uint_as_float(o[11]) * inv, f16),
-                                      pack_h2(__uint_as_float(o[12]) * inv, __uint_as_float(o[13]) * inv, f16),
-                                      pack_h2(__uint_as_float(o[14]) * inv, __uint_as_float(o[15]) * inv, f16));
-                *reinterpret_cast<uint4*>(orow + c * 16) = v0;
-                *reinterpret_cast<uint4*>(orow + c * 16 + 8) = v1;
+                for (int c = 0; c < 4; ++c) {
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        float e[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            float v = exp2f(fmaf(__uint_as_float(s[c][g * 8 + i]), sc, neg_m));
+                            if (valid < ATT_BN && c * 32 + g * 8 + i >= valid) v = 0.f;
+                            e[i] = v;
+                            lsum += v;
+                        }
+                        const int col0 = c * 32 + g * 8;
+                        const int chunk = col0 >> 6;      // which 64-wide kv chunk
+                        const int cc = (col0 & 63) >> 3;  // 16-byte chunk inside the 128-byte row
+                        *reinterpret_cast<uint4*>(prow + chunk * ATT_TILE + ((cc ^ (row & 7)) << 4)) =
+                            make_uint4(pack_h2(e[0], e[1], f16), pack_h2(e[2], e[3], f16), pack_h2(e[4], e[5], f16),
+                                       pack_h2(e[6], e[7], f16));
+                    }
+                }
+                l += lsum;
+                fence_proxy_async_smem();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&p_full[t]);
+            }
+            // ---- epilogue: O / l -> 16-bit
+            mbar_wait(&pv_done[t], (n_tiles - 1) & 1);
+            tc_fence_after();
+            const float inv = 1.0f / l;
+            const int qrow = q0 + t * ATT_BM + row;
+            uint16_t* orow = p.out + ((long long)b * p.sq + qrow) * p.ld_out + head * ATT_D;
+#pragma unroll
+            for (int c = 0; c < ATT_D / 16; ++c) {
+                uint32_t o[16];
+                tmem_ld_x16(o_addr + c * 16, o);
+                tmem_ld_wait();
+                if (qrow < p.sq) {
+                    uint4 v0 = make_uint4(pack_h2(__uint_as_float(o[0]) * inv, __uint_as_float(o[1]) * inv, f16),
+                                          pack_h2(__uint_as_float(o[2]) * inv, __uint_as_float(o[3]) * inv, f16),
+                                          pack_h2(__uint_as_float(o[4]) * inv, __uint_as_float(o[5]) * inv, f16),
+                                          pack_h2(__uint_as_float(o[6]) * inv, __uint_as_float(o[7]) * inv, f16));
+                    uint4 v1 = make_uint4(pack_h2(__uint_as_float(o[8]) * inv, __uint_as_float(o[9]) * inv, f16),
+                                          pack_h2(__uint_as_float(o[10]) * inv, __uint_as_float(o[11]) * inv, f16),
+                                          pack_h2(__uint_as_float(o[12]) * inv, __uint_as_float(o[13]) * inv, f16),
+                                          pack_h2(__uint_as_float(o[14]) * inv, __uint_as_float(o[15]) * inv, f16));
+                    *reinterpret_cast<uint4*>(orow + c * 16) = v0;
+                    *reinterpret_cast<uint4*>(orow + c * 16 + 8) = v1;
+                }
             }
         }
     }
@@ -303,7 +326,8 @@ extern "C" int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_str
     kp.out = static_cast<uint16_t*>(p->out);
     kp.ld_out = p->ld_out;
     kp.is_f16 = p->dtype == B200SD_F16;
-    dim3 grid((p->sq + ATT_BM - 1) / ATT_BM, p->heads, p->batch);
+    const int rows_per_cta = ATT_BM * ATT_QT;
+    dim3 grid((p->sq + rows_per_cta - 1) / rows_per_cta, p->heads, p->batch);
     attention_kernel<<<grid, ATT_THREADS, ATT_SMEM, as_stream(stream)>>>(tmQ, tmK, tmV, kp);
     count_launch();
     B200SD_CHECK_LAUNCH("attention_kernel");
