@@ -224,8 +224,12 @@ def run_b200(args):
 
     if args.profile_only:
         pipe.use_cuda_graph = False
+        ops._taglog = []
         one_pass_device()
         torch.cuda.synchronize()
+        out = Path(os.environ.get("B200SD_TAGLOG", str(ROOT / "gpurun_out" / "taglog.json")))
+        out.parent.mkdir(exist_ok=True)
+        out.write_text(json.dumps(ops._taglog))
         return
     if args.shape_profile:
         pipe.use_cuda_graph = False

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200SD_ABI_VERSION 2
+#define B200SD_ABI_VERSION 3
 
 typedef struct CUstream_st* b200sd_stream_t; /* == cudaStream_t / CUstream */
 
@@ -82,8 +82,15 @@ typedef struct {
                                tile by the host packer, b200sd/layers.py pack_geglu (first half of a tile = values,
                                second half = gates) */
     int32_t block_n;        /* 0 = choose; else one of 64, 128, 160, 256 */
+    void* workspace;        /* optional split-K scratch, 256-byte aligned, ZERO-FILLED once by the caller (the kernel
+                               leaves its counters at zero again); NULL = never split K */
+    int64_t workspace_bytes;
+    int32_t split_k;        /* 0 = choose (splits only when the problem has fewer tiles than SMs and a workspace is
+                               given), 1 = off, 2..8 = forced */
 } b200sd_gemm_params;
 int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stream);
+/* bytes of workspace this problem would use if one were supplied (0 = it would not split K) */
+int64_t b200sd_gemm_workspace_bytes(const b200sd_gemm_params* p);
 /* the block_n the library would choose for this problem (weight packers for GEGLU need it) */
 int32_t b200sd_gemm_pick_block_n(int32_t n_out, int32_t geglu);
 

@@ -7,7 +7,7 @@ from pathlib import Path
 
 _HERE = Path(__file__).resolve().parent
 LIB_PATH = _HERE / "libb200sd.so"
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 BF16, F32, F16 = 1, 2, 3
 
@@ -19,7 +19,8 @@ class GemmParams(C.Structure):
                 ("cin", c_i32), ("taps", c_i32), ("w", c_vp), ("w_dtype", c_i32), ("n_out", c_i32), ("bias", c_vp),
                 ("bias_along_m", c_i32), ("row_bias", c_vp), ("row_bias_stride", c_i64), ("residual", c_vp),
                 ("residual_dtype", c_i32), ("ld_res", c_i64), ("out", c_vp), ("out_dtype", c_i32), ("ld_out", c_i64),
-                ("geglu", c_i32), ("block_n", c_i32)]
+                ("geglu", c_i32), ("block_n", c_i32), ("workspace", c_vp), ("workspace_bytes", c_i64),
+                ("split_k", c_i32)]
 
 
 class AttentionParams(C.Structure):
@@ -81,6 +82,7 @@ SYMBOLS = {
     "b200sd_launch_count": (c_i64, []),
     "b200sd_gemm": (c_i32, [C.POINTER(GemmParams), c_vp]),
     "b200sd_gemm_pick_block_n": (c_i32, [c_i32, c_i32]),
+    "b200sd_gemm_workspace_bytes": (c_i64, [C.POINTER(GemmParams)]),
     "b200sd_attention": (c_i32, [C.POINTER(AttentionParams), c_vp]),
     "b200sd_groupnorm_workspace_bytes": (c_i64, [C.POINTER(GroupNormParams)]),
     "b200sd_groupnorm": (c_i32, [C.POINTER(GroupNormParams), c_vp]),

@@ -62,6 +62,9 @@ class Kernels:
         self.op_dtype = op_dtype or default_op_dtype()
         assert self.op_dtype in (torch.float16, torch.bfloat16)
         self._gn_ws: Optional[torch.Tensor] = None
+        # split-K scratch for GEMMs with fewer output tiles than SMs; zero-filled once, the kernel keeps its counters clean
+        self.gemm_ws = torch.zeros(int(os.environ.get("B200SD_GEMM_WS_MB", "96")) << 18, device=device,
+                                   dtype=torch.float32) if device.type == "cuda" else None
 
     def gn_workspace(self, n_img: int, hw: int, groups: int) -> torch.Tensor:
         need = ops.groupnorm_workspace_bytes(n_img, hw, groups)
@@ -93,11 +96,13 @@ class Kernels:
         if row_bias is not None and row_bias.shape[0] > 1:
             rb_stride = row_bias.stride(0)
         res2 = residual.view(-1, cout) if residual is not None else None
-        ops.gemm(a, n, h, wd, cin, 9, w, bias, False, row_bias, rb_stride, res2, out.view(-1, cout), False, 0)
+        ops.gemm(a, n, h, wd, cin, 9, w, bias, False, row_bias, rb_stride, res2, out.view(-1, cout), False, 0,
+                 self.gemm_ws, 0)
         return out
 
     def linear(self, a: torch.Tensor, w: torch.Tensor, bias, *, residual=None, out_dtype=None, geglu=False,
-               out: Optional[torch.Tensor] = None, bias_along_m: bool = False, block_n: int = 0) -> torch.Tensor:
+               out: Optional[torch.Tensor] = None, bias_along_m: bool = False, block_n: int = 0,
+               split_k: int = 0) -> torch.Tensor:
         """a 16-bit [M, K] (any leading dims), w 16-bit [N, K]."""
         k = a.shape[-1]
         m = a.numel() // k
@@ -105,7 +110,8 @@ class Kernels:
         if out is None:
             out = torch.empty(*a.shape[:-1], n_cols, device=self.device, dtype=out_dtype or self.trunk_dtype)
         res2 = residual.view(m, n_cols) if residual is not None else None
-        ops.gemm(a, 1, 1, m, k, 1, w, bias, bias_along_m, None, 0, res2, out.view(m, n_cols), geglu, block_n)
+        ops.gemm(a, 1, 1, m, k, 1, w, bias, bias_along_m, None, 0, res2, out.view(m, n_cols), geglu, block_n,
+                 self.gemm_ws, split_k)
         return out
 
     def im2col(self, x: torch.Tensor, n_img: int, stride: int, k_pad: int) -> torch.Tensor:

@@ -73,7 +73,12 @@ def profile_end(by_shape: bool = False):
     return out
 
 
+_taglog = None  # when a list: (kind, tag, work) of every launch in order (tools/ncu_by_shape.py joins it with ncu)
+
+
 def _run(kind: str, work: float, fn, p, tag: str = "") -> None:
+    if _taglog is not None:
+        _taglog.append((kind, tag, work))
     if _prof is None:
         L.check(fn(C.byref(p), _stream()), kind)
         return
@@ -90,7 +95,7 @@ def _nbytes(*ts) -> float:
 
 # ------------------------------------------------------------------------------------------------ impls
 def _gemm(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, row_bias_stride, residual, out,
-          geglu, block_n):
+          geglu, block_n, workspace=None, split_k=0):
     p = L.GemmParams()
     p.a, p.a_dtype, p.n_img, p.img_h, p.img_w, p.cin, p.taps = _ptr(a), _dt(a), n_img, img_h, img_w, cin, taps
     p.w, p.w_dtype, p.n_out = _ptr(w), _dt(w), w.shape[0]
@@ -100,7 +105,9 @@ def _gemm(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, ro
     if residual is not None:
         p.residual, p.residual_dtype, p.ld_res = _ptr(residual), _dt(residual), residual.stride(-2)
     p.out, p.out_dtype, p.ld_out = _ptr(out), _dt(out), out.stride(-2)
-    p.geglu, p.block_n = int(geglu), block_n
+    p.geglu, p.block_n, p.split_k = int(geglu), block_n, split_k
+    if workspace is not None:
+        p.workspace, p.workspace_bytes = _ptr(workspace), workspace.numel() * workspace.element_size()
     m = n_img * img_h * img_w
     _run("gemm", 2.0 * m * w.shape[0] * taps * cin, L.load().b200sd_gemm, p,
          f"M{m} N{w.shape[0]} K{taps * cin} taps{taps} img{n_img}x{img_h}x{img_w}{' geglu' if geglu else ''}")
@@ -212,7 +219,8 @@ def umma_selftest(a: torch.Tensor, b: torch.Tensor, b_mn_major: bool) -> torch.T
 # ------------------------------------------------------------------------------------------------ registration
 _SCHEMAS = {
     "gemm": ("(Tensor a, int n_img, int img_h, int img_w, int cin, int taps, Tensor w, Tensor? bias, bool bias_along_m, "
-             "Tensor? row_bias, int row_bias_stride, Tensor? residual, Tensor(a!) out, bool geglu, int block_n) -> ()", _gemm),
+             "Tensor? row_bias, int row_bias_stride, Tensor? residual, Tensor(a!) out, bool geglu, int block_n, "
+             "Tensor(b!)? workspace=None, int split_k=0) -> ()", _gemm),
     "attention": ("(Tensor q, Tensor k, Tensor v, Tensor(a!) out, int batch, int heads, int sq, int skv, float scale) -> ()",
                   _attention),
     "groupnorm": ("(Tensor x1, Tensor? x2, int n_img, int hw, int groups, float eps, Tensor gamma, Tensor beta, bool silu, "

@@ -56,7 +56,19 @@ __global__ void gn_stats_kernel(const void* __restrict__ x1, int c1, const void*
     const int cs = second ? c2 : c1;
     const size_t off = (size_t)n * hw * cs + (second ? ch - c1 : ch);
     float s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
-    for (int p = p0 + pl; p < p1; p += lanes) {
+    int p = p0 + pl;
+    // four independent loads in flight per thread: these tensors are read once, so latency hiding is all that matters
+    for (; p + 3 * lanes < p1; p += 4 * lanes) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = load4(src, off + (size_t)(p + u * lanes) * cs, dt);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            s[0] += v[u].x, s[1] += v[u].y, s[2] += v[u].z, s[3] += v[u].w;
+            q[0] += v[u].x * v[u].x, q[1] += v[u].y * v[u].y, q[2] += v[u].z * v[u].z, q[3] += v[u].w * v[u].w;
+        }
+    }
+    for (; p < p1; p += lanes) {
         const float4 v = load4(src, off + (size_t)p * cs, dt);
         s[0] += v.x, s[1] += v.y, s[2] += v.z, s[3] += v.w;
         q[0] += v.x * v.x, q[1] += v.y * v.y, q[2] += v.z * v.z, q[3] += v.w * v.w;
@@ -89,12 +101,22 @@ __global__ void gn_apply_kernel(const void* __restrict__ x1, int c1, const void*
     const int ch = vec << 2;
     const int n = blockIdx.y;
     const int cpg = C / groups;
+    // fixed-order reduction of the split statistics: 8 strided partial sums per group, then those 8 in order
+    __shared__ float s_pa[64][8], s_pb[64][8];
+    for (int t = threadIdx.x; t < groups * 8; t += blockDim.x) {
+        const int g = t >> 3, k = t & 7;
+        float a = 0.f, b = 0.f;
+        for (int s = k; s < splits; s += 8) {
+            const float2 in = *reinterpret_cast<const float2*>(partial + (((size_t)n * splits + s) * groups + g) * 2);
+            a += in.x, b += in.y;
+        }
+        s_pa[g][k] = a, s_pb[g][k] = b;
+    }
+    __syncthreads();
     for (int g = threadIdx.x; g < groups; g += blockDim.x) {
         float a = 0.f, b = 0.f;
-        for (int s = 0; s < splits; ++s) {
-            const float* in = partial + (((size_t)n * splits + s) * groups + g) * 2;
-            a += in[0], b += in[1];
-        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a += s_pa[g][k], b += s_pb[g][k];
         const float inv = 1.0f / ((float)cpg * (float)hw);
         const float mean = a * inv;
         const float var = fmaxf(b * inv - mean * mean, 0.f);
@@ -116,14 +138,22 @@ __global__ void gn_apply_kernel(const void* __restrict__ x1, int c1, const void*
     const int p0 = blockIdx.x * per;
     const int p1 = min(hw, p0 + per);
     const bool f16 = out_f16 != 0;
-    for (int p = p0 + pl; p < p1; p += lanes) {
-        const float4 v = load4(src, off + (size_t)p * cs, dt);
+    auto emit = [&](int p, const float4& v) {
         const size_t o = ((size_t)n * hw + p) * C + ch;
         if (raw) store4_h(raw, o, v, f16);
         float4 r = make_float4(v.x * sc[0] + sh[0], v.y * sc[1] + sh[1], v.z * sc[2] + sh[2], v.w * sc[3] + sh[3]);
         if (silu) r = make_float4(silu_f(r.x), silu_f(r.y), silu_f(r.z), silu_f(r.w));
         store4_h(y, o, r, f16);
+    };
+    int p = p0 + pl;
+    for (; p + 3 * lanes < p1; p += 4 * lanes) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = load4(src, off + (size_t)(p + u * lanes) * cs, dt);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) emit(p + u * lanes, v[u]);
     }
+    for (; p < p1; p += lanes) emit(p, load4(src, off + (size_t)p * cs, dt));
 }
 
 static int gn_splits(int n_img, int hw) {

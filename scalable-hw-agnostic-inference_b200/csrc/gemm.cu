@@ -3,10 +3,13 @@
 //   warp 0      TMA producer   : A = 4-D NHWC box (64 ch x bw x bh x bn pixels, shifted by the filter tap,
 //                                zero-filled outside the image = the conv padding), B = 64 x BLOCK_N weight box
 //   warp 1      UMMA issuer    : tcgen05.mma 128 x BLOCK_N x 16, fp32 accumulators in TMEM, double-buffered
-//   warps 2..5  epilogue       : tcgen05.ld -> bias / timestep-row bias / residual / GEGLU -> bf16|fp32 stores
+//   warps 2..5  epilogue       : tcgen05.ld -> bias / timestep-row bias / residual / GEGLU -> 16-bit | fp32 stores
 //
-// One CTA per SM; tiles are walked n-fastest so an A tile is fetched from HBM once and the weight matrix
-// stays L2-resident.  Algorithmic work per launch: 2*M*n_out*taps*cin FLOP.
+// One CTA per SM; work items are walked n-fastest so an A tile is fetched from HBM once and the weight matrix
+// stays L2-resident.  When a problem has fewer output tiles than SMs (the 24x24 and 12x12 UNet levels at small
+// batch) the K loop is split across CTAs: every split writes its fp32 partial tile to a caller-owned workspace,
+// and the CTA that arrives last at the tile's counter adds the partials in split order (deterministic) and runs
+// the epilogue.  Algorithmic work per launch: 2*M*n_out*taps*cin FLOP.
 #include "common.h"
 #include "ptx.cuh"
 
@@ -19,6 +22,11 @@ constexpr int A_TILE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
 constexpr int ACC_STRIDE = 256;                      // TMEM columns between the two accumulator buffers
 constexpr int TMEM_COLS = 512;
 constexpr int GEMM_THREADS = 192;
+constexpr int MAX_SPLITS = 8;
+constexpr int AUTO_SPLITS = 3;          // automatic K split factor (see plan_tiles)
+constexpr int AUTO_SPLIT_MIN_KB = 128;  // ... only for K >= 8192
+constexpr int AUTO_SPLIT_MAX_M_TILES = 4;  // ... and at most 512 output rows
+constexpr int WS_COUNTERS = 1024;  // int32 tile counters at the start of the split-K workspace
 
 struct GemmKernelParams {
     int n_img, img_h, img_w, cin, taps;
@@ -27,6 +35,9 @@ struct GemmKernelParams {
     int tiles_x, tiles_y, m_tiles, n_tiles, kb_per_tap;
     int n_out, n_cols;  // n_cols = columns actually written (n_out, or n_out/2 for GEGLU)
     uint32_t a_box_bytes;
+    int splits;          // >= 1
+    float* partials;     // [tiles * splits][128][BLOCK_N] fp32 when splits > 1
+    int* counters;       // [tiles] int32, zero between launches
     const float* bias;
     int bias_along_m;
     const float* row_bias;
@@ -113,6 +124,51 @@ __device__ __forceinline__ void epilogue_store32(const GemmKernelParams& p, floa
     }
 }
 
+// ---- the same epilogue split into request / consume halves, for full 32-column chunks only -------------------
+__device__ __forceinline__ void res_prefetch32(const GemmKernelParams& p, long long m, int col0, uint4 (&buf)[8]) {
+    if (p.res_dtype == B200SD_F32) {
+        const uint4* r = reinterpret_cast<const uint4*>(static_cast<const float*>(p.residual) + m * p.ld_res + col0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) buf[j] = r[j];
+    } else {
+        const uint4* r = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.residual) + m * p.ld_res + col0);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) buf[j] = r[j];
+    }
+}
+__device__ __forceinline__ void res_add32(const GemmKernelParams& p, float (&v)[32], const uint4 (&buf)[8]) {
+    if (p.res_dtype == B200SD_F32) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            v[4 * j + 0] += __uint_as_float(buf[j].x), v[4 * j + 1] += __uint_as_float(buf[j].y);
+            v[4 * j + 2] += __uint_as_float(buf[j].z), v[4 * j + 3] += __uint_as_float(buf[j].w);
+        }
+    } else {
+        const bool f16 = p.res_dtype == B200SD_F16;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            v[8 * j + 0] += h_lo(buf[j].x, f16), v[8 * j + 1] += h_hi(buf[j].x, f16);
+            v[8 * j + 2] += h_lo(buf[j].y, f16), v[8 * j + 3] += h_hi(buf[j].y, f16);
+            v[8 * j + 4] += h_lo(buf[j].z, f16), v[8 * j + 5] += h_hi(buf[j].z, f16);
+            v[8 * j + 6] += h_lo(buf[j].w, f16), v[8 * j + 7] += h_hi(buf[j].w, f16);
+        }
+    }
+}
+__device__ __forceinline__ void store32_full(const GemmKernelParams& p, const float (&v)[32], long long m, int col0) {
+    if (p.out_dtype == B200SD_F32) {
+        float4* o = reinterpret_cast<float4*>(static_cast<float*>(p.out) + m * p.ld_out + col0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    } else {
+        const bool f16 = p.out_dtype == B200SD_F16;
+        uint4* o = reinterpret_cast<uint4*>(static_cast<uint16_t*>(p.out) + m * p.ld_out + col0);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            o[j] = make_uint4(pack_h2(v[8 * j], v[8 * j + 1], f16), pack_h2(v[8 * j + 2], v[8 * j + 3], f16),
+                              pack_h2(v[8 * j + 4], v[8 * j + 5], f16), pack_h2(v[8 * j + 6], v[8 * j + 7], f16));
+    }
+}
+
 // adds bias[n0 + j] (n0 = index into the bias vector, guarded by n_out) and the per-image row bias
 __device__ __forceinline__ void add_col_bias32(const GemmKernelParams& p, float (&v)[32], long long m, int img,
                                                int n0) {
@@ -162,6 +218,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     uint64_t* tmem_full = empty_bar + STAGES;
     uint64_t* tmem_empty = tmem_full + 2;
     uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    int* last_flag = reinterpret_cast<int*>(tmem_base_slot + 1);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -187,7 +244,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     tc_fence_after();
     const uint32_t tmem_base = *tmem_base_slot;
 
-    const int total_tiles = p.m_tiles * p.n_tiles;
+    const int splits = p.splits;
+    const int total_work = p.m_tiles * p.n_tiles * splits;  // work item w = tile * splits + split
     const int num_kb = p.taps * p.kb_per_tap;
 
     if (warp == 0) {
@@ -195,14 +253,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+            for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+                const int t = w / splits, split = w - t * splits;
                 const int n_tile = t % p.n_tiles;
                 const int m_tile = t / p.n_tiles;
                 const int tx = m_tile % p.tiles_x;
                 const int ty = (m_tile / p.tiles_x) % p.tiles_y;
                 const int tn = m_tile / (p.tiles_x * p.tiles_y);
                 const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bn;
-                for (int kb = 0; kb < num_kb; ++kb) {
+                const int kb0 = (int)((long long)split * num_kb / splits);
+                const int kb1 = (int)((long long)(split + 1) * num_kb / splits);
+                for (int kb = kb0; kb < kb1; ++kb) {
                     const int tap = kb / p.kb_per_tap;
                     const int c0 = (kb - tap * p.kb_per_tap) * BLOCK_K;
                     int dx = 0, dy = 0;
@@ -232,11 +293,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+            for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+                const int split = w % splits;
+                const int nkb = (int)((long long)(split + 1) * num_kb / splits) - (int)((long long)split * num_kb / splits);
                 mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * ACC_STRIDE;
-                for (int kb = 0; kb < num_kb; ++kb) {
+                for (int kb = 0; kb < nkb; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
                     const uint32_t a_addr = smem_u32(smem + stage * Cfg::STAGE_BYTES);
@@ -266,7 +329,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         const int box_pix = p.bw * p.bh;
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+            const int t = w / splits, split = w - t * splits;
             const int n_tile = t % p.n_tiles;
             const int m_tile = t / p.n_tiles;
             const int tx = m_tile % p.tiles_x;
@@ -285,44 +349,113 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
             const uint32_t t_addr = tmem_base + acc * ACC_STRIDE + ((uint32_t)(quad * 32) << 16);
-            if (!p.geglu) {
+            if (splits > 1) {
+                // ---- split-K: park the partial tile, release TMEM, elect the last-arriving split to finish the tile
+                float* mine = p.partials + ((size_t)w * BLOCK_M + row_in_tile) * BLOCK_N;
 #pragma unroll 1
                 for (int c = 0; c < BLOCK_N / 32; ++c) {
                     uint32_t r[32];
                     tmem_ld_x32(t_addr + c * 32, r);
                     tmem_ld_wait();
-                    const int col0 = n_tile * BLOCK_N + c * 32;
-                    if (valid && col0 < p.n_cols) {
-                        float v[32];
+                    float4* o = reinterpret_cast<float4*>(mine + c * 32);
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                        add_col_bias32(p, v, m, img, col0);
-                        epilogue_store32(p, v, m, img, col0);
+                    for (int j = 0; j < 8; ++j)
+                        o[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                           __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+                named_bar_sync(1, 128);  // all 128 rows of the partial tile are written ...
+                if (row_in_tile == 0) {
+                    __threadfence();     // ... and (fence cumulativity) visible device-wide before the count goes up
+                    const int old = atomicAdd(p.counters + t, 1);
+                    const int last = (old == splits - 1);
+                    if (last) {
+                        p.counters[t] = 0;  // leave the workspace clean for the next launch
+                        __threadfence();
+                    }
+                    *last_flag = last;
+                }
+                named_bar_sync(1, 128);
+                const bool last = *last_flag != 0;
+                named_bar_sync(1, 128);  // everyone has read the flag before the next work item rewrites it
+                if (last) {
+                    const float* base = p.partials + ((size_t)t * splits * BLOCK_M + row_in_tile) * BLOCK_N;
+#pragma unroll 1
+                    for (int c = 0; c < BLOCK_N / 32; ++c) {
+                        const int col0 = n_tile * BLOCK_N + c * 32;
+                        if (valid && col0 < p.n_cols) {
+                            float v[32];
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) v[j] = 0.f;
+                            for (int s = 0; s < splits; ++s) {
+                                const float4* src =
+                                    reinterpret_cast<const float4*>(base + (size_t)s * BLOCK_M * BLOCK_N + c * 32);
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) {
+                                    const float4 q = __ldcg(src + j);
+                                    v[4 * j] += q.x, v[4 * j + 1] += q.y, v[4 * j + 2] += q.z, v[4 * j + 3] += q.w;
+                                }
+                            }
+                            add_col_bias32(p, v, m, img, col0);
+                            epilogue_store32(p, v, m, img, col0);
+                        }
                     }
                 }
             } else {
-                constexpr int HALF = BLOCK_N / 2;
+                if (!p.geglu) {
+                    // The residual of chunk c+1 is requested before chunk c is finished: with one row per thread the
+                    // epilogue is latency-bound, so bytes in flight per SM are what set its speed.
+                    constexpr int NC = BLOCK_N / 32;
+                    const int colbase = n_tile * BLOCK_N;
+                    const bool pre = valid && p.residual != nullptr;
+                    uint4 rbuf[2][8];
+                    if (pre && colbase + 32 <= p.n_cols) res_prefetch32(p, m, colbase, rbuf[0]);
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) {
+                        const int col0 = colbase + c * 32;
+                        if (c + 1 < NC && pre && col0 + 64 <= p.n_cols) res_prefetch32(p, m, col0 + 32, rbuf[(c + 1) & 1]);
+                        uint32_t r[32];
+                        tmem_ld_x32(t_addr + c * 32, r);
+                        tmem_ld_wait();
+                        if (valid && col0 < p.n_cols) {
+                            float v[32];
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                            add_col_bias32(p, v, m, img, col0);
+                            if (col0 + 32 <= p.n_cols) {
+                                if (pre) res_add32(p, v, rbuf[c & 1]);
+                                store32_full(p, v, m, col0);
+                            } else {
+                                epilogue_store32(p, v, m, img, col0);  // ragged last chunk: element-wise path
+                            }
+                        }
+                    }
+                } else {
+                    constexpr int HALF = BLOCK_N / 2;
 #pragma unroll 1
-                for (int c = 0; c < HALF / 32; ++c) {
-                    uint32_t rv[32], rg[32];
-                    tmem_ld_x32(t_addr + c * 32, rv);
-                    tmem_ld_x32(t_addr + HALF + c * 32, rg);
-                    tmem_ld_wait();
-                    if (valid) {
-                        float v[32], g[32];
+                    for (int c = 0; c < HALF / 32; ++c) {
+                        uint32_t rv[32], rg[32];
+                        tmem_ld_x32(t_addr + c * 32, rv);
+                        tmem_ld_x32(t_addr + HALF + c * 32, rg);
+                        tmem_ld_wait();
+                        if (valid) {
+                            float v[32], g[32];
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(rv[j]), g[j] = __uint_as_float(rg[j]);
-                        add_col_bias32(p, v, m, img, n_tile * BLOCK_N + c * 32);
-                        add_col_bias32(p, g, m, img, n_tile * BLOCK_N + HALF + c * 32);
+                            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(rv[j]), g[j] = __uint_as_float(rg[j]);
+                            add_col_bias32(p, v, m, img, n_tile * BLOCK_N + c * 32);
+                            add_col_bias32(p, g, m, img, n_tile * BLOCK_N + HALF + c * 32);
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] *= gelu_erf(g[j]);
-                        epilogue_store32(p, v, m, img, n_tile * HALF + c * 32);
+                            for (int j = 0; j < 32; ++j) v[j] *= gelu_erf(g[j]);
+                            epilogue_store32(p, v, m, img, n_tile * HALF + c * 32);
+                        }
                     }
                 }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tmem_empty[acc]);
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
         }
@@ -362,25 +495,61 @@ static void choose_box(int n_img, int h, int w, int* bw, int* bh, int* bn) {
 
 static int pick_block_n_auto(int n_out, int geglu, long long m_tiles) {
     if (geglu) return (n_out % 256 == 0) ? 256 : 128;
-    const int sms = num_sms();
+    if (n_out <= 64) return 64;
+    // The main loop is bound by L2->SM bandwidth per SM (measured, tools/gemm_sweep.py): a work item costs
+    // (16 KiB of A + 128 B x block_n of B) per k-block, and items run in ceil(tiles / SMs) waves.  Pick the width
+    // that minimises waves x bytes; ties go to the wider tile.
+    const long long sms = num_sms();
     const int cands[4] = {256, 160, 128, 64};
-    int divisible[4], nd = 0;
-    for (int i = 0; i < 4; ++i)
-        if (n_out % cands[i] == 0) divisible[nd++] = cands[i];
-    if (nd == 0) {
-        if (n_out <= 64) return 64;
-        // least padded
-        int best = 128, waste = 1 << 30;
-        for (int i = 0; i < 3; ++i) {
-            int w = ((n_out + cands[i] - 1) / cands[i]) * cands[i] - n_out;
-            if (w < waste) waste = w, best = cands[i];
-        }
-        return best;
+    int best = 128;
+    long long best_cost = -1;
+    for (int i = 0; i < 4; ++i) {
+        const int bn = cands[i];
+        const long long tiles = m_tiles * ((n_out + bn - 1) / bn);
+        const long long cost = ((tiles + sms - 1) / sms) * (128 + bn);
+        if (best_cost < 0 || cost < best_cost) best_cost = cost, best = bn;
     }
-    // largest tile that still gives every SM a tile; else the smallest available
-    for (int i = 0; i < nd; ++i)
-        if (m_tiles * (n_out / divisible[i]) >= sms) return divisible[i];
-    return divisible[nd - 1];
+    return best;
+}
+
+// Tile width and K-split for a problem.  With a workspace, under-filled problems keep the widest tile (least L2->SM
+// traffic per FLOP) and split K instead of shrinking the tile.
+static void plan_tiles(int n_out, int geglu, long long m_tiles, int num_kb, int user_block_n, int user_split,
+                       bool have_ws, int* block_n, int* splits) {
+    *splits = 1;
+    if (user_block_n) {
+        *block_n = user_block_n;
+    } else {
+        *block_n = pick_block_n_auto(n_out, geglu, m_tiles);
+    }
+    if (geglu || !have_ws || user_split == 1) return;
+    const int sms = num_sms();
+    long long tiles = m_tiles * ((n_out + *block_n - 1) / *block_n);
+    int s = 1;
+    if (user_split > 1) {
+        s = user_split;
+    } else if (!user_block_n && m_tiles <= AUTO_SPLIT_MAX_M_TILES && num_kb >= AUTO_SPLIT_MIN_KB) {
+        // Measured (tools/gemm_sweep.py): parking partials + the counter handshake cost several us per work item, so
+        // splitting pays only for long K loops over very few rows -- the 12x12 UNet level at small batch
+        // (M = 288, K = 11520 / 23040): 128-wide tiles x 3 splits run 1.4-1.8x faster than any unsplit tiling.
+        const long long t128 = m_tiles * ((n_out + 127) / 128);
+        if (t128 * AUTO_SPLITS <= sms) {
+            *block_n = 128;
+            tiles = t128;
+            s = AUTO_SPLITS;
+        }
+    }
+    if (s > MAX_SPLITS) s = MAX_SPLITS;
+    if (s > num_kb) s = num_kb;
+    if (s >= 2 && tiles <= WS_COUNTERS) *splits = s;
+}
+
+static int64_t ws_bytes_for(long long tiles, int splits, int block_n) {
+    if (splits <= 1) return 0;
+    // the counter region has a FIXED size so that partial tiles of one launch can never land where another launch
+    // (with more tiles) keeps its counters; split problems have fewer tiles than SMs, far below WS_COUNTERS
+    if (tiles > WS_COUNTERS) return -1;
+    return WS_COUNTERS * 4 + (int64_t)tiles * splits * BLOCK_M * block_n * 4;
 }
 
 template <int BLOCK_N>
@@ -396,11 +565,52 @@ static int32_t launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const
         if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "gemm smem attribute: %s", cudaGetErrorString(e));
         attr_set[dev] = true;
     }
-    long long total = (long long)kp.m_tiles * kp.n_tiles;
+    long long total = (long long)kp.m_tiles * kp.n_tiles * kp.splits;
     int grid = (int)(total < num_sms() ? total : num_sms());
     gemm_kernel<BLOCK_N><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, kp);
     count_launch();
     B200SD_CHECK_LAUNCH("gemm_kernel");
+    return B200SD_OK;
+}
+
+struct GemmPlan {
+    GemmKernelParams kp;
+    int block_n;
+    int64_t ws_bytes;
+};
+
+static int32_t make_plan(const b200sd_gemm_params* p, bool have_ws, GemmPlan* plan) {
+    B200SD_CHECK_ARG(p->taps == 1 || p->taps == 9, "gemm: taps must be 1 or 9 (got %d)", p->taps);
+    B200SD_CHECK_ARG(p->n_img > 0 && p->img_h > 0 && p->img_w > 0 && p->cin > 0 && p->n_out > 0, "gemm: bad shape");
+    B200SD_CHECK_ARG(p->cin % 8 == 0, "gemm: cin (%d) must be a multiple of 8", p->cin);
+    GemmKernelParams& kp = plan->kp;
+    kp = GemmKernelParams{};
+    kp.n_img = p->n_img, kp.img_h = p->img_h, kp.img_w = p->img_w, kp.cin = p->cin, kp.taps = p->taps;
+    choose_box(p->n_img, p->img_h, p->img_w, &kp.bw, &kp.bh, &kp.bn);
+    kp.tiles_x = (p->img_w + kp.bw - 1) / kp.bw;
+    kp.tiles_y = (p->img_h + kp.bh - 1) / kp.bh;
+    const int tiles_n = (p->n_img + kp.bn - 1) / kp.bn;
+    kp.m_tiles = kp.tiles_x * kp.tiles_y * tiles_n;
+    kp.kb_per_tap = (p->cin + BLOCK_K - 1) / BLOCK_K;
+    kp.geglu = p->geglu ? 1 : 0;
+    kp.n_out = p->n_out, kp.n_cols = kp.geglu ? p->n_out / 2 : p->n_out;
+    kp.a_box_bytes = (uint32_t)(kp.bw * kp.bh * kp.bn) * BLOCK_K * 2;
+    B200SD_CHECK_ARG(p->block_n == 0 || p->block_n == 64 || p->block_n == 128 || p->block_n == 160 || p->block_n == 256,
+                     "gemm: block_n %d not in {0,64,128,160,256}", p->block_n);
+    B200SD_CHECK_ARG(p->split_k >= 0 && p->split_k <= MAX_SPLITS, "gemm: split_k %d not in [0,%d]", p->split_k,
+                     MAX_SPLITS);
+    int block_n = 0, splits = 1;
+    plan_tiles(p->n_out, kp.geglu, kp.m_tiles, p->taps * kp.kb_per_tap, p->block_n, p->split_k, have_ws, &block_n,
+               &splits);
+    if (kp.geglu) {
+        B200SD_CHECK_ARG((block_n == 128 || block_n == 256) && p->n_out % block_n == 0,
+                         "gemm: GEGLU needs block_n in {128,256} dividing n_out (%d)", p->n_out);
+        B200SD_CHECK_ARG(!p->bias_along_m, "gemm: GEGLU with bias_along_m is not supported");
+    }
+    kp.n_tiles = (p->n_out + block_n - 1) / block_n;
+    kp.splits = splits;
+    plan->block_n = block_n;
+    plan->ws_bytes = ws_bytes_for((long long)kp.m_tiles * kp.n_tiles, splits, block_n);
     return B200SD_OK;
 }
 
@@ -412,11 +622,15 @@ extern "C" int32_t b200sd_gemm_pick_block_n(int32_t n_out, int32_t geglu) {
     return pick_block_n_auto(n_out, geglu, 1 << 20);
 }
 
+extern "C" int64_t b200sd_gemm_workspace_bytes(const b200sd_gemm_params* p) {
+    if (!p) return 0;
+    GemmPlan plan;
+    if (make_plan(p, true, &plan) != B200SD_OK) return 0;
+    return plan.ws_bytes;
+}
+
 extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stream) {
     B200SD_CHECK_ARG(p && p->a && p->w && p->out, "gemm: null pointer");
-    B200SD_CHECK_ARG(p->taps == 1 || p->taps == 9, "gemm: taps must be 1 or 9 (got %d)", p->taps);
-    B200SD_CHECK_ARG(p->n_img > 0 && p->img_h > 0 && p->img_w > 0 && p->cin > 0 && p->n_out > 0, "gemm: bad shape");
-    B200SD_CHECK_ARG(p->cin % 8 == 0, "gemm: cin (%d) must be a multiple of 8", p->cin);
     B200SD_CHECK_ARG((reinterpret_cast<uintptr_t>(p->a) & 15) == 0 && (reinterpret_cast<uintptr_t>(p->w) & 15) == 0,
                      "gemm: a / w must be 16-byte aligned");
     B200SD_CHECK_ARG(p->out_dtype >= B200SD_BF16 && p->out_dtype <= B200SD_F16, "gemm: bad out_dtype");
@@ -446,33 +660,32 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
             B200SD_CHECK_ARG((reinterpret_cast<uintptr_t>(p->row_bias) & 15) == 0 && p->row_bias_stride % 4 == 0,
                              "gemm: row_bias must be 16-byte aligned, stride %% 4 == 0");
     }
-
-    GemmKernelParams kp{};
-    kp.n_img = p->n_img, kp.img_h = p->img_h, kp.img_w = p->img_w, kp.cin = p->cin, kp.taps = p->taps;
+    const bool have_ws = p->workspace != nullptr && p->workspace_bytes > 0;
+    B200SD_CHECK_ARG(!have_ws || (reinterpret_cast<uintptr_t>(p->workspace) & 255) == 0,
+                     "gemm: workspace must be 256-byte aligned");
+    GemmPlan plan;
+    int32_t rc = make_plan(p, have_ws, &plan);
+    if (rc) return rc;
+    if (plan.kp.splits > 1 && plan.ws_bytes > p->workspace_bytes) {
+        if (p->split_k > 1)
+            return set_error(B200SD_ERR_WORKSPACE, "gemm: split_k=%d needs %lld workspace bytes, have %lld", p->split_k,
+                             (long long)plan.ws_bytes, (long long)p->workspace_bytes);
+        rc = make_plan(p, false, &plan);  // workspace too small for the automatic split: run unsplit
+        if (rc) return rc;
+    }
+    GemmKernelParams& kp = plan.kp;
+    const int block_n = plan.block_n;
     kp.a_bf16 = p->a_dtype == B200SD_BF16, kp.b_bf16 = p->w_dtype == B200SD_BF16;
-    choose_box(p->n_img, p->img_h, p->img_w, &kp.bw, &kp.bh, &kp.bn);
-    kp.tiles_x = (p->img_w + kp.bw - 1) / kp.bw;
-    kp.tiles_y = (p->img_h + kp.bh - 1) / kp.bh;
-    const int tiles_n = (p->n_img + kp.bn - 1) / kp.bn;
-    kp.m_tiles = kp.tiles_x * kp.tiles_y * tiles_n;
-    kp.kb_per_tap = (p->cin + BLOCK_K - 1) / BLOCK_K;
-    kp.n_out = p->n_out, kp.n_cols = n_cols;
-    kp.a_box_bytes = (uint32_t)(kp.bw * kp.bh * kp.bn) * BLOCK_K * 2;
     kp.bias = p->bias, kp.bias_along_m = p->bias_along_m;
     kp.row_bias = p->row_bias, kp.row_bias_stride = p->row_bias_stride;
     kp.residual = p->residual, kp.res_dtype = p->residual_dtype, kp.ld_res = p->ld_res;
     kp.out = p->out, kp.out_dtype = p->out_dtype, kp.ld_out = p->ld_out;
-    kp.geglu = p->geglu ? 1 : 0;
-
-    int block_n = p->block_n ? p->block_n : pick_block_n_auto(p->n_out, kp.geglu, kp.m_tiles);
-    B200SD_CHECK_ARG(block_n == 64 || block_n == 128 || block_n == 160 || block_n == 256,
-                     "gemm: block_n %d not in {64,128,160,256}", block_n);
-    if (kp.geglu) {
-        B200SD_CHECK_ARG((block_n == 128 || block_n == 256) && p->n_out % block_n == 0,
-                         "gemm: GEGLU needs block_n in {128,256} dividing n_out (%d)", p->n_out);
-        B200SD_CHECK_ARG(!p->bias_along_m, "gemm: GEGLU with bias_along_m is not supported");
+    if (kp.splits > 1) {
+        const long long tiles = (long long)kp.m_tiles * kp.n_tiles;
+        kp.counters = static_cast<int*>(p->workspace);
+        (void)tiles;
+        kp.partials = reinterpret_cast<float*>(static_cast<uint8_t*>(p->workspace) + WS_COUNTERS * 4);
     }
-    kp.n_tiles = (p->n_out + block_n - 1) / block_n;
 
     CUtensorMap tmA, tmB;
     {
@@ -517,7 +730,7 @@ __global__ void __launch_bounds__(128, 1)
     __shared__ uint32_t tmem_slot;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
-    // A: row r, 16-byte chunk index cc (8 bf16) over the whole K extent
+    // A: row r, 16-byte chunk index cc (8 elements) over the whole K extent
     for (int i = tid; i < 128 * (k / 8); i += 128) {
         int r = i / (k / 8), cc = i % (k / 8);
         int kc = cc / 8, c = cc % 8;

@@ -68,6 +68,35 @@ def test_linear_plain(K, cuda, m, n, k, block_n):
     assert rel(out_h, ref) < out_tol(dt)
 
 
+@pytest.mark.parametrize("m,n,k,split", [(300, 1280, 2048, 0), (300, 1280, 2048, 4), (130, 320, 1024, 8), (1152, 640, 5120, 3),
+                                         (64, 64, 512, 2)])
+def test_linear_split_k_is_exact_and_deterministic(K, cuda, m, n, k, split):
+    """few output tiles -> K is split across CTAs through the workspace; partials are added in split order"""
+    dt = K.op_dtype
+    a, w = rnd(m, k, dev=cuda, seed=1, dtype=dt), rnd(n, k, dev=cuda, seed=2, scale=k ** -0.5, dtype=dt)
+    bias, res = rnd(n, dev=cuda, seed=3), rnd(m, n, dev=cuda, seed=4)
+    ref = a.float() @ w.float().t() + bias + res
+    outs = [K.linear(a, w, bias, residual=res, out_dtype=torch.float32, split_k=split) for _ in range(3)]
+    assert rel(outs[0], ref) < 2e-5
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[1], outs[2])
+    unsplit = K.linear(a, w, bias, residual=res, out_dtype=torch.float32, split_k=1)
+    assert rel(outs[0], unsplit) < 5e-6  # same products, different fp32 summation order
+    assert int(K.gemm_ws.view(torch.int32)[:1024].abs().max()) == 0  # tile counters are left at zero
+
+
+def test_conv3x3_split_k_low_res_levels(K, cuda):
+    """the 24x24 / 12x12 UNet levels at CFG batch 2: 1280 channels, automatic split"""
+    from b200sd.layers import pack_conv3x3
+    dt = K.op_dtype
+    for n, h, cin, cout in [(2, 12, 1280, 1280), (2, 24, 640, 1280)]:
+        x = rnd(n, h, h, cin, dev=cuda, seed=1, dtype=dt)
+        wt = rnd(cout, cin, 3, 3, dev=cuda, seed=2, scale=(9 * cin) ** -0.5)
+        bias = rnd(cout, dev=cuda, seed=3)
+        out = K.conv3x3(x, pack_conv3x3(wt, dt), bias, out_dtype=torch.float32)
+        ref = F.conv2d(x.float().permute(0, 3, 1, 2), wt.to(dt).float(), bias, padding=1).permute(0, 2, 3, 1)
+        assert rel(out, ref) < 2e-5
+
+
 def test_linear_mixed_operand_formats_rejected(cuda, lib_built):
     """fp16 x bf16 in one tcgen05.mma traps on B200 (measured: illegal instruction), so the ABI refuses it up front"""
     from b200sd.layers import Kernels
