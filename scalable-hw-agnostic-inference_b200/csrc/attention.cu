@@ -2,15 +2,18 @@
 //
 // One CTA owns 256 query rows = two 128-row tiles (A, B) that share every K/V tile:
 //   warp 0        TMA producer : both Q tiles once, then K/V tiles (128 kv rows x 64) through a 3-stage ring
-//   warp 1        UMMA issuer  : S_t = Q_t K^T (128x128x64) into TMEM, O_t += P_t V (128x64x128) with P_t from
-//                                shared memory and V as an MN-major operand (no transpose of V anywhere)
+//   warp 1        UMMA issuer  : S_t = Q_t K^T (128x128x64) into TMEM; O_t += P_t V (128x64x128) with P_t from shared
+//                                memory and V as an MN-major operand (no transpose of V anywhere); L_t += P_t 1
+//                                (128x16x128 against a constant tile of ones) = the softmax denominators, accumulated
+//                                in fp32 by the tensor core instead of one FADD per element in the softmax warps
 //   warps 2..5    softmax A    } one query row per thread (tcgen05.ld 32x32b => no cross-lane reductions), the whole
-//   warps 6..9    softmax B    } score row held in registers so S_t is released to the next QK^T at once; exp2 with the
-//                                scale folded in; lazy rescale of O (only when the running max grows by more than 2^8);
-//                                P written as 16-bit into the SWIZZLE_128B layout UMMA reads
-// Two softmax groups per SM give every scheduler two resident warps, and the tensor pipe always has the other
-// tile's GEMM to run while one group is in its exponentials.  The S x S score matrix never leaves the SM.
-// FLOPs per launch: 4 * batch * heads * sq * skv * 64.
+//   warps 6..9    softmax B    } score row held in registers so S_t is released to the next QK^T at once; lazy rescale
+//                                of O and L (only when the running max grows by more than 2^TAU); P written as 16-bit
+//                                into the SWIZZLE_128B layout UMMA reads.
+// The exponentials are the bound at d = 64 (16 MUFU/clk/SM against 8192 MACs/clk/SM).  With fp16 operands the
+// exponent is computed two at a time by ex2.approx.ftz.f16x2, whose packed result IS the fp16 P tile: half the MUFU
+// work, no conversion.  With bf16 operands the fp32 ex2 path is kept (a bf16 exponent argument is too coarse).
+// The S x S score matrix never leaves the SM.  FLOPs per launch: 4 * batch * heads * sq * skv * 64.
 #include "common.h"
 #include "ptx.cuh"
 
@@ -23,37 +26,60 @@ constexpr int ATT_BN = 128;          // kv rows per tile
 constexpr int ATT_D = 64;
 constexpr int ATT_STAGES = 3;
 constexpr int ATT_TILE = 128 * 128;  // bytes of a [128 x 64] 16-bit tile
+constexpr int ATT_ONES = 2 * 16 * 128;  // [16 rows x 128 k] of 1.0, two 64-wide k chunks
 constexpr int ATT_THREADS = 32 * (2 + 4 * ATT_QT);
 constexpr int ATT_SMEM = ATT_QT * ATT_TILE /*Q*/ + ATT_STAGES * 2 * ATT_TILE /*K,V*/ + ATT_QT * 2 * ATT_TILE /*P*/ +
-                         1024 + 256;
-// TMEM columns: S_A 0..127, S_B 128..255, O_A 256..319, O_B 320..383
-constexpr uint32_t ATT_TMEM_S = 0, ATT_TMEM_O = 256;
+                         ATT_ONES + 1024 + 256;
+// TMEM columns: S_A 0..127, S_B 128..255, O_A 256..319, O_B 320..383, L_A 384..399, L_B 400..415
+constexpr uint32_t ATT_TMEM_S = 0, ATT_TMEM_O = 256, ATT_TMEM_L = 384;
 
 struct AttnKernelParams {
     int sq, skv, n_kv_tiles;
     float scale_log2;  // scale * log2(e)
     uint16_t* out;
     long long ld_out;
-    int is_f16;        // q/k/v/P/out are fp16 (1) or bf16 (0)
 };
 
+__device__ __forceinline__ float ex2_ftz(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+// two exponentials at once on fp16 inputs; the packed fp16 result goes straight into the P tile
+__device__ __forceinline__ uint32_t ex2_f16x2(float lo, float hi) {
+    uint32_t h, y;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h) : "f"(hi), "f"(lo));
+    asm("ex2.approx.f16x2 %0, %1;" : "=r"(y) : "r"(h));
+    return y;
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+    float d;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+
+template <bool F16>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
     attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                      const __grid_constant__ CUtensorMap tmV, const AttnKernelParams p) {
+    // largest allowed gap between the true running max and the one the exponent still uses (log2 units):
+    // the fp16 exponent argument keeps 0.1 % accuracy up to |x| = 4; the fp32 path can afford 2^8
+    constexpr float TAU = F16 ? 4.0f : 8.0f;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
     uint8_t* sQ = smem;                                  // tile t at t*TILE
     uint8_t* sKV = sQ + ATT_QT * ATT_TILE;               // stage s: K at s*2*TILE, V at s*2*TILE + TILE
     uint8_t* sP = sKV + ATT_STAGES * 2 * ATT_TILE;       // tile t at t*2*TILE; two 64-wide kv chunks each
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + ATT_QT * 2 * ATT_TILE);
+    uint8_t* sOnes = sP + ATT_QT * 2 * ATT_TILE;         // chunk c at c*2048: [16 rows x 128 B] of 1.0
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sOnes + ATT_ONES);
     uint64_t* q_full = bars;
     uint64_t* kv_full = bars + 1;
     uint64_t* kv_empty = kv_full + ATT_STAGES;
     uint64_t* s_full = kv_empty + ATT_STAGES;  // [QT] UMMA -> softmax : S tile ready
     uint64_t* s_free = s_full + ATT_QT;        // [QT] softmax -> UMMA : S tile copied to registers
-    uint64_t* p_full = s_free + ATT_QT;        // [QT] softmax -> UMMA : P tile written (and O rescaled)
-    uint64_t* pv_done = p_full + ATT_QT;       // [QT] UMMA -> softmax : O += P V finished (P buffer free, O current)
+    uint64_t* p_full = s_free + ATT_QT;        // [QT] softmax -> UMMA : P tile written (and O, L rescaled)
+    uint64_t* pv_done = p_full + ATT_QT;       // [QT] UMMA -> softmax : O += P V, L += P 1 finished
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + ATT_QT);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -79,6 +105,13 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_slot, 512);
+    if (warp >= 2) {
+        // constant B operand of the row-sum MMA: every element 1.0 (so the swizzle pattern is immaterial)
+        const uint32_t one2 = F16 ? 0x3C003C00u : 0x3F803F80u;
+        uint4* o = reinterpret_cast<uint4*>(sOnes);
+        for (int i = threadIdx.x - 64; i < ATT_ONES / 16; i += ATT_THREADS - 64) o[i] = make_uint4(one2, one2, one2, one2);
+        fence_proxy_async_smem();
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -103,10 +136,12 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
         __syncwarp();
     } else if (warp == 1) {
         if (lane == 0) {
-            const uint32_t bf = p.is_f16 ? 0u : 1u;
-            const uint32_t idesc_qk = umma_idesc(128, ATT_BN, bf, bf, 0, 0);
-            const uint32_t idesc_pv = umma_idesc(128, ATT_D, bf, bf, 0, 1);  // V is MN-major
+            constexpr uint32_t bf = F16 ? 0u : 1u;
+            constexpr uint32_t idesc_qk = umma_idesc(128, ATT_BN, bf, bf, 0, 0);
+            constexpr uint32_t idesc_pv = umma_idesc(128, ATT_D, bf, bf, 0, 1);  // V is MN-major
+            constexpr uint32_t idesc_l = umma_idesc(128, 16, bf, bf, 0, 0);
             const int nq = has_b ? 2 : 1;
+            const uint32_t ones_addr = smem_u32(sOnes);
             auto issue_qk = [&](int t, int stage) {
                 const uint32_t q_addr = smem_u32(sQ + t * ATT_TILE);
                 const uint32_t k_addr = smem_u32(sKV + stage * 2 * ATT_TILE);
@@ -117,39 +152,55 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                               ks != 0);
                 umma_commit(&s_full[t]);
             };
-            mbar_wait(q_full, 0);
-            mbar_wait(&kv_full[0], 0);
-            tc_fence_after();
-            for (int t = 0; t < nq; ++t) issue_qk(t, 0);
-            int stage = 0;       // stage of kv tile j
-            uint32_t phase = 0;  // phase of that stage
-            for (int j = 0; j < n_tiles; ++j) {
-                int nstage = stage + 1;
-                uint32_t nphase = phase;
-                if (nstage == ATT_STAGES) nstage = 0, nphase ^= 1;
-                if (j + 1 < n_tiles) {
-                    mbar_wait(&kv_full[nstage], nphase);
-                    for (int t = 0; t < nq; ++t) {
-                        mbar_wait(&s_free[t], j & 1);  // softmax t has S_t(j) in registers
-                        tc_fence_after();
-                        issue_qk(t, nstage);
-                    }
-                }
+            auto issue_pv = [&](int t, int j, int stage) {
                 const uint32_t v_addr = smem_u32(sKV + stage * 2 * ATT_TILE + ATT_TILE);
-                for (int t = 0; t < nq; ++t) {
-                    mbar_wait(&p_full[t], j & 1);
-                    tc_fence_after();
-                    const uint32_t p_addr = smem_u32(sP + t * 2 * ATT_TILE);
+                const uint32_t p_addr = smem_u32(sP + t * 2 * ATT_TILE);
 #pragma unroll
-                    for (int ks = 0; ks < ATT_BN / 16; ++ks) {
-                        const uint64_t adesc = umma_desc_sw128(p_addr + (ks >> 2) * ATT_TILE + (ks & 3) * 32);
-                        const uint64_t bdesc = umma_desc_sw128(v_addr + ks * 2048, /*lbo*/ 128 * 128, /*sbo*/ 1024);
-                        umma_bf16(tmem_base + ATT_TMEM_O + t * ATT_D, adesc, bdesc, idesc_pv, (j | ks) != 0);
-                    }
-                    umma_commit(&pv_done[t]);
+                for (int ks = 0; ks < ATT_BN / 16; ++ks) {
+                    const uint64_t adesc = umma_desc_sw128(p_addr + (ks >> 2) * ATT_TILE + (ks & 3) * 32);
+                    const uint64_t bdesc = umma_desc_sw128(v_addr + ks * 2048, /*lbo*/ 128 * 128, /*sbo*/ 1024);
+                    umma_bf16(tmem_base + ATT_TMEM_O + t * ATT_D, adesc, bdesc, idesc_pv, (j | ks) != 0);
                 }
-                umma_commit(&kv_empty[stage]);
-                stage = nstage, phase = nphase;
+#pragma unroll
+                for (int ks = 0; ks < ATT_BN / 16; ++ks) {
+                    const uint64_t adesc = umma_desc_sw128(p_addr + (ks >> 2) * ATT_TILE + (ks & 3) * 32);
+                    const uint64_t bdesc = umma_desc_sw128(ones_addr + (ks >> 2) * 2048 + (ks & 3) * 32);
+                    umma_bf16(tmem_base + ATT_TMEM_L + t * 16, adesc, bdesc, idesc_l, (j | ks) != 0);
+                }
+                umma_commit(&pv_done[t]);
+            };
+            // Event-driven issue: the two Q tiles advance independently.  Whatever is ready goes next, P V first (the
+            // softmax group of that tile needs its completion before it may overwrite P), then the next Q K^T.
+            mbar_wait(q_full, 0);
+            tc_fence_after();
+            int next_qk[ATT_QT] = {0, 0}, next_pv[ATT_QT] = {0, 0};
+            int kv_ready = 0;  // kv tiles [0, kv_ready) have landed in shared memory
+            int released = 0;  // kv tiles [0, released) have been handed back to the producer
+            int pending = nq * n_tiles;
+            while (pending > 0) {
+                while (kv_ready < n_tiles &&
+                       mbar_try_wait(&kv_full[kv_ready % ATT_STAGES], (kv_ready / ATT_STAGES) & 1))
+                    ++kv_ready;
+#pragma unroll
+                for (int t = 0; t < ATT_QT; ++t) {
+                    if (t >= nq) continue;
+                    int j = next_pv[t];
+                    if (j < next_qk[t] && mbar_try_wait(&p_full[t], j & 1)) {
+                        tc_fence_after();
+                        issue_pv(t, j, j % ATT_STAGES);
+                        next_pv[t] = j + 1;
+                        --pending;
+                        int mn = next_pv[0];
+                        if (nq > 1 && next_pv[1] < mn) mn = next_pv[1];
+                        for (; released < mn; ++released) umma_commit(&kv_empty[released % ATT_STAGES]);
+                    }
+                    j = next_qk[t];
+                    if (j < kv_ready && (j == 0 || mbar_try_wait(&s_free[t], (j - 1) & 1))) {
+                        tc_fence_after();
+                        issue_qk(t, j % ATT_STAGES);
+                        next_qk[t] = j + 1;
+                    }
+                }
             }
         }
         __syncwarp();
@@ -162,10 +213,10 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
             const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
             const uint32_t s_addr = tmem_base + ATT_TMEM_S + t * 128 + lane_off;
             const uint32_t o_addr = tmem_base + ATT_TMEM_O + t * ATT_D + lane_off;
+            const uint32_t l_addr = tmem_base + ATT_TMEM_L + t * 16 + lane_off;
             uint8_t* prow = sP + t * 2 * ATT_TILE + row * 128;
-            const bool f16 = p.is_f16 != 0;
             const float sc = p.scale_log2;
-            float m_used = 0.f, l = 0.f;
+            float m_used = 0.f;
             for (int j = 0; j < n_tiles; ++j) {
                 mbar_wait(&s_full[t], j & 1);
                 tc_fence_after();
@@ -178,79 +229,92 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                 if (lane == 0) mbar_arrive(&s_free[t]);
 
                 const int valid = p.skv - j * ATT_BN;  // live kv columns of this tile (>= 128: all)
-                float mx = -INFINITY;
-                if (valid >= ATT_BN) {
-#pragma unroll
-                    for (int c = 0; c < 4; ++c)
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(s[c][i]));
-                } else {
+                if (valid < ATT_BN) {
+                    // ragged last tile: dead columns get a score whose exponential is exactly 0
 #pragma unroll
                     for (int c = 0; c < 4; ++c)
 #pragma unroll
                         for (int i = 0; i < 32; ++i)
-                            if (c * 32 + i < valid) mx = fmaxf(mx, __uint_as_float(s[c][i]));
+                            if (c * 32 + i >= valid) s[c][i] = __float_as_uint(-INFINITY);
                 }
-                const float m_new = mx * sc;
+                float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+#pragma unroll
+                    for (int i = 0; i < 32; i += 4) {
+                        mx0 = fmax3(mx0, __uint_as_float(s[c][i]), __uint_as_float(s[c][i + 1]));
+                        mx1 = fmax3(mx1, __uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3]));
+                    }
+                const float m_new = fmaxf(mx0, mx1) * sc;
                 float alpha = 1.f;
                 bool need = false;
                 if (j == 0) {
                     m_used = m_new;
-                } else if (m_new > m_used + 8.0f) {
-                    alpha = exp2f(m_used - m_new);
+                } else if (m_new > m_used + TAU) {
+                    alpha = ex2_ftz(m_used - m_new);
                     m_used = m_new;
                     need = true;
                 }
-                // PV(j-1) must be complete before P_t is overwritten or O_t rescaled
+                // exponentials first (registers only); they hide the tail of PV(j-1)
+                const float neg_m = -m_used;
+                uint32_t pk[16][4];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            // -inf * sc stays -inf (sc > 0); the fp16 conversion saturates it and ex2 returns 0
+                            const float x0 = fmaf(__uint_as_float(s[c][g * 8 + 2 * i]), sc, neg_m);
+                            const float x1 = fmaf(__uint_as_float(s[c][g * 8 + 2 * i + 1]), sc, neg_m);
+                            if constexpr (F16)
+                                pk[c * 4 + g][i] = ex2_f16x2(x0, x1);
+                            else
+                                pk[c * 4 + g][i] = pack_bf16x2(ex2_ftz(x0), ex2_ftz(x1));
+                        }
+                    }
+                }
+                // PV(j-1) must be complete before P_t is overwritten or O_t / L_t rescaled
                 if (j > 0) {
                     mbar_wait(&pv_done[t], (j - 1) & 1);
                     tc_fence_after();
                 }
                 if (__any_sync(0xffffffffu, need)) {
-                    l *= alpha;
 #pragma unroll
-                    for (int c = 0; c < ATT_D / 16; ++c) {
+                    for (int c = 0; c < ATT_D / 16 + 1; ++c) {  // four O chunks, then the L chunk
+                        const uint32_t a = c < ATT_D / 16 ? o_addr + c * 16 : l_addr;
                         uint32_t o[16];
-                        tmem_ld_x16(o_addr + c * 16, o);
+                        tmem_ld_x16(a, o);
                         tmem_ld_wait();
 #pragma unroll
                         for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-                        tmem_st_x16(o_addr + c * 16, o);
+                        tmem_st_x16(a, o);
                     }
                     tmem_st_wait();
                 }
-                float lsum = 0.f;
-                const float neg_m = -m_used;
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-#pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        float e[8];
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            float v = exp2f(fmaf(__uint_as_float(s[c][g * 8 + i]), sc, neg_m));
-                            if (valid < ATT_BN && c * 32 + g * 8 + i >= valid) v = 0.f;
-                            e[i] = v;
-                            lsum += v;
-                        }
-                        const int col0 = c * 32 + g * 8;
-                        const int chunk = col0 >> 6;      // which 64-wide kv chunk
-                        const int cc = (col0 & 63) >> 3;  // 16-byte chunk inside the 128-byte row
-                        *reinterpret_cast<uint4*>(prow + chunk * ATT_TILE + ((cc ^ (row & 7)) << 4)) =
-                            make_uint4(pack_h2(e[0], e[1], f16), pack_h2(e[2], e[3], f16), pack_h2(e[4], e[5], f16),
-                                       pack_h2(e[6], e[7], f16));
-                    }
+                for (int q = 0; q < 16; ++q) {
+                    const int col0 = q * 8;
+                    const int chunk = col0 >> 6;      // which 64-wide kv chunk
+                    const int cc = (col0 & 63) >> 3;  // 16-byte chunk inside the 128-byte row
+                    *reinterpret_cast<uint4*>(prow + chunk * ATT_TILE + ((cc ^ (row & 7)) << 4)) =
+                        make_uint4(pk[q][0], pk[q][1], pk[q][2], pk[q][3]);
                 }
-                l += lsum;
                 fence_proxy_async_smem();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&p_full[t]);
             }
-            // ---- epilogue: O / l -> 16-bit
+            // ---- epilogue: O / L -> 16-bit
             mbar_wait(&pv_done[t], (n_tiles - 1) & 1);
             tc_fence_after();
-            const float inv = 1.0f / l;
+            float inv;
+            {
+                uint32_t lv[16];
+                tmem_ld_x16(l_addr, lv);
+                tmem_ld_wait();
+                inv = 1.0f / __uint_as_float(lv[0]);
+            }
             const int qrow = q0 + t * ATT_BM + row;
             uint16_t* orow = p.out + ((long long)b * p.sq + qrow) * p.ld_out + head * ATT_D;
 #pragma unroll
@@ -259,16 +323,12 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                 tmem_ld_x16(o_addr + c * 16, o);
                 tmem_ld_wait();
                 if (qrow < p.sq) {
-                    uint4 v0 = make_uint4(pack_h2(__uint_as_float(o[0]) * inv, __uint_as_float(o[1]) * inv, f16),
-                                          pack_h2(__uint_as_float(o[2]) * inv, __uint_as_float(o[3]) * inv, f16),
-                                          pack_h2(__uint_as_float(o[4]) * inv, __uint_as_float(o[5]) * inv, f16),
-                                          pack_h2(__uint_as_float(o[6]) * inv, __uint_as_float(o[7]) * inv, f16));
-                    uint4 v1 = make_uint4(pack_h2(__uint_as_float(o[8]) * inv, __uint_as_float(o[9]) * inv, f16),
-                                          pack_h2(__uint_as_float(o[10]) * inv, __uint_as_float(o[11]) * inv, f16),
-                                          pack_h2(__uint_as_float(o[12]) * inv, __uint_as_float(o[13]) * inv, f16),
-                                          pack_h2(__uint_as_float(o[14]) * inv, __uint_as_float(o[15]) * inv, f16));
-                    *reinterpret_cast<uint4*>(orow + c * 16) = v0;
-                    *reinterpret_cast<uint4*>(orow + c * 16 + 8) = v1;
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        pk[i] = pack_h2(__uint_as_float(o[2 * i]) * inv, __uint_as_float(o[2 * i + 1]) * inv, F16);
+                    *reinterpret_cast<uint4*>(orow + c * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    *reinterpret_cast<uint4*>(orow + c * 16 + 8) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                 }
             }
         }
@@ -276,6 +336,24 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
     tc_fence_before();
     __syncthreads();
     if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+template <bool F16>
+static int32_t launch_attention(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
+                                const AttnKernelParams& kp, dim3 grid, cudaStream_t stream) {
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        cudaError_t e =
+            cudaFuncSetAttribute(attention_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM);
+        if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "attention smem attribute: %s", cudaGetErrorString(e));
+        attr_set[dev] = true;
+    }
+    attention_kernel<F16><<<grid, ATT_THREADS, ATT_SMEM, stream>>>(tmQ, tmK, tmV, kp);
+    count_launch();
+    B200SD_CHECK_LAUNCH("attention_kernel");
+    return B200SD_OK;
 }
 
 }  // namespace b200sd
@@ -287,6 +365,7 @@ extern "C" int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_str
     if (p->head_dim != 64) return set_error(B200SD_ERR_UNSUPPORTED, "attention: head_dim %d (only 64)", p->head_dim);
     B200SD_CHECK_ARG(p->batch > 0 && p->heads > 0 && p->sq > 0 && p->skv > 0, "attention: bad shape");
     B200SD_CHECK_ARG(p->dtype == B200SD_BF16 || p->dtype == B200SD_F16, "attention: dtype must be bf16 or fp16");
+    B200SD_CHECK_ARG(p->scale > 0.f, "attention: scale must be positive");
     B200SD_CHECK_ARG(p->ld_q % 8 == 0 && p->ld_k % 8 == 0 && p->ld_v % 8 == 0 && p->ld_out % 8 == 0,
                      "attention: leading dimensions must be multiples of 8");
     B200SD_CHECK_ARG(((reinterpret_cast<uintptr_t>(p->q) | reinterpret_cast<uintptr_t>(p->k) |
@@ -310,26 +389,14 @@ extern "C" int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_str
         r = encode_tmap_bf16(&tmV, p->v, 2, dims, strv, box);
         if (r) return r;
     }
-    static bool attr_set[64] = {false};
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-        cudaError_t e =
-            cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM);
-        if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "attention smem attribute: %s", cudaGetErrorString(e));
-        attr_set[dev] = true;
-    }
     AttnKernelParams kp;
     kp.sq = p->sq, kp.skv = p->skv;
     kp.n_kv_tiles = (p->skv + ATT_BN - 1) / ATT_BN;
     kp.scale_log2 = p->scale * 1.4426950408889634f;
     kp.out = static_cast<uint16_t*>(p->out);
     kp.ld_out = p->ld_out;
-    kp.is_f16 = p->dtype == B200SD_F16;
     const int rows_per_cta = ATT_BM * ATT_QT;
     dim3 grid((p->sq + rows_per_cta - 1) / rows_per_cta, p->heads, p->batch);
-    attention_kernel<<<grid, ATT_THREADS, ATT_SMEM, as_stream(stream)>>>(tmQ, tmK, tmV, kp);
-    count_launch();
-    B200SD_CHECK_LAUNCH("attention_kernel");
-    return B200SD_OK;
+    if (p->dtype == B200SD_F16) return launch_attention<true>(tmQ, tmK, tmV, kp, grid, as_stream(stream));
+    return launch_attention<false>(tmQ, tmK, tmV, kp, grid, as_stream(stream));
 }
