@@ -1,19 +1,22 @@
 // K3: fused flash attention for head_dim 64 on sm_100a (self- and cross-attention of BasicTransformerBlock).
 //
 // One CTA owns 256 query rows = two 128-row tiles (A, B) that share every K/V tile:
-//   warp 0        TMA producer : both Q tiles once, then K/V tiles (128 kv rows x 64) through a 3-stage ring
-//   warp 1        UMMA issuer  : S_t = Q_t K^T (128x128x64) into TMEM; O_t += P_t V (128x64x128) with P_t from shared
-//                                memory and V as an MN-major operand (no transpose of V anywhere); L_t += P_t 1
-//                                (128x16x128 against a constant tile of ones) = the softmax denominators, accumulated
-//                                in fp32 by the tensor core instead of one FADD per element in the softmax warps
-//   warps 2..5    softmax A    } one query row per thread (tcgen05.ld 32x32b => no cross-lane reductions), the whole
-//   warps 6..9    softmax B    } score row held in registers so S_t is released to the next QK^T at once; lazy rescale
-//                                of O and L (only when the running max grows by more than 2^TAU); P written as 16-bit
-//                                into the SWIZZLE_128B layout UMMA reads.
-// The exponentials are the bound at d = 64 (16 MUFU/clk/SM against 8192 MACs/clk/SM).  With fp16 operands the
-// exponent is computed two at a time by ex2.approx.ftz.f16x2, whose packed result IS the fp16 P tile: half the MUFU
-// work, no conversion.  With bf16 operands the fp32 ex2 path is kept (a bf16 exponent argument is too coarse).
+//   warp 0        TMA producer : both Q tiles once, then K/V tiles (128 kv rows x 64) through a 4-stage ring
+//   warp 1        UMMA issuer  : S_t = Q_t K^T (128x128x64, both operands from shared memory) into TMEM;
+//                                O_t += P_t V (128x64x128) with P_t read FROM TMEM (tcgen05.mma A-in-TMEM form) and V as
+//                                an MN-major shared-memory operand -- no transpose of V and no shared-memory round trip
+//                                for P.  Issue is event-driven: whichever of {P_A V, P_B V, Q_A K^T, Q_B K^T} is ready goes.
+//   warps 2..9    softmax A    } two threads per query row, 64 score columns each (tcgen05.ld 32x32b: a thread owns whole
+//   warps 10..17  softmax B    } columns of its row, so the only cross-thread step is one row-max exchange per tile);
+//                                the scores are held in registers so S_t is released to the next QK^T at once; exp2 with
+//                                the scale folded in; lazy rescale of O (only when the running max grows by more than
+//                                2^8); P packed to 16 bits and written back to TMEM with one tcgen05.st per thread.
+// Why P lives in TMEM: measured with P staged in shared memory, the kernel time did not move when the softmax work
+// was halved or the softmax warps doubled -- the shared-memory port (Q, K, V, P reads by the tensor core + P writes)
+// and the UMMA issue side were the bound, not the exponentials.
 // The S x S score matrix never leaves the SM.  FLOPs per launch: 4 * batch * heads * sq * skv * 64.
+#include <cstdlib>
+
 #include "common.h"
 #include "ptx.cuh"
 
@@ -24,14 +27,13 @@ constexpr int ATT_BM = 128;          // rows per Q tile
 constexpr int ATT_QT = 2;            // Q tiles per CTA
 constexpr int ATT_BN = 128;          // kv rows per tile
 constexpr int ATT_D = 64;
-constexpr int ATT_STAGES = 3;
+constexpr int ATT_STAGES = 4;
 constexpr int ATT_TILE = 128 * 128;  // bytes of a [128 x 64] 16-bit tile
-constexpr int ATT_ONES = 2 * 16 * 128;  // [16 rows x 128 k] of 1.0, two 64-wide k chunks
-constexpr int ATT_THREADS = 32 * (2 + 4 * ATT_QT);
-constexpr int ATT_SMEM = ATT_QT * ATT_TILE /*Q*/ + ATT_STAGES * 2 * ATT_TILE /*K,V*/ + ATT_QT * 2 * ATT_TILE /*P*/ +
-                         ATT_ONES + 1024 + 256;
-// TMEM columns: S_A 0..127, S_B 128..255, O_A 256..319, O_B 320..383, L_A 384..399, L_B 400..415
-constexpr uint32_t ATT_TMEM_S = 0, ATT_TMEM_O = 256, ATT_TMEM_L = 384;
+constexpr int ATT_THREADS = 32 * (2 + 8 * ATT_QT);  // TMA, UMMA, then 8 softmax warps per Q tile
+constexpr int ATT_XCH = 2 * ATT_QT * 256 * 4;       // row-max exchange [parity][tile][half][128] fp32
+constexpr int ATT_SMEM = ATT_QT * ATT_TILE /*Q*/ + ATT_STAGES * 2 * ATT_TILE /*K,V*/ + ATT_XCH + 1024 + 256;
+// TMEM columns: S_A 0..127, S_B 128..255, O_A 256..319, O_B 320..383, P_A 384..447, P_B 448..511 (16-bit pairs)
+constexpr uint32_t ATT_TMEM_S = 0, ATT_TMEM_O = 256, ATT_TMEM_P = 384;
 
 struct AttnKernelParams {
     int sq, skv, n_kv_tiles;
@@ -45,41 +47,65 @@ __device__ __forceinline__ float ex2_ftz(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
-// two exponentials at once on fp16 inputs; the packed fp16 result goes straight into the P tile
-__device__ __forceinline__ uint32_t ex2_f16x2(float lo, float hi) {
-    uint32_t h, y;
-    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h) : "f"(hi), "f"(lo));
-    asm("ex2.approx.f16x2 %0, %1;" : "=r"(y) : "r"(h));
-    return y;
+// 2^x on the FMA / ALU pipes (no MUFU): round-to-nearest split x = n + f, degree-3 minimax polynomial for 2^f on
+// [-0.5, 0.5] (max relative error 7.5e-5, well under half an fp16 ulp), then n added into the exponent field.
+// Valid for x <= 64; anything below -30 (including -inf) returns a value that rounds to 0 in 16 bits.
+__device__ __forceinline__ float exp2_poly(float x) {
+    x = fmaxf(x, -30.f);
+    const float t = x + 12582912.f;  // 1.5 * 2^23: the low mantissa bits of t now hold round(x)
+    const float f = x - (t - 12582912.f);
+    const float p = fmaf(fmaf(fmaf(0.055171668f, f, 0.24261112f), f, 0.69326099f), f, 0.99992807f);
+    return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
 }
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
     float d;
     asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
     return d;
 }
+// D[tmem] (+)= A[tmem] * B[smem]
+__device__ __forceinline__ void umma_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                        uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_x32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
+        "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
+        "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+        : "memory");
+}
 
-template <bool F16>
+// EMU_MASK: bit i set = pair i of every four pairs of exponentials is evaluated by exp2_poly instead of the MUFU.
+template <bool F16, int EMU_MASK>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
     attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                      const __grid_constant__ CUtensorMap tmV, const AttnKernelParams p) {
-    // largest allowed gap between the true running max and the one the exponent still uses (log2 units):
-    // the fp16 exponent argument keeps 0.1 % accuracy up to |x| = 4; the fp32 path can afford 2^8
-    constexpr float TAU = F16 ? 4.0f : 8.0f;
+    constexpr float TAU = 8.0f;  // largest lag (log2 units) of the max the exponent uses behind the true running max
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
     uint8_t* sQ = smem;                                  // tile t at t*TILE
     uint8_t* sKV = sQ + ATT_QT * ATT_TILE;               // stage s: K at s*2*TILE, V at s*2*TILE + TILE
-    uint8_t* sP = sKV + ATT_STAGES * 2 * ATT_TILE;       // tile t at t*2*TILE; two 64-wide kv chunks each
-    uint8_t* sOnes = sP + ATT_QT * 2 * ATT_TILE;         // chunk c at c*2048: [16 rows x 128 B] of 1.0
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sOnes + ATT_ONES);
+    float* xchg = reinterpret_cast<float*>(sKV + ATT_STAGES * 2 * ATT_TILE);  // [parity][tile][half][128]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(xchg) + ATT_XCH);
     uint64_t* q_full = bars;
     uint64_t* kv_full = bars + 1;
     uint64_t* kv_empty = kv_full + ATT_STAGES;
     uint64_t* s_full = kv_empty + ATT_STAGES;  // [QT] UMMA -> softmax : S tile ready
     uint64_t* s_free = s_full + ATT_QT;        // [QT] softmax -> UMMA : S tile copied to registers
-    uint64_t* p_full = s_free + ATT_QT;        // [QT] softmax -> UMMA : P tile written (and O, L rescaled)
-    uint64_t* pv_done = p_full + ATT_QT;       // [QT] UMMA -> softmax : O += P V, L += P 1 finished
+    uint64_t* p_full = s_free + ATT_QT;        // [QT] softmax -> UMMA : P tile in TMEM (and O rescaled)
+    uint64_t* pv_done = p_full + ATT_QT;       // [QT] UMMA -> softmax : O += P V finished
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + ATT_QT);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -98,20 +124,13 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
         for (int s = 0; s < ATT_STAGES; ++s) mbar_init(&kv_full[s], 1), mbar_init(&kv_empty[s], 1);
         for (int t = 0; t < ATT_QT; ++t) {
             mbar_init(&s_full[t], 1);
-            mbar_init(&s_free[t], 4);
-            mbar_init(&p_full[t], 4);
+            mbar_init(&s_free[t], 8);
+            mbar_init(&p_full[t], 8);
             mbar_init(&pv_done[t], 1);
         }
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_slot, 512);
-    if (warp >= 2) {
-        // constant B operand of the row-sum MMA: every element 1.0 (so the swizzle pattern is immaterial)
-        const uint32_t one2 = F16 ? 0x3C003C00u : 0x3F803F80u;
-        uint4* o = reinterpret_cast<uint4*>(sOnes);
-        for (int i = threadIdx.x - 64; i < ATT_ONES / 16; i += ATT_THREADS - 64) o[i] = make_uint4(one2, one2, one2, one2);
-        fence_proxy_async_smem();
-    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -138,10 +157,8 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
         if (lane == 0) {
             constexpr uint32_t bf = F16 ? 0u : 1u;
             constexpr uint32_t idesc_qk = umma_idesc(128, ATT_BN, bf, bf, 0, 0);
-            constexpr uint32_t idesc_pv = umma_idesc(128, ATT_D, bf, bf, 0, 1);  // V is MN-major
-            constexpr uint32_t idesc_l = umma_idesc(128, 16, bf, bf, 0, 0);
+            constexpr uint32_t idesc_pv = umma_idesc(128, ATT_D, bf, bf, 0, 1);  // A = P (TMEM, K-major), B = V MN-major
             const int nq = has_b ? 2 : 1;
-            const uint32_t ones_addr = smem_u32(sOnes);
             auto issue_qk = [&](int t, int stage) {
                 const uint32_t q_addr = smem_u32(sQ + t * ATT_TILE);
                 const uint32_t k_addr = smem_u32(sKV + stage * 2 * ATT_TILE);
@@ -154,23 +171,15 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
             };
             auto issue_pv = [&](int t, int j, int stage) {
                 const uint32_t v_addr = smem_u32(sKV + stage * 2 * ATT_TILE + ATT_TILE);
-                const uint32_t p_addr = smem_u32(sP + t * 2 * ATT_TILE);
+                const uint32_t p_tmem = tmem_base + ATT_TMEM_P + t * 64;
 #pragma unroll
                 for (int ks = 0; ks < ATT_BN / 16; ++ks) {
-                    const uint64_t adesc = umma_desc_sw128(p_addr + (ks >> 2) * ATT_TILE + (ks & 3) * 32);
+                    // 16 K-elements of P = 8 TMEM columns (two 16-bit values per column); 16 kv rows of V = 2048 bytes
                     const uint64_t bdesc = umma_desc_sw128(v_addr + ks * 2048, /*lbo*/ 128 * 128, /*sbo*/ 1024);
-                    umma_bf16(tmem_base + ATT_TMEM_O + t * ATT_D, adesc, bdesc, idesc_pv, (j | ks) != 0);
-                }
-#pragma unroll
-                for (int ks = 0; ks < ATT_BN / 16; ++ks) {
-                    const uint64_t adesc = umma_desc_sw128(p_addr + (ks >> 2) * ATT_TILE + (ks & 3) * 32);
-                    const uint64_t bdesc = umma_desc_sw128(ones_addr + (ks >> 2) * 2048 + (ks & 3) * 32);
-                    umma_bf16(tmem_base + ATT_TMEM_L + t * 16, adesc, bdesc, idesc_l, (j | ks) != 0);
+                    umma_ts(tmem_base + ATT_TMEM_O + t * ATT_D, p_tmem + ks * 8, bdesc, idesc_pv, (j | ks) != 0);
                 }
                 umma_commit(&pv_done[t]);
             };
-            // Event-driven issue: the two Q tiles advance independently.  Whatever is ready goes next, P V first (the
-            // softmax group of that tile needs its completion before it may overwrite P), then the next Q K^T.
             mbar_wait(q_full, 0);
             tc_fence_after();
             int next_qk[ATT_QT] = {0, 0}, next_pv[ATT_QT] = {0, 0};
@@ -179,13 +188,13 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
             int pending = nq * n_tiles;
             while (pending > 0) {
                 while (kv_ready < n_tiles &&
-                       mbar_try_wait(&kv_full[kv_ready % ATT_STAGES], (kv_ready / ATT_STAGES) & 1))
+                       mbar_test_wait(&kv_full[kv_ready % ATT_STAGES], (kv_ready / ATT_STAGES) & 1))
                     ++kv_ready;
 #pragma unroll
                 for (int t = 0; t < ATT_QT; ++t) {
                     if (t >= nq) continue;
                     int j = next_pv[t];
-                    if (j < next_qk[t] && mbar_try_wait(&p_full[t], j & 1)) {
+                    if (j < next_qk[t] && mbar_test_wait(&p_full[t], j & 1)) {
                         tc_fence_after();
                         issue_pv(t, j, j % ATT_STAGES);
                         next_pv[t] = j + 1;
@@ -195,7 +204,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                         for (; released < mn; ++released) umma_commit(&kv_empty[released % ATT_STAGES]);
                     }
                     j = next_qk[t];
-                    if (j < kv_ready && (j == 0 || mbar_try_wait(&s_free[t], (j - 1) & 1))) {
+                    if (j < kv_ready && (j == 0 || mbar_test_wait(&s_free[t], (j - 1) & 1))) {
                         tc_fence_after();
                         issue_qk(t, j % ATT_STAGES);
                         next_qk[t] = j + 1;
@@ -205,47 +214,54 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
         }
         __syncwarp();
     } else {
-        // ---------------------------------------------------------------- softmax + output, group t = (warp-2)/4
-        const int t = (warp - 2) >> 2;
+        // ---------------------------------------------------------------- softmax + output
+        // 8 warps per Q tile: tile t = (warp-2)/8; inside a tile warps 0..3 own score columns 0..63 of their 32 rows,
+        // warps 4..7 own columns 64..127 of the same rows (TMEM lane quadrant = warp % 4 either way).
+        const int t = (warp - 2) >> 3;
         if (t == 0 || has_b) {
+            const int half = ((warp - 2) >> 2) & 1;
             const int quad = warp & 3;
             const int row = quad * 32 + lane;
             const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
-            const uint32_t s_addr = tmem_base + ATT_TMEM_S + t * 128 + lane_off;
-            const uint32_t o_addr = tmem_base + ATT_TMEM_O + t * ATT_D + lane_off;
-            const uint32_t l_addr = tmem_base + ATT_TMEM_L + t * 16 + lane_off;
-            uint8_t* prow = sP + t * 2 * ATT_TILE + row * 128;
+            const uint32_t s_addr = tmem_base + ATT_TMEM_S + t * 128 + half * 64 + lane_off;
+            const uint32_t o_addr = tmem_base + ATT_TMEM_O + t * ATT_D + half * 32 + lane_off;
+            const uint32_t p_addr = tmem_base + ATT_TMEM_P + t * 64 + half * 32 + lane_off;
             const float sc = p.scale_log2;
-            float m_used = 0.f;
+            float m_used = 0.f, l = 0.f;
             for (int j = 0; j < n_tiles; ++j) {
                 mbar_wait(&s_full[t], j & 1);
                 tc_fence_after();
-                uint32_t s[4][32];
+                uint32_t s[2][32];
 #pragma unroll
-                for (int c = 0; c < 4; ++c) tmem_ld_x32(s_addr + c * 32, s[c]);
+                for (int c = 0; c < 2; ++c) tmem_ld_x32(s_addr + c * 32, s[c]);
                 tmem_ld_wait();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&s_free[t]);
 
-                const int valid = p.skv - j * ATT_BN;  // live kv columns of this tile (>= 128: all)
-                if (valid < ATT_BN) {
+                const int valid = p.skv - j * ATT_BN - half * 64;  // live kv columns among this thread's 64
+                if (valid < 64) {
                     // ragged last tile: dead columns get a score whose exponential is exactly 0
 #pragma unroll
-                    for (int c = 0; c < 4; ++c)
+                    for (int c = 0; c < 2; ++c)
 #pragma unroll
                         for (int i = 0; i < 32; ++i)
                             if (c * 32 + i >= valid) s[c][i] = __float_as_uint(-INFINITY);
                 }
                 float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
-                for (int c = 0; c < 4; ++c)
+                for (int c = 0; c < 2; ++c)
 #pragma unroll
                     for (int i = 0; i < 32; i += 4) {
                         mx0 = fmax3(mx0, __uint_as_float(s[c][i]), __uint_as_float(s[c][i + 1]));
                         mx1 = fmax3(mx1, __uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3]));
                     }
-                const float m_new = fmaxf(mx0, mx1) * sc;
+                // the other half of this row lives in the warp 4 further on (or back): exchange through shared memory,
+                // double-buffered by tile parity so one named barrier per tile suffices
+                float* xch = xchg + ((j & 1) * ATT_QT + t) * 256;
+                xch[half * 128 + row] = fmaxf(mx0, mx1);
+                named_bar_sync(2 + t, 256);
+                const float m_new = fmaxf(xch[row], xch[128 + row]) * sc;
                 float alpha = 1.f;
                 bool need = false;
                 if (j == 0) {
@@ -255,70 +271,61 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                     m_used = m_new;
                     need = true;
                 }
-                // exponentials first (registers only); they hide the tail of PV(j-1)
+                // exponentials (registers only); they hide the tail of PV(j-1)
                 const float neg_m = -m_used;
-                uint32_t pk[16][4];
+                uint32_t pk[32];
+                float ls0 = 0.f, ls1 = 0.f;
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
+                for (int c = 0; c < 2; ++c) {
 #pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            // -inf * sc stays -inf (sc > 0); the fp16 conversion saturates it and ex2 returns 0
-                            const float x0 = fmaf(__uint_as_float(s[c][g * 8 + 2 * i]), sc, neg_m);
-                            const float x1 = fmaf(__uint_as_float(s[c][g * 8 + 2 * i + 1]), sc, neg_m);
-                            if constexpr (F16)
-                                pk[c * 4 + g][i] = ex2_f16x2(x0, x1);
-                            else
-                                pk[c * 4 + g][i] = pack_bf16x2(ex2_ftz(x0), ex2_ftz(x1));
+                    for (int i = 0; i < 16; ++i) {
+                        // -inf * sc stays -inf (sc > 0) and both exponentials return 0 for it
+                        const float x0 = fmaf(__uint_as_float(s[c][2 * i]), sc, neg_m);
+                        const float x1 = fmaf(__uint_as_float(s[c][2 * i + 1]), sc, neg_m);
+                        float e0, e1;
+                        if ((EMU_MASK >> (i & 3)) & 1) {
+                            e0 = exp2_poly(x0), e1 = exp2_poly(x1);
+                        } else {
+                            e0 = ex2_ftz(x0), e1 = ex2_ftz(x1);
                         }
+                        ls0 += e0, ls1 += e1;
+                        pk[c * 16 + i] = pack_h2(e0, e1, F16);
                     }
                 }
-                // PV(j-1) must be complete before P_t is overwritten or O_t / L_t rescaled
+                // PV(j-1) must be complete before P_t is overwritten or O_t rescaled
                 if (j > 0) {
                     mbar_wait(&pv_done[t], (j - 1) & 1);
                     tc_fence_after();
                 }
                 if (__any_sync(0xffffffffu, need)) {
 #pragma unroll
-                    for (int c = 0; c < ATT_D / 16 + 1; ++c) {  // four O chunks, then the L chunk
-                        const uint32_t a = c < ATT_D / 16 ? o_addr + c * 16 : l_addr;
+                    for (int c = 0; c < 2; ++c) {  // this thread's 32 O columns
                         uint32_t o[16];
-                        tmem_ld_x16(a, o);
+                        tmem_ld_x16(o_addr + c * 16, o);
                         tmem_ld_wait();
 #pragma unroll
                         for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-                        tmem_st_x16(a, o);
+                        tmem_st_x16(o_addr + c * 16, o);
                     }
-                    tmem_st_wait();
                 }
-#pragma unroll
-                for (int q = 0; q < 16; ++q) {
-                    const int col0 = q * 8;
-                    const int chunk = col0 >> 6;      // which 64-wide kv chunk
-                    const int cc = (col0 & 63) >> 3;  // 16-byte chunk inside the 128-byte row
-                    *reinterpret_cast<uint4*>(prow + chunk * ATT_TILE + ((cc ^ (row & 7)) << 4)) =
-                        make_uint4(pk[q][0], pk[q][1], pk[q][2], pk[q][3]);
-                }
-                fence_proxy_async_smem();
+                l = l * alpha + (ls0 + ls1);
+                tmem_st_x32(p_addr, pk);  // 64 probabilities = 32 TMEM columns of this row
+                tmem_st_wait();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&p_full[t]);
             }
-            // ---- epilogue: O / L -> 16-bit
+            // ---- epilogue: O / l -> 16-bit (this thread's 32 of the 64 head-dim columns)
+            float* xch = xchg + (n_tiles & 1) * ATT_QT * 256 + t * 256;  // the buffer the last tile did not use
+            xch[half * 128 + row] = l;
+            named_bar_sync(2 + t, 256);
+            const float inv = 1.0f / (xch[row] + xch[128 + row]);
             mbar_wait(&pv_done[t], (n_tiles - 1) & 1);
             tc_fence_after();
-            float inv;
-            {
-                uint32_t lv[16];
-                tmem_ld_x16(l_addr, lv);
-                tmem_ld_wait();
-                inv = 1.0f / __uint_as_float(lv[0]);
-            }
             const int qrow = q0 + t * ATT_BM + row;
-            uint16_t* orow = p.out + ((long long)b * p.sq + qrow) * p.ld_out + head * ATT_D;
+            uint16_t* orow = p.out + ((long long)b * p.sq + qrow) * p.ld_out + head * ATT_D + half * 32;
 #pragma unroll
-            for (int c = 0; c < ATT_D / 16; ++c) {
+            for (int c = 0; c < 2; ++c) {
                 uint32_t o[16];
                 tmem_ld_x16(o_addr + c * 16, o);
                 tmem_ld_wait();
@@ -338,22 +345,31 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
     if (warp == 2) tmem_dealloc(tmem_base, 512);
 }
 
-template <bool F16>
+template <bool F16, int EMU_MASK>
 static int32_t launch_attention(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                                 const AttnKernelParams& kp, dim3 grid, cudaStream_t stream) {
     static bool attr_set[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-        cudaError_t e =
-            cudaFuncSetAttribute(attention_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM);
+        cudaError_t e = cudaFuncSetAttribute(attention_kernel<F16, EMU_MASK>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM);
         if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "attention smem attribute: %s", cudaGetErrorString(e));
         attr_set[dev] = true;
     }
-    attention_kernel<F16><<<grid, ATT_THREADS, ATT_SMEM, stream>>>(tmQ, tmK, tmV, kp);
+    attention_kernel<F16, EMU_MASK><<<grid, ATT_THREADS, ATT_SMEM, stream>>>(tmQ, tmK, tmV, kp);
     count_launch();
     B200SD_CHECK_LAUNCH("attention_kernel");
     return B200SD_OK;
+}
+
+static int emu_mask_from_env() {
+    static int cached = -1;
+    if (cached < 0) {
+        const char* e = getenv("B200SD_ATTN_EXP_EMU");
+        cached = (e && e[0] == '1') ? 1 : 0;
+    }
+    return cached;
 }
 
 }  // namespace b200sd
@@ -397,6 +413,11 @@ extern "C" int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_str
     kp.ld_out = p->ld_out;
     const int rows_per_cta = ATT_BM * ATT_QT;
     dim3 grid((p->sq + rows_per_cta - 1) / rows_per_cta, p->heads, p->batch);
-    if (p->dtype == B200SD_F16) return launch_attention<true>(tmQ, tmK, tmV, kp, grid, as_stream(stream));
-    return launch_attention<false>(tmQ, tmK, tmV, kp, grid, as_stream(stream));
+    cudaStream_t s = as_stream(stream);
+    const bool emu = emu_mask_from_env() != 0;
+    if (p->dtype == B200SD_F16)
+        return emu ? launch_attention<true, 0b1010>(tmQ, tmK, tmV, kp, grid, s)
+                   : launch_attention<true, 0>(tmQ, tmK, tmV, kp, grid, s);
+    return emu ? launch_attention<false, 0b1010>(tmQ, tmK, tmV, kp, grid, s)
+               : launch_attention<false, 0>(tmQ, tmK, tmV, kp, grid, s);
 }
