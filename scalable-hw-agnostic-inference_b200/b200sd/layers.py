@@ -22,6 +22,12 @@ def default_op_dtype() -> torch.dtype:
     return _OP_DTYPES[os.environ.get("B200SD_OPERAND_DTYPE", "fp16").lower()]
 
 
+def default_trunk_dtype() -> torch.dtype:
+    """dtype of the residual stream (the tensors every block adds into): fp32 unless B200SD_TRUNK_DTYPE says fp16/bf16"""
+    name = os.environ.get("B200SD_TRUNK_DTYPE", "fp32").lower()
+    return torch.float32 if name in ("fp32", "float32") else _OP_DTYPES[name]
+
+
 # ------------------------------------------------------------------------------------------------ packing
 def pack_conv3x3(w: torch.Tensor, dtype: torch.dtype = torch.float16) -> torch.Tensor:
     """[Cout, Cin, 3, 3] -> 16-bit [Cout, 9*Cin], K order (ky, kx, c)."""
@@ -55,10 +61,10 @@ def pack_geglu(w: torch.Tensor, b: torch.Tensor, block_n: int,
 class Kernels:
     """Helper bound to one device: owns the GroupNorm scratch and the dtype policy."""
 
-    def __init__(self, device: torch.device, trunk_dtype: torch.dtype = torch.float32,
+    def __init__(self, device: torch.device, trunk_dtype: Optional[torch.dtype] = None,
                  op_dtype: Optional[torch.dtype] = None):
         self.device = device
-        self.trunk_dtype = trunk_dtype
+        self.trunk_dtype = trunk_dtype or default_trunk_dtype()
         self.op_dtype = op_dtype or default_op_dtype()
         assert self.op_dtype in (torch.float16, torch.bfloat16)
         self._gn_ws: Optional[torch.Tensor] = None

@@ -76,7 +76,15 @@ def profile_end(by_shape: bool = False):
 _taglog = None  # when a list: (kind, tag, work) of every launch in order (tools/ncu_by_shape.py joins it with ncu)
 
 
+import os as _os
+
+# timing experiments only (tools/ablate.sh): kernel classes named here are NOT launched, so results are garbage
+_SKIP = frozenset(k for k in _os.environ.get("B200SD_DEBUG_SKIP", "").split(",") if k)
+
+
 def _run(kind: str, work: float, fn, p, tag: str = "") -> None:
+    if _SKIP and kind in _SKIP:
+        return
     if _taglog is not None:
         _taglog.append((kind, tag, work))
     if _prof is None:

@@ -40,7 +40,7 @@ class _TransformerParams:
 
 class B200UNet(torch.nn.Module):
     def __init__(self, state_dict: Dict[str, torch.Tensor], config=None, device="cuda",
-                 trunk_dtype: torch.dtype = torch.float32, op_dtype: Optional[torch.dtype] = None):
+                 trunk_dtype: Optional[torch.dtype] = None, op_dtype: Optional[torch.dtype] = None):
         super().__init__()
         self.config = UNetConfig.from_any(config if config is not None else UNetConfig())
         cfg = self.config

@@ -26,7 +26,7 @@ class B200PostQuantConv(torch.nn.Module):
 
 class B200VAEDecoder(torch.nn.Module):
     def __init__(self, state_dict: Dict[str, torch.Tensor], config=None, device="cuda",
-                 trunk_dtype: torch.dtype = torch.float32, op_dtype=None, max_images_per_pass: int = 4):
+                 trunk_dtype=None, op_dtype=None, max_images_per_pass: int = 4):
         super().__init__()
         self.config = VAEConfig.from_any(config if config is not None else VAEConfig())
         cfg = self.config

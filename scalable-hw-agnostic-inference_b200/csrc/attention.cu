@@ -136,83 +136,104 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    // Warps 0 and 1 keep all 32 lanes in warp-uniform control flow and predicate only the asynchronous instructions
+    // on one elected lane; barrier probes are made uniform with a vote.  Issued from inside an `if (lane == 0)`
+    // region, every UMMA / TMA operand is thread-varying to the compiler and each instruction gets wrapped in an
+    // R2UR + ELECT + BRA.U.ANY waterfall loop: measured, ~700 scalar instructions per kv step at ~5 cycles each on
+    // the one issuing thread -- the whole kernel ran at the speed of that thread.
+    constexpr uint32_t FULL = 0xffffffffu;
     if (warp == 0) {
-        if (lane == 0) {
+        if (elect_one()) {
             mbar_expect_tx(q_full, (has_b ? 2 : 1) * ATT_TILE);
             tma_load_2d(sQ, &tmQ, q_full, head * ATT_D, b * p.sq + q0);
             if (has_b) tma_load_2d(sQ + ATT_TILE, &tmQ, q_full, head * ATT_D, b * p.sq + q0 + ATT_BM);
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int j = 0; j < n_tiles; ++j) {
-                mbar_wait(&kv_empty[stage], phase ^ 1);
-                uint8_t* sk = sKV + stage * 2 * ATT_TILE;
+        }
+        __syncwarp();
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int j = 0; j < n_tiles; ++j) {
+            mbar_wait(&kv_empty[stage], phase ^ 1);
+            uint8_t* sk = sKV + stage * 2 * ATT_TILE;
+            if (elect_one()) {
                 mbar_expect_tx(&kv_full[stage], 2 * ATT_TILE);
                 tma_load_2d(sk, &tmK, &kv_full[stage], head * ATT_D, b * p.skv + j * ATT_BN);
                 tma_load_2d(sk + ATT_TILE, &tmV, &kv_full[stage], head * ATT_D, b * p.skv + j * ATT_BN);
-                if (++stage == ATT_STAGES) stage = 0, phase ^= 1;
             }
+            __syncwarp();
+            if (++stage == ATT_STAGES) stage = 0, phase ^= 1;
         }
-        __syncwarp();
     } else if (warp == 1) {
-        if (lane == 0) {
-            constexpr uint32_t bf = F16 ? 0u : 1u;
-            constexpr uint32_t idesc_qk = umma_idesc(128, ATT_BN, bf, bf, 0, 0);
-            constexpr uint32_t idesc_pv = umma_idesc(128, ATT_D, bf, bf, 0, 1);  // A = P (TMEM, K-major), B = V MN-major
-            const int nq = has_b ? 2 : 1;
-            auto issue_qk = [&](int t, int stage) {
-                const uint32_t q_addr = smem_u32(sQ + t * ATT_TILE);
-                const uint32_t k_addr = smem_u32(sKV + stage * 2 * ATT_TILE);
-                const uint32_t d = tmem_base + ATT_TMEM_S + t * 128;
+        constexpr uint32_t bf = F16 ? 0u : 1u;
+        constexpr uint32_t idesc_qk = umma_idesc(128, ATT_BN, bf, bf, 0, 0);
+        constexpr uint32_t idesc_pv = umma_idesc(128, ATT_D, bf, bf, 0, 1);  // A = P (TMEM, K-major), B = V MN-major
+        const int nq = has_b ? 2 : 1;
+        const uint32_t tmem_u = __shfl_sync(FULL, tmem_base, 0);
+        const uint32_t q_u = __shfl_sync(FULL, smem_u32(sQ), 0);
+        const uint32_t kv_u = __shfl_sync(FULL, smem_u32(sKV), 0);
+        auto issue_qk = [&](int t, int stage) {
+            const uint32_t q_addr = q_u + t * ATT_TILE;
+            const uint32_t k_addr = kv_u + stage * 2 * ATT_TILE;
+            const uint32_t d = tmem_u + ATT_TMEM_S + t * 128;
+            if (elect_one()) {
 #pragma unroll
                 for (int ks = 0; ks < ATT_D / 16; ++ks)
                     umma_bf16(d, umma_desc_sw128(q_addr + ks * 32), umma_desc_sw128(k_addr + ks * 32), idesc_qk,
                               ks != 0);
                 umma_commit(&s_full[t]);
-            };
-            auto issue_pv = [&](int t, int j, int stage) {
-                const uint32_t v_addr = smem_u32(sKV + stage * 2 * ATT_TILE + ATT_TILE);
-                const uint32_t p_tmem = tmem_base + ATT_TMEM_P + t * 64;
+            }
+            __syncwarp();
+        };
+        auto issue_pv = [&](int t, int j, int stage) {
+            const uint32_t v_addr = kv_u + stage * 2 * ATT_TILE + ATT_TILE;
+            const uint32_t p_tmem = tmem_u + ATT_TMEM_P + t * 64;
+            const uint32_t o_tmem = tmem_u + ATT_TMEM_O + t * ATT_D;
+            if (elect_one()) {
 #pragma unroll
                 for (int ks = 0; ks < ATT_BN / 16; ++ks) {
                     // 16 K-elements of P = 8 TMEM columns (two 16-bit values per column); 16 kv rows of V = 2048 bytes
                     const uint64_t bdesc = umma_desc_sw128(v_addr + ks * 2048, /*lbo*/ 128 * 128, /*sbo*/ 1024);
-                    umma_ts(tmem_base + ATT_TMEM_O + t * ATT_D, p_tmem + ks * 8, bdesc, idesc_pv, (j | ks) != 0);
+                    umma_ts(o_tmem, p_tmem + ks * 8, bdesc, idesc_pv, (j | ks) != 0);
                 }
                 umma_commit(&pv_done[t]);
-            };
-            mbar_wait(q_full, 0);
-            tc_fence_after();
-            int next_qk[ATT_QT] = {0, 0}, next_pv[ATT_QT] = {0, 0};
-            int kv_ready = 0;  // kv tiles [0, kv_ready) have landed in shared memory
-            int released = 0;  // kv tiles [0, released) have been handed back to the producer
-            int pending = nq * n_tiles;
-            while (pending > 0) {
-                while (kv_ready < n_tiles &&
-                       mbar_test_wait(&kv_full[kv_ready % ATT_STAGES], (kv_ready / ATT_STAGES) & 1))
-                    ++kv_ready;
+            }
+            __syncwarp();
+        };
+        // Event-driven issue: the two Q tiles advance independently.  Whatever is ready goes next, P V first (the
+        // softmax group of that tile needs its completion before it may overwrite P), then the next Q K^T.
+        mbar_wait(q_full, 0);
+        tc_fence_after();
+        int next_qk[ATT_QT] = {0, 0}, next_pv[ATT_QT] = {0, 0};
+        int kv_ready = 0;  // kv tiles [0, kv_ready) have landed in shared memory
+        int released = 0;  // kv tiles [0, released) have been handed back to the producer
+        int pending = nq * n_tiles;
+        while (pending > 0) {
+            while (kv_ready < n_tiles &&
+                   __all_sync(FULL, mbar_test_wait(&kv_full[kv_ready % ATT_STAGES], (kv_ready / ATT_STAGES) & 1)))
+                ++kv_ready;
 #pragma unroll
-                for (int t = 0; t < ATT_QT; ++t) {
-                    if (t >= nq) continue;
-                    int j = next_pv[t];
-                    if (j < next_qk[t] && mbar_test_wait(&p_full[t], j & 1)) {
-                        tc_fence_after();
-                        issue_pv(t, j, j % ATT_STAGES);
-                        next_pv[t] = j + 1;
-                        --pending;
-                        int mn = next_pv[0];
-                        if (nq > 1 && next_pv[1] < mn) mn = next_pv[1];
-                        for (; released < mn; ++released) umma_commit(&kv_empty[released % ATT_STAGES]);
+            for (int t = 0; t < ATT_QT; ++t) {
+                if (t >= nq) continue;
+                int j = next_pv[t];
+                if (j < next_qk[t] && __all_sync(FULL, mbar_test_wait(&p_full[t], j & 1))) {
+                    tc_fence_after();
+                    issue_pv(t, j, j % ATT_STAGES);
+                    next_pv[t] = j + 1;
+                    --pending;
+                    int mn = next_pv[0];
+                    if (nq > 1 && next_pv[1] < mn) mn = next_pv[1];
+                    for (; released < mn; ++released) {
+                        if (elect_one()) umma_commit(&kv_empty[released % ATT_STAGES]);
+                        __syncwarp();
                     }
-                    j = next_qk[t];
-                    if (j < kv_ready && (j == 0 || mbar_test_wait(&s_free[t], (j - 1) & 1))) {
-                        tc_fence_after();
-                        issue_qk(t, j % ATT_STAGES);
-                        next_qk[t] = j + 1;
-                    }
+                }
+                j = next_qk[t];
+                if (j < kv_ready && (j == 0 || __all_sync(FULL, mbar_test_wait(&s_free[t], (j - 1) & 1)))) {
+                    tc_fence_after();
+                    issue_qk(t, j % ATT_STAGES);
+                    next_qk[t] = j + 1;
                 }
             }
         }
-        __syncwarp();
     } else {
         // ---------------------------------------------------------------- softmax + output
         // 8 warps per Q tile: tile t = (warp-2)/8; inside a tile warps 0..3 own score columns 0..63 of their 32 rows,

@@ -248,80 +248,87 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     const int total_work = p.m_tiles * p.n_tiles * splits;  // work item w = tile * splits + split
     const int num_kb = p.taps * p.kb_per_tap;
 
+    // Warps 0 and 1 keep all 32 lanes in the (warp-uniform) control flow and predicate only the asynchronous
+    // instructions on one elected lane.  Run from inside an `if (lane == 0)` region instead, every TMA / UMMA operand
+    // would count as thread-varying and the compiler would wrap each instruction in an R2UR + ELECT + BRA.U.ANY
+    // waterfall loop (measured in the attention kernel: ~5 cycles per scalar instruction on the single issuing
+    // thread, which made instruction ISSUE, not the tensor pipe, the limit).
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
-                const int t = w / splits, split = w - t * splits;
-                const int n_tile = t % p.n_tiles;
-                const int m_tile = t / p.n_tiles;
-                const int tx = m_tile % p.tiles_x;
-                const int ty = (m_tile / p.tiles_x) % p.tiles_y;
-                const int tn = m_tile / (p.tiles_x * p.tiles_y);
-                const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bn;
-                const int kb0 = (int)((long long)split * num_kb / splits);
-                const int kb1 = (int)((long long)(split + 1) * num_kb / splits);
-                for (int kb = kb0; kb < kb1; ++kb) {
-                    const int tap = kb / p.kb_per_tap;
-                    const int c0 = (kb - tap * p.kb_per_tap) * BLOCK_K;
-                    int dx = 0, dy = 0;
-                    if (p.taps == 9) {
-                        dy = tap / 3 - 1;
-                        dx = tap - (tap / 3) * 3 - 1;
-                    }
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
-                    uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
-                    uint8_t* sb = sa + A_TILE_BYTES;
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+            const int t = w / splits, split = w - t * splits;
+            const int n_tile = t % p.n_tiles;
+            const int m_tile = t / p.n_tiles;
+            const int tx = m_tile % p.tiles_x;
+            const int ty = (m_tile / p.tiles_x) % p.tiles_y;
+            const int tn = m_tile / (p.tiles_x * p.tiles_y);
+            const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bn;
+            const int kb0 = (int)((long long)split * num_kb / splits);
+            const int kb1 = (int)((long long)(split + 1) * num_kb / splits);
+            for (int kb = kb0; kb < kb1; ++kb) {
+                const int tap = kb / p.kb_per_tap;
+                const int c0 = (kb - tap * p.kb_per_tap) * BLOCK_K;
+                int dx = 0, dy = 0;
+                if (p.taps == 9) {
+                    dy = tap / 3 - 1;
+                    dx = tap - (tap / 3) * 3 - 1;
+                }
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+                uint8_t* sb = sa + A_TILE_BYTES;
+                if (elect_one()) {
                     mbar_expect_tx(&full_bar[stage], p.a_box_bytes + Cfg::B_TILE_BYTES);
                     tma_load_4d(sa, &tmA, &full_bar[stage], c0, x0 + dx, y0 + dy, n0);
                     tma_load_2d(sb, &tmB, &full_bar[stage], tap * p.cin + c0, n_tile * BLOCK_N);
-                    if (++stage == STAGES) {
-                        stage = 0;
-                        phase ^= 1;
-                    }
+                }
+                __syncwarp();
+                if (++stage == STAGES) {
+                    stage = 0;
+                    phase ^= 1;
                 }
             }
         }
-        __syncwarp();
     } else if (warp == 1) {
         // ------------------------------------------------------------------ UMMA issuer
-        if (lane == 0) {
-            const uint32_t idesc = umma_idesc(BLOCK_M, BLOCK_N, (uint32_t)p.a_bf16, (uint32_t)p.b_bf16);
-            int stage = 0;
-            uint32_t phase = 0;
-            int acc = 0;
-            uint32_t acc_phase = 0;
-            for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
-                const int split = w % splits;
-                const int nkb = (int)((long long)(split + 1) * num_kb / splits) - (int)((long long)split * num_kb / splits);
-                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        const uint32_t idesc = umma_idesc(BLOCK_M, BLOCK_N, (uint32_t)p.a_bf16, (uint32_t)p.b_bf16);
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+        const uint32_t smem_u = __shfl_sync(0xffffffffu, smem_u32(smem), 0);
+        int stage = 0;
+        uint32_t phase = 0;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+            const int split = w % splits;
+            const int nkb = (int)((long long)(split + 1) * num_kb / splits) - (int)((long long)split * num_kb / splits);
+            mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+            tc_fence_after();
+            const uint32_t d_tmem = tmem_u + acc * ACC_STRIDE;
+            for (int kb = 0; kb < nkb; ++kb) {
+                mbar_wait(&full_bar[stage], phase);
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + acc * ACC_STRIDE;
-                for (int kb = 0; kb < nkb; ++kb) {
-                    mbar_wait(&full_bar[stage], phase);
-                    tc_fence_after();
-                    const uint32_t a_addr = smem_u32(smem + stage * Cfg::STAGE_BYTES);
-                    const uint64_t adesc = umma_desc_sw128(a_addr);
-                    const uint64_t bdesc = umma_desc_sw128(a_addr + A_TILE_BYTES);
+                const uint32_t a_addr = smem_u + stage * Cfg::STAGE_BYTES;
+                const uint64_t adesc = umma_desc_sw128(a_addr);
+                const uint64_t bdesc = umma_desc_sw128(a_addr + A_TILE_BYTES);
+                if (elect_one()) {
 #pragma unroll
                     for (int k = 0; k < BLOCK_K / 16; ++k) {
                         // +32 bytes along K inside the 128-byte swizzle row = +2 in the (addr >> 4) field
                         umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
                     }
                     umma_commit(&empty_bar[stage]);
-                    if (++stage == STAGES) {
-                        stage = 0;
-                        phase ^= 1;
-                    }
+                    if (kb == nkb - 1) umma_commit(&tmem_full[acc]);
                 }
-                umma_commit(&tmem_full[acc]);
-                acc ^= 1;
-                if (acc == 0) acc_phase ^= 1;
+                __syncwarp();
+                if (++stage == STAGES) {
+                    stage = 0;
+                    phase ^= 1;
+                }
             }
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
         }
-        __syncwarp();
     } else {
         // ------------------------------------------------------------------ epilogue (warps 2..5)
         const int quad = warp & 3;  // TMEM lane quadrant this warp may read
