@@ -37,10 +37,12 @@ VAE_TFLOP = {64: 2.5145, 96: 5.7543, 128: 10.4704}    # per image
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10, help="timed passes of the hot path")
+    ap.add_argument("--steps", type=int, default=5, help="timed passes of the hot path")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=1, help="images per GPU per pass (BASELINE configs[1] = 1, configs[2] = 16)")
+    ap.add_argument("--batch", type=int, default=16,
+                    help="images per GPU per pass: 16 = BASELINE configs[2], the throughput-serving config the images/s "
+                         "metric at 1/2/4/8 GPUs is quoted on; 1 = configs[1], single-request latency")
     ap.add_argument("--denoise-steps", type=int, default=25)
     ap.add_argument("--size", type=int, default=768)
     ap.add_argument("--scheduler", default="ddim", choices=["ddim", "dpm++2m", "euler"])
@@ -347,6 +349,21 @@ def run_b200(args):
                     "ms_per_step": round(ms_e2e / args.steps, 3)},
             "gpu_launches": int(launches_per_pass * args.steps),
             "clocks": clk, "roofline": roofline}
+    if B != 1:
+        # BASELINE configs[1] beside the headline: one request at batch 1 through the same pipeline (own CUDA graph)
+        lat1 = lat_dev[:1].contiguous()
+        ctx1 = torch.cat([ctx2_dev[:1], ctx2_dev[B:B + 1]]).contiguous()
+        for _ in range(2):
+            pipe.decode(pipe.denoise(lat1, ctx1, args.denoise_steps), "uint8")
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            pipe.decode(pipe.denoise(lat1, ctx1, args.denoise_steps), "uint8")
+        e1.record()
+        torch.cuda.synchronize()
+        line["single_request"] = {"batch": 1, "ms_per_image": round(e0.elapsed_time(e1) / 3, 3),
+                                  "images_per_s": round(3000.0 / e0.elapsed_time(e1), 4)}
     if not args.no_cpu_baseline and world == 1:
         ips, info = cpu_oracle_sample(args.size, args.denoise_steps, n_unet=2)
         line["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": info["cores"], "kind": "port",
