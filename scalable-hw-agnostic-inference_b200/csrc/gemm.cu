@@ -21,7 +21,8 @@ constexpr int BLOCK_K = 64;
 constexpr int A_TILE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
 constexpr int ACC_STRIDE = 256;                      // TMEM columns between the two accumulator buffers
 constexpr int TMEM_COLS = 512;
-constexpr int GEMM_THREADS = 192;
+constexpr int EPI_WARPS = 8;  // two warps per TMEM lane quadrant, interleaved over the 32-column chunks
+constexpr int GEMM_THREADS = 64 + 32 * EPI_WARPS;
 constexpr int MAX_SPLITS = 8;
 constexpr int AUTO_SPLITS = 3;          // automatic K split factor (see plan_tiles)
 constexpr int AUTO_SPLIT_MIN_KB = 128;  // ... only for K >= 8192
@@ -49,6 +50,7 @@ struct GemmKernelParams {
     int out_dtype;
     long long ld_out;
     int geglu;
+    int fast_epi;  // 1: outputs leave through the per-warp staging tile as full 128-byte row segments
 };
 
 template <int BLOCK_N>
@@ -56,10 +58,33 @@ struct GemmCfg {
     static constexpr int B_TILE_BYTES = BLOCK_N * 128;
     static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
     static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+    // operand ring | barriers | per-tile column bias (2 x 256 fp32) | one 32x32 fp32 staging tile per epilogue warp.
+    // No alignment slack: the kernel traps if the dynamic segment is not 1024-byte aligned (it always is in practice:
+    // there is no static shared memory in front of it).
+    static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
+    static constexpr int BIAS_OFF = BAR_OFF + 256;
+    static constexpr int STG_OFF = BIAS_OFF + 2 * 256 * 4;
+    static constexpr int SMEM_BYTES = STG_OFF + EPI_WARPS * 4096;
+    static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
 
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+// x * Phi(x), the erf-form GELU.  Phi(-u) = 2^Q(u) with Q a degree-7 fit of log2 Phi(-u) on [0, 6] (|dQ| < 6e-6, so
+// Phi keeps ~4e-6 RELATIVE accuracy in the negative tail, where 0.5 * (1 + erff) cancels); Phi(u) = 1 - Phi(-u).
+// 14 instructions per value instead of erff's 34: the GEGLU epilogue is instruction-bound.
+__device__ __forceinline__ float gelu_erf(float x) {
+    const float u = fminf(fabsf(x), 6.0f);
+    float q = -1.889626233e-06f;
+    q = fmaf(q, u, 6.268140101e-05f);
+    q = fmaf(q, u, -9.388679333e-04f);
+    q = fmaf(q, u, 8.539461332e-03f);
+    q = fmaf(q, u, -5.402068712e-02f);
+    q = fmaf(q, u, -4.584097768e-01f);
+    q = fmaf(q, u, -1.151269147e+00f);
+    q = fmaf(q, u, -9.999943403e-01f);
+    float e;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(q));
+    return x * (x < 0.f ? e : 1.0f - e);
+}
 
 // Applies the epilogue to 32 consecutive output columns [col0, col0+32) of one row and stores them.
 __device__ __forceinline__ void epilogue_store32(const GemmKernelParams& p, float (&v)[32], long long m, int img,
@@ -124,48 +149,91 @@ __device__ __forceinline__ void epilogue_store32(const GemmKernelParams& p, floa
     }
 }
 
-// ---- the same epilogue split into request / consume halves, for full 32-column chunks only -------------------
-__device__ __forceinline__ void res_prefetch32(const GemmKernelParams& p, long long m, int col0, uint4 (&buf)[8]) {
-    if (p.res_dtype == B200SD_F32) {
-        const uint4* r = reinterpret_cast<const uint4*>(static_cast<const float*>(p.residual) + m * p.ld_res + col0);
+// ---- staged epilogue -------------------------------------------------------------------------------------------
+// tcgen05.ld hands every thread one accumulator ROW, so direct stores touch 32 different 128-byte lines per
+// instruction (32 L1 wavefronts; measured: the fp32-residual linears ran at 65% LSU wavefront utilisation and 3 TB/s).
+// Each epilogue warp therefore owns a 32x32 fp32 staging tile: rows are written as they come from TMEM (16-byte
+// chunks XOR-swizzled by row, conflict-free), and read back transposed so that 8 (fp32) or 4 (16-bit) neighbouring
+// lanes cover one row's 128 / 64 contiguous bytes.  Residual loads use the same mapping.
+__device__ __forceinline__ void stage_rows(float* stg, int lane, const float (&v)[32]) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) buf[j] = r[j];
-    } else {
-        const uint4* r = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.residual) + m * p.ld_res + col0);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) buf[j] = r[j];
-    }
+    for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<float4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) =
+            make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
 }
-__device__ __forceinline__ void res_add32(const GemmKernelParams& p, float (&v)[32], const uint4 (&buf)[8]) {
-    if (p.res_dtype == B200SD_F32) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            v[4 * j + 0] += __uint_as_float(buf[j].x), v[4 * j + 1] += __uint_as_float(buf[j].y);
-            v[4 * j + 2] += __uint_as_float(buf[j].z), v[4 * j + 3] += __uint_as_float(buf[j].w);
-        }
-    } else {
-        const bool f16 = p.res_dtype == B200SD_F16;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            v[8 * j + 0] += h_lo(buf[j].x, f16), v[8 * j + 1] += h_hi(buf[j].x, f16);
-            v[8 * j + 2] += h_lo(buf[j].y, f16), v[8 * j + 3] += h_hi(buf[j].y, f16);
-            v[8 * j + 4] += h_lo(buf[j].z, f16), v[8 * j + 5] += h_hi(buf[j].z, f16);
-            v[8 * j + 6] += h_lo(buf[j].w, f16), v[8 * j + 7] += h_hi(buf[j].w, f16);
-        }
-    }
+__device__ __forceinline__ float4 stage_read(const float* stg, int row, int chunk) {
+    return *reinterpret_cast<const float4*>(stg + row * 32 + ((chunk ^ (row & 7)) << 2));
 }
-__device__ __forceinline__ void store32_full(const GemmKernelParams& p, const float (&v)[32], long long m, int col0) {
+// Transposed lane mapping.  fp32 outputs: 8 passes, row = 4*i + lane/8, columns 4*(lane%8)..+3.
+//                            16-bit outputs: 4 passes, row = 8*i + lane/4, columns 8*(lane%4)..+7.
+__device__ __forceinline__ void res_request(const GemmKernelParams& p, const int (&mt)[8], uint32_t vmask, int lane,
+                                            int col0, uint4 (&buf)[8]) {
     if (p.out_dtype == B200SD_F32) {
-        float4* o = reinterpret_cast<float4*>(static_cast<float*>(p.out) + m * p.ld_out + col0);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        for (int i = 0; i < 8; ++i) {
+            const int row = 4 * i + (lane >> 3);
+            buf[i] = make_uint4(0, 0, 0, 0);
+            if ((vmask >> row) & 1)
+                buf[i] = *reinterpret_cast<const uint4*>(static_cast<const float*>(p.residual) +
+                                                         (long long)mt[i] * p.ld_res + col0 + 4 * (lane & 7));
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int row = 8 * i + (lane >> 2);
+            buf[i] = make_uint4(0, 0, 0, 0);
+            if ((vmask >> row) & 1)
+                buf[i] = *reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.residual) +
+                                                         (long long)mt[i] * p.ld_res + col0 + 8 * (lane & 3));
+        }
+    }
+}
+// Reads the staged chunk back transposed, adds the column bias (`bs` = this chunk's 32 bias values in shared memory,
+// or nullptr) and the requested residual (`use_res`), converts and stores full row segments.
+__device__ __forceinline__ void staged_store(const GemmKernelParams& p, const float* stg, const int (&mt)[8],
+                                             uint32_t vmask, int lane, int col0, const float* bs, bool use_res,
+                                             const uint4 (&buf)[8]) {
+    if (p.out_dtype == B200SD_F32) {
+        const int cg = lane & 7;
+        float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (bs) b = *reinterpret_cast<const float4*>(bs + 4 * cg);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int row = 4 * i + (lane >> 3);
+            float4 a = stage_read(stg, row, cg);
+            a.x += b.x, a.y += b.y, a.z += b.z, a.w += b.w;
+            if (use_res) {
+                a.x += __uint_as_float(buf[i].x), a.y += __uint_as_float(buf[i].y);
+                a.z += __uint_as_float(buf[i].z), a.w += __uint_as_float(buf[i].w);
+            }
+            if ((vmask >> row) & 1)
+                *reinterpret_cast<float4*>(static_cast<float*>(p.out) + (long long)mt[i] * p.ld_out + col0 + 4 * cg) = a;
+        }
     } else {
         const bool f16 = p.out_dtype == B200SD_F16;
-        uint4* o = reinterpret_cast<uint4*>(static_cast<uint16_t*>(p.out) + m * p.ld_out + col0);
+        const int cg = lane & 3;
+        float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
+        if (bs) {
+            b0 = *reinterpret_cast<const float4*>(bs + 8 * cg);
+            b1 = *reinterpret_cast<const float4*>(bs + 8 * cg + 4);
+        }
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-            o[j] = make_uint4(pack_h2(v[8 * j], v[8 * j + 1], f16), pack_h2(v[8 * j + 2], v[8 * j + 3], f16),
-                              pack_h2(v[8 * j + 4], v[8 * j + 5], f16), pack_h2(v[8 * j + 6], v[8 * j + 7], f16));
+        for (int i = 0; i < 4; ++i) {
+            const int row = 8 * i + (lane >> 2);
+            float4 a0 = stage_read(stg, row, 2 * cg), a1 = stage_read(stg, row, 2 * cg + 1);
+            a0.x += b0.x, a0.y += b0.y, a0.z += b0.z, a0.w += b0.w;
+            a1.x += b1.x, a1.y += b1.y, a1.z += b1.z, a1.w += b1.w;
+            if (use_res) {
+                a0.x += h_lo(buf[i].x, f16), a0.y += h_hi(buf[i].x, f16);
+                a0.z += h_lo(buf[i].y, f16), a0.w += h_hi(buf[i].y, f16);
+                a1.x += h_lo(buf[i].z, f16), a1.y += h_hi(buf[i].z, f16);
+                a1.z += h_lo(buf[i].w, f16), a1.w += h_hi(buf[i].w, f16);
+            }
+            if ((vmask >> row) & 1)
+                *reinterpret_cast<uint4*>(static_cast<uint16_t*>(p.out) + (long long)mt[i] * p.ld_out + col0 + 8 * cg) =
+                    make_uint4(pack_h2(a0.x, a0.y, f16), pack_h2(a0.z, a0.w, f16), pack_h2(a1.x, a1.y, f16),
+                               pack_h2(a1.z, a1.w, f16));
+        }
     }
 }
 
@@ -209,11 +277,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                 const GemmKernelParams p) {
     using Cfg = GemmCfg<BLOCK_N>;
     constexpr int STAGES = Cfg::STAGES;
-    extern __shared__ uint8_t smem_raw[];
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
     // SWIZZLE_128B tiles need 1024-byte alignment in the shared address space
-    const uint32_t raw_addr = smem_u32(smem_raw);
-    uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+    uint8_t* smem = smem_raw;
+    if (smem_u32(smem_raw) & 1023u) __trap();
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::BAR_OFF);
+    float* bias_s = reinterpret_cast<float*>(smem + Cfg::BIAS_OFF);
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* tmem_full = empty_bar + STAGES;
     uint64_t* tmem_empty = tmem_full + 2;
@@ -234,7 +303,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(&tmem_full[s], 1);
-            mbar_init(&tmem_empty[s], 4);
+            mbar_init(&tmem_empty[s], EPI_WARPS);
         }
         fence_barrier_init();
     }
@@ -257,6 +326,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         // ------------------------------------------------------------------ TMA producer
         int stage = 0;
         uint32_t phase = 0;
+        const int res_esz = p.res_dtype == B200SD_F32 ? 4 : 2;
+        const bool res_l2_prefetch =
+            p.residual != nullptr && splits == 1 && !p.geglu &&
+            ((reinterpret_cast<uintptr_t>(p.residual) | (uintptr_t)(p.ld_res * res_esz)) & 15) == 0;
         for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
             const int t = w / splits, split = w - t * splits;
             const int n_tile = t % p.n_tiles;
@@ -267,6 +340,28 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
             const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bn;
             const int kb0 = (int)((long long)split * num_kb / splits);
             const int kb1 = (int)((long long)(split + 1) * num_kb / splits);
+            if (res_l2_prefetch) {
+                // The residual rows of this tile are asked into L2 now, a pipeline depth ahead of the epilogue that
+                // adds them: its row-per-thread loads then see L2 latency instead of HBM latency.
+                const int colb = n_tile * BLOCK_N;
+                const int ncol = (p.n_cols - colb) < BLOCK_N ? (p.n_cols - colb) : BLOCK_N;
+                const uint32_t bytes = (uint32_t)(ncol * res_esz);
+                if ((bytes & 15u) == 0) {
+                    const int box_pix = p.bw * p.bh;
+                    for (int r = lane; r < BLOCK_M; r += 32) {
+                        const int ln = r / box_pix;
+                        const int rem = r - ln * box_pix;
+                        const int ly = rem / p.bw;
+                        const int img = n0 + ln, y = y0 + ly, x = x0 + (rem - ly * p.bw);
+                        if (ln < p.bn && img < p.n_img && y < p.img_h && x < p.img_w) {
+                            const long long m = ((long long)img * p.img_h + y) * p.img_w + x;
+                            l2_prefetch_bulk(static_cast<const uint8_t*>(p.residual) +
+                                                 (m * p.ld_res + colb) * (long long)res_esz, bytes);
+                        }
+                    }
+                }
+                __syncwarp();
+            }
             for (int kb = kb0; kb < kb1; ++kb) {
                 const int tap = kb / p.kb_per_tap;
                 const int c0 = (kb - tap * p.kb_per_tap) * BLOCK_K;
@@ -330,14 +425,21 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
             if (acc == 0) acc_phase ^= 1;
         }
     } else {
-        // ------------------------------------------------------------------ epilogue (warps 2..5)
+        // ------------------------------------------------------------------ epilogue (warps 2..9)
+        // The epilogue is bound by bytes in flight (residual reads) or by ALU work (GEGLU), not by TMEM bandwidth, so
+        // two warps share each lane quadrant: warp group `eg` takes the 32-column chunks c = eg, eg + 2, ...
         const int quad = warp & 3;  // TMEM lane quadrant this warp may read
+        const int eg = (warp - 2) >> 2;
+        const int et = threadIdx.x - 64;  // 0..255 over the epilogue warps
+        float* stg = reinterpret_cast<float*>(smem + Cfg::STG_OFF) + (warp - 2) * 1024;
+        const bool out32 = p.out_dtype == B200SD_F32;
+        const bool fast = p.fast_epi != 0;
         const int row_in_tile = quad * 32 + lane;
         const int box_pix = p.bw * p.bh;
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
-            const int t = w / splits, split = w - t * splits;
+            const int t = w / splits;
             const int n_tile = t % p.n_tiles;
             const int m_tile = t / p.n_tiles;
             const int tx = m_tile % p.tiles_x;
@@ -353,6 +455,25 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
             const bool valid = (ln < p.bn) && (img < p.n_img) && (y < p.img_h) && (x < p.img_w);
             const long long m = ((long long)img * p.img_h + y) * p.img_w + x;
 
+            // column bias of this tile -> shared memory (read back as broadcasts); double-buffered with the accumulator
+            float* bs = bias_s + acc * 256;
+            if (et < BLOCK_N) {
+                const int col = n_tile * BLOCK_N + et;
+                bs[et] = (p.bias != nullptr && !p.bias_along_m && col < p.n_out) ? __ldg(p.bias + col) : 0.f;
+            }
+            // rows this lane handles in the transposed (staged) mapping
+            const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+            int mt[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                mt[i] = __shfl_sync(0xffffffffu, (int)m, out32 ? 4 * i + (lane >> 3) : 8 * (i & 3) + (lane >> 2));
+            const int colbase = n_tile * BLOCK_N;
+            const bool use_res = fast && p.residual != nullptr;
+            uint4 rbuf[2][8];
+            if (use_res && splits == 1 && colbase + eg * 32 + 32 <= p.n_cols)
+                res_request(p, mt, vmask, lane, colbase + eg * 32, rbuf[0]);
+            named_bar_sync(2, 32 * EPI_WARPS);  // bias tile complete
+
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
             const uint32_t t_addr = tmem_base + acc * ACC_STRIDE + ((uint32_t)(quad * 32) << 16);
@@ -360,7 +481,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                 // ---- split-K: park the partial tile, release TMEM, elect the last-arriving split to finish the tile
                 float* mine = p.partials + ((size_t)w * BLOCK_M + row_in_tile) * BLOCK_N;
 #pragma unroll 1
-                for (int c = 0; c < BLOCK_N / 32; ++c) {
+                for (int c = eg; c < BLOCK_N / 32; c += 2) {
                     uint32_t r[32];
                     tmem_ld_x32(t_addr + c * 32, r);
                     tmem_ld_wait();
@@ -373,8 +494,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&tmem_empty[acc]);
-                named_bar_sync(1, 128);  // all 128 rows of the partial tile are written ...
-                if (row_in_tile == 0) {
+                named_bar_sync(1, 32 * EPI_WARPS);  // all 128 rows of the partial tile are written ...
+                if (row_in_tile == 0 && eg == 0) {
                     __threadfence();     // ... and (fence cumulativity) visible device-wide before the count goes up
                     const int old = atomicAdd(p.counters + t, 1);
                     const int last = (old == splits - 1);
@@ -384,13 +505,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                     }
                     *last_flag = last;
                 }
-                named_bar_sync(1, 128);
+                named_bar_sync(1, 32 * EPI_WARPS);
                 const bool last = *last_flag != 0;
-                named_bar_sync(1, 128);  // everyone has read the flag before the next work item rewrites it
+                named_bar_sync(1, 32 * EPI_WARPS);  // everyone has read the flag before the next work item rewrites it
                 if (last) {
                     const float* base = p.partials + ((size_t)t * splits * BLOCK_M + row_in_tile) * BLOCK_N;
 #pragma unroll 1
-                    for (int c = 0; c < BLOCK_N / 32; ++c) {
+                    for (int c = eg; c < BLOCK_N / 32; c += 2) {
                         const int col0 = n_tile * BLOCK_N + c * 32;
                         if (valid && col0 < p.n_cols) {
                             float v[32];
@@ -412,50 +533,61 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                 }
             } else {
                 if (!p.geglu) {
-                    // The residual of chunk c+1 is requested before chunk c is finished: with one row per thread the
-                    // epilogue is latency-bound, so bytes in flight per SM are what set its speed.
                     constexpr int NC = BLOCK_N / 32;
-                    const int colbase = n_tile * BLOCK_N;
-                    const bool pre = valid && p.residual != nullptr;
-                    uint4 rbuf[2][8];
-                    if (pre && colbase + 32 <= p.n_cols) res_prefetch32(p, m, colbase, rbuf[0]);
+                    constexpr int NI = (NC + 1) / 2;  // chunks per warp group (the last one may be absent for eg = 1)
 #pragma unroll
-                    for (int c = 0; c < NC; ++c) {
-                        const int col0 = colbase + c * 32;
-                        if (c + 1 < NC && pre && col0 + 64 <= p.n_cols) res_prefetch32(p, m, col0 + 32, rbuf[(c + 1) & 1]);
-                        uint32_t r[32];
-                        tmem_ld_x32(t_addr + c * 32, r);
-                        tmem_ld_wait();
-                        if (valid && col0 < p.n_cols) {
-                            float v[32];
+                    for (int i = 0; i < NI; ++i) {
+                        const int c = 2 * i + eg;
+                        if (c < NC) {
+                            const int col0 = colbase + c * 32;
+                            // the residual of this warp's next chunk is requested before this one is finished
+                            if (i + 1 < NI && c + 2 < NC && use_res && col0 + 96 <= p.n_cols)
+                                res_request(p, mt, vmask, lane, col0 + 64, rbuf[(i + 1) & 1]);
+                            uint32_t r[32];
+                            tmem_ld_x32(t_addr + c * 32, r);
+                            tmem_ld_wait();
+                            if (col0 < p.n_cols) {
+                                float v[32];
 #pragma unroll
-                            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                            add_col_bias32(p, v, m, img, col0);
-                            if (col0 + 32 <= p.n_cols) {
-                                if (pre) res_add32(p, v, rbuf[c & 1]);
-                                store32_full(p, v, m, col0);
-                            } else {
-                                epilogue_store32(p, v, m, img, col0);  // ragged last chunk: element-wise path
+                                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                                if (fast && col0 + 32 <= p.n_cols) {
+                                    stage_rows(stg, lane, v);
+                                    __syncwarp();
+                                    staged_store(p, stg, mt, vmask, lane, col0, bs + c * 32, use_res, rbuf[i & 1]);
+                                    __syncwarp();
+                                } else if (valid) {  // ragged last chunk, row bias, bias along M, mixed widths
+                                    add_col_bias32(p, v, m, img, col0);
+                                    epilogue_store32(p, v, m, img, col0);
+                                }
                             }
                         }
                     }
                 } else {
                     constexpr int HALF = BLOCK_N / 2;
 #pragma unroll 1
-                    for (int c = 0; c < HALF / 32; ++c) {
+                    for (int c = eg; c < HALF / 32; c += 2) {
                         uint32_t rv[32], rg[32];
                         tmem_ld_x32(t_addr + c * 32, rv);
                         tmem_ld_x32(t_addr + HALF + c * 32, rg);
                         tmem_ld_wait();
-                        if (valid) {
-                            float v[32], g[32];
+                        float v[32];
 #pragma unroll
-                            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(rv[j]), g[j] = __uint_as_float(rg[j]);
-                            add_col_bias32(p, v, m, img, n_tile * BLOCK_N + c * 32);
-                            add_col_bias32(p, g, m, img, n_tile * BLOCK_N + HALF + c * 32);
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) v[j] *= gelu_erf(g[j]);
-                            epilogue_store32(p, v, m, img, n_tile * HALF + c * 32);
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 bv = *reinterpret_cast<const float4*>(bs + c * 32 + 4 * j);
+                            const float4 bg = *reinterpret_cast<const float4*>(bs + HALF + c * 32 + 4 * j);
+                            v[4 * j + 0] = (__uint_as_float(rv[4 * j + 0]) + bv.x) * gelu_erf(__uint_as_float(rg[4 * j + 0]) + bg.x);
+                            v[4 * j + 1] = (__uint_as_float(rv[4 * j + 1]) + bv.y) * gelu_erf(__uint_as_float(rg[4 * j + 1]) + bg.y);
+                            v[4 * j + 2] = (__uint_as_float(rv[4 * j + 2]) + bv.z) * gelu_erf(__uint_as_float(rg[4 * j + 2]) + bg.z);
+                            v[4 * j + 3] = (__uint_as_float(rv[4 * j + 3]) + bv.w) * gelu_erf(__uint_as_float(rg[4 * j + 3]) + bg.w);
+                        }
+                        const int col0 = n_tile * HALF + c * 32;
+                        if (fast) {
+                            stage_rows(stg, lane, v);
+                            __syncwarp();
+                            staged_store(p, stg, mt, vmask, lane, col0, nullptr, false, rbuf[0]);
+                            __syncwarp();
+                        } else if (valid) {
+                            epilogue_store32(p, v, m, img, col0);
                         }
                     }
                 }
@@ -687,6 +819,12 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
     kp.row_bias = p->row_bias, kp.row_bias_stride = p->row_bias_stride;
     kp.residual = p->residual, kp.res_dtype = p->residual_dtype, kp.ld_res = p->ld_res;
     kp.out = p->out, kp.out_dtype = p->out_dtype, kp.ld_out = p->ld_out;
+    {
+        // staged (transposed) epilogue: column bias only, residual of the output's dtype; 16-byte alignment
+        // of out / residual rows was checked above for n_cols >= 32
+        const bool res_ok = !p->residual || p->residual_dtype == p->out_dtype;
+        kp.fast_epi = (n_cols >= 32 && !p->bias_along_m && !p->row_bias && res_ok) ? 1 : 0;
+    }
     if (kp.splits > 1) {
         const long long tiles = (long long)kp.m_tiles * kp.n_tiles;
         kp.counters = static_cast<int*>(p->workspace);
