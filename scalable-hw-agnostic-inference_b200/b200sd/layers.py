@@ -75,7 +75,7 @@ class Kernels:
     def gn_workspace(self, n_img: int, hw: int, groups: int) -> torch.Tensor:
         need = ops.groupnorm_workspace_bytes(n_img, hw, groups)
         if self._gn_ws is None or self._gn_ws.numel() * 4 < need:
-            self._gn_ws = torch.empty(max(need // 4, 1 << 16), device=self.device, dtype=torch.float32)
+            self._gn_ws = torch.empty(max(need // 4, 1 << 18), device=self.device, dtype=torch.float32)
         return self._gn_ws
 
     def groupnorm(self, x1: torch.Tensor, x2: Optional[torch.Tensor], gamma, beta, eps: float, silu: bool,
