@@ -40,6 +40,7 @@ struct AttnKernelParams {
     float scale_log2;  // scale * log2(e)
     uint16_t* out;
     long long ld_out;
+    int stagger;  // 1: Q tile B starts half a softmax period behind tile A (see the UMMA warp)
 };
 
 __device__ __forceinline__ float ex2_ftz(float x) {
@@ -106,7 +107,8 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
     uint64_t* s_free = s_full + ATT_QT;        // [QT] softmax -> UMMA : S tile copied to registers
     uint64_t* p_full = s_free + ATT_QT;        // [QT] softmax -> UMMA : P tile in TMEM (and O rescaled)
     uint64_t* pv_done = p_full + ATT_QT;       // [QT] UMMA -> softmax : O += P V finished
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + ATT_QT);
+    uint64_t* b_go = pv_done + ATT_QT;         // softmax(A) -> UMMA : tile A entered its first exponential phase
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(b_go + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q0 = blockIdx.x * (ATT_BM * ATT_QT);
@@ -128,6 +130,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
             mbar_init(&p_full[t], 8);
             mbar_init(&pv_done[t], 1);
         }
+        mbar_init(b_go, 8);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_slot, 512);
@@ -227,7 +230,14 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                     }
                 }
                 j = next_qk[t];
-                if (j < kv_ready && (j == 0 || __all_sync(FULL, mbar_test_wait(&s_free[t], (j - 1) & 1)))) {
+                // The softmax groups of the two tiles alternate between a MUFU-bound phase (exponentials) and a phase
+                // that does not touch the MUFU (TMEM loads, row max, exchange, P store).  Started together they stay in
+                // step and fight over the MUFU, then leave it idle together; tile B's first Q K^T therefore waits until
+                // tile A has entered its first exponential phase, and the offset persists (the loops are self-paced).
+                bool go = j < kv_ready;
+                if (go && j == 0) go = (t == 0 || !p.stagger) || __all_sync(FULL, mbar_test_wait(b_go, 0));
+                else if (go) go = __all_sync(FULL, mbar_test_wait(&s_free[t], (j - 1) & 1));
+                if (go) {
                     tc_fence_after();
                     issue_qk(t, j % ATT_STAGES);
                     next_qk[t] = j + 1;
@@ -282,6 +292,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                 float* xch = xchg + ((j & 1) * ATT_QT + t) * 256;
                 xch[half * 128 + row] = fmaxf(mx0, mx1);
                 named_bar_sync(2 + t, 256);
+                if (t == 0 && j == 0 && lane == 0) mbar_arrive(b_go);
                 const float m_new = fmaxf(xch[row], xch[128 + row]) * sc;
                 float alpha = 1.f;
                 bool need = false;
@@ -384,6 +395,15 @@ static int32_t launch_attention(const CUtensorMap& tmQ, const CUtensorMap& tmK, 
     return B200SD_OK;
 }
 
+static int stagger_from_env() {
+    static int cached = -1;
+    if (cached < 0) {
+        const char* e = getenv("B200SD_ATTN_STAGGER");
+        cached = (e && e[0] == '0') ? 0 : 1;
+    }
+    return cached;
+}
+
 static int emu_mask_from_env() {
     static int cached = -1;
     if (cached < 0) {
@@ -432,6 +452,7 @@ extern "C" int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_str
     kp.scale_log2 = p->scale * 1.4426950408889634f;
     kp.out = static_cast<uint16_t*>(p->out);
     kp.ld_out = p->ld_out;
+    kp.stagger = stagger_from_env();
     const int rows_per_cta = ATT_BM * ATT_QT;
     dim3 grid((p->sq + rows_per_cta - 1) / rows_per_cta, p->heads, p->batch);
     cudaStream_t s = as_stream(stream);

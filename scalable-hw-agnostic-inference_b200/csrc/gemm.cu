@@ -436,6 +436,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         const bool fast = p.fast_epi != 0;
         const int row_in_tile = quad * 32 + lane;
         const int box_pix = p.bw * p.bh;
+        // position of this thread's accumulator row inside the pixel box (the same for every tile)
+        const int ln = row_in_tile / box_pix;
+        const int ly = (row_in_tile - ln * box_pix) / p.bw;
+        const int lx = row_in_tile - ln * box_pix - ly * p.bw;
+        // the column bias of a tile is fetched one tile ahead (one value per epilogue thread)
+        const bool col_bias = p.bias != nullptr && !p.bias_along_m;
+        auto bias_fetch = [&](int w) -> float {
+            const int col = ((w / splits) % p.n_tiles) * BLOCK_N + et;
+            return (col_bias && et < BLOCK_N && w < total_work && col < p.n_out) ? __ldg(p.bias + col) : 0.f;
+        };
+        float bias_cur = bias_fetch(blockIdx.x);
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
@@ -445,10 +456,6 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
             const int tx = m_tile % p.tiles_x;
             const int ty = (m_tile / p.tiles_x) % p.tiles_y;
             const int tn = m_tile / (p.tiles_x * p.tiles_y);
-            const int ln = row_in_tile / box_pix;
-            const int rem = row_in_tile - ln * box_pix;
-            const int ly = rem / p.bw;
-            const int lx = rem - ly * p.bw;
             const int img = tn * p.bn + ln;
             const int y = ty * p.bh + ly;
             const int x = tx * p.bw + lx;
@@ -457,10 +464,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 
             // column bias of this tile -> shared memory (read back as broadcasts); double-buffered with the accumulator
             float* bs = bias_s + acc * 256;
-            if (et < BLOCK_N) {
-                const int col = n_tile * BLOCK_N + et;
-                bs[et] = (p.bias != nullptr && !p.bias_along_m && col < p.n_out) ? __ldg(p.bias + col) : 0.f;
-            }
+            if (et < BLOCK_N) bs[et] = bias_cur;
+            bias_cur = bias_fetch(w + gridDim.x);
             // rows this lane handles in the transposed (staged) mapping
             const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
             int mt[8];
@@ -469,9 +474,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                 mt[i] = __shfl_sync(0xffffffffu, (int)m, out32 ? 4 * i + (lane >> 3) : 8 * (i & 3) + (lane >> 2));
             const int colbase = n_tile * BLOCK_N;
             const bool use_res = fast && p.residual != nullptr;
-            uint4 rbuf[2][8];
+            uint4 rbuf[8];
             if (use_res && splits == 1 && colbase + eg * 32 + 32 <= p.n_cols)
-                res_request(p, mt, vmask, lane, colbase + eg * 32, rbuf[0]);
+                res_request(p, mt, vmask, lane, colbase + eg * 32, rbuf);
             named_bar_sync(2, 32 * EPI_WARPS);  // bias tile complete
 
             mbar_wait(&tmem_full[acc], acc_phase);
@@ -532,43 +537,60 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                     }
                 }
             } else {
+                // Chunk loops are NOT unrolled: the kernel's code size (instruction-cache misses were 11% of the
+                // epilogue's stall samples) matters more than the loop overhead.  The TMEM load of a warp's next chunk
+                // is issued as soon as the registers of the current one are staged, and the accumulator buffer is
+                // handed back to the UMMA warp right after the last load, before the last stores.
                 if (!p.geglu) {
                     constexpr int NC = BLOCK_N / 32;
-                    constexpr int NI = (NC + 1) / 2;  // chunks per warp group (the last one may be absent for eg = 1)
+                    uint32_t r[32];
+                    if (eg < NC) tmem_ld_x32(t_addr + eg * 32, r);
+#pragma unroll 1
+                    for (int c = eg; c < NC; c += 2) {
+                        const int col0 = colbase + c * 32;
+                        const bool more = c + 2 < NC;
+                        tmem_ld_wait();
+                        const bool full = fast && col0 + 32 <= p.n_cols;
+                        if (full) {
+                            float v[32];
 #pragma unroll
-                    for (int i = 0; i < NI; ++i) {
-                        const int c = 2 * i + eg;
-                        if (c < NC) {
-                            const int col0 = colbase + c * 32;
-                            // the residual of this warp's next chunk is requested before this one is finished
-                            if (i + 1 < NI && c + 2 < NC && use_res && col0 + 96 <= p.n_cols)
-                                res_request(p, mt, vmask, lane, col0 + 64, rbuf[(i + 1) & 1]);
-                            uint32_t r[32];
-                            tmem_ld_x32(t_addr + c * 32, r);
-                            tmem_ld_wait();
-                            if (col0 < p.n_cols) {
-                                float v[32];
+                            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                            stage_rows(stg, lane, v);
+                        } else if (valid && col0 < p.n_cols) {  // ragged last chunk, row bias, bias along M, mixed dtypes
+                            float v[32];
 #pragma unroll
-                                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                                if (fast && col0 + 32 <= p.n_cols) {
-                                    stage_rows(stg, lane, v);
-                                    __syncwarp();
-                                    staged_store(p, stg, mt, vmask, lane, col0, bs + c * 32, use_res, rbuf[i & 1]);
-                                    __syncwarp();
-                                } else if (valid) {  // ragged last chunk, row bias, bias along M, mixed widths
-                                    add_col_bias32(p, v, m, img, col0);
-                                    epilogue_store32(p, v, m, img, col0);
-                                }
-                            }
+                            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                            add_col_bias32(p, v, m, img, col0);
+                            epilogue_store32(p, v, m, img, col0);
                         }
+                        if (more) {
+                            tmem_ld_x32(t_addr + (c + 2) * 32, r);
+                        } else {
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+                        }
+                        __syncwarp();
+                        if (full) {
+                            staged_store(p, stg, mt, vmask, lane, col0, bs + c * 32, use_res, rbuf);
+                            if (more && use_res && col0 + 96 <= p.n_cols)
+                                res_request(p, mt, vmask, lane, col0 + 64, rbuf);
+                            __syncwarp();
+                        }
+                    }
+                    if (eg >= NC) {  // BLOCK_N = 32 * odd: the second warp group may have no chunk at all
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
                     }
                 } else {
                     constexpr int HALF = BLOCK_N / 2;
+                    uint32_t rv[32], rg[32];
+                    tmem_ld_x32(t_addr + eg * 32, rv);
+                    tmem_ld_x32(t_addr + HALF + eg * 32, rg);
 #pragma unroll 1
                     for (int c = eg; c < HALF / 32; c += 2) {
-                        uint32_t rv[32], rg[32];
-                        tmem_ld_x32(t_addr + c * 32, rv);
-                        tmem_ld_x32(t_addr + HALF + c * 32, rg);
+                        const bool more = c + 2 < HALF / 32;
                         tmem_ld_wait();
                         float v[32];
 #pragma unroll
@@ -580,20 +602,25 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                             v[4 * j + 2] = (__uint_as_float(rv[4 * j + 2]) + bv.z) * gelu_erf(__uint_as_float(rg[4 * j + 2]) + bg.z);
                             v[4 * j + 3] = (__uint_as_float(rv[4 * j + 3]) + bv.w) * gelu_erf(__uint_as_float(rg[4 * j + 3]) + bg.w);
                         }
+                        if (more) {
+                            tmem_ld_x32(t_addr + (c + 2) * 32, rv);
+                            tmem_ld_x32(t_addr + HALF + (c + 2) * 32, rg);
+                        } else {
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+                        }
                         const int col0 = n_tile * HALF + c * 32;
                         if (fast) {
                             stage_rows(stg, lane, v);
                             __syncwarp();
-                            staged_store(p, stg, mt, vmask, lane, col0, nullptr, false, rbuf[0]);
+                            staged_store(p, stg, mt, vmask, lane, col0, nullptr, false, rbuf);
                             __syncwarp();
                         } else if (valid) {
                             epilogue_store32(p, v, m, img, col0);
                         }
                     }
                 }
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&tmem_empty[acc]);
             }
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
