@@ -323,7 +323,10 @@ def run_b200(args):
     tf = ROOT / "profiles" / "roofline_traffic.json"
     if tf.exists():
         try:
+            # bytes per launch (dram read + write, averaged over every launch of the class in one ncu'd pass)
             traffic = json.loads(tf.read_text()).get(dk)
+            if isinstance(traffic, dict):
+                traffic = traffic.get("dram_bytes_per_launch")
         except Exception:
             traffic = None
     roofline = {"kernel": {"gemm": "gemm_kernel (implicit-GEMM conv/linear, tcgen05)", "attention": "attention_kernel"}.get(dk, dk),
