@@ -155,7 +155,9 @@ def run_reference(args):
     line = {"impl": "reference", "metric": "sd21_images_per_sec", "value": ips, "unit": "images/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 / ips, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-            "config": workload_config(args, 1),
+            # same workload as the B200 arm; the bounded CPU sample runs one image (CFG batch 2) at a time -- the
+            # oracle's images/s does not depend on how many prompts are queued
+            "config": dict(workload_config(args, args.batch), cpu_sample_batch=1),
             "cpu_baseline": {"value": ips, "unit": "images/s", "cores": info["cores"], "kind": "port", "sample": sample,
                              "unet_step_s": info["unet_step_s"], "vae_decode_s": info["vae_decode_s"]},
             "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
