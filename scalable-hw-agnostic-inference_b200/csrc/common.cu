@@ -80,6 +80,27 @@ int32_t encode_tmap_bf16(CUtensorMap* map, const void* base, int rank, const uin
     return B200SD_OK;
 }
 
+// 2-D row-major tensor [rows][cols] of 2- or 4-byte elements, box = box_cols x box_rows, swizzle 64 or 128 bytes
+// (= box_cols * elem_bytes).  Used for the GEMM epilogue's TMA stores.
+int32_t encode_tmap_2d(CUtensorMap* map, const void* base, int elem_bytes, uint64_t cols, uint64_t rows,
+                       uint64_t row_stride_bytes, uint32_t box_cols, uint32_t box_rows, int swizzle_bytes) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) return set_error(B200SD_ERR_DEVICE, "cuTensorMapEncodeTiled not available from the driver");
+    cuuint64_t gdim[2] = {cols, rows};
+    cuuint64_t gstr[1] = {row_stride_bytes};
+    cuuint32_t bx[2] = {box_cols, box_rows};
+    cuuint32_t es[2] = {1, 1};
+    CUresult r = fn(map, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT16, 2,
+                    const_cast<void*>(base), gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                    CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return set_error(B200SD_ERR_BAD_ARG, "cuTensorMapEncodeTiled (2-D, %d-byte) failed (%d): base=%p cols=%llu rows=%llu "
+                         "stride=%llu", elem_bytes, (int)r, base, (unsigned long long)cols, (unsigned long long)rows,
+                         (unsigned long long)row_stride_bytes);
+    return B200SD_OK;
+}
+
 }  // namespace b200sd
 
 using namespace b200sd;

@@ -18,6 +18,8 @@ int num_sms();
 // dims/strides innermost first; strides[i] is the byte stride of dim i+1 (dim 0 is contiguous).
 int32_t encode_tmap_bf16(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
                          const uint64_t* strides_bytes, const uint32_t* box);
+int32_t encode_tmap_2d(CUtensorMap* map, const void* base, int elem_bytes, uint64_t cols, uint64_t rows,
+                       uint64_t row_stride_bytes, uint32_t box_cols, uint32_t box_rows, int swizzle_bytes);
 
 #define B200SD_CHECK_ARG(cond, ...)                                  \
     do {                                                             \

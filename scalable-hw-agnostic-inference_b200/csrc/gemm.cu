@@ -3,7 +3,12 @@
 //   warp 0      TMA producer   : A = 4-D NHWC box (64 ch x bw x bh x bn pixels, shifted by the filter tap,
 //                                zero-filled outside the image = the conv padding), B = 64 x BLOCK_N weight box
 //   warp 1      UMMA issuer    : tcgen05.mma 128 x BLOCK_N x 16, fp32 accumulators in TMEM, double-buffered
-//   warps 2..5  epilogue       : tcgen05.ld -> bias / timestep-row bias / residual / GEGLU -> 16-bit | fp32 stores
+//   warps 2..9  epilogue       : tcgen05.ld -> bias / timestep-row bias / residual / GEGLU -> 16-bit | fp32.  Two warps
+//                                per TMEM lane quadrant take alternate 32-column chunks.  Linear layers without a
+//                                residual leave by TMA store from a per-warp staging tile; everything else that has a
+//                                plain column bias goes through the same tile transposed, so that global loads and
+//                                stores are whole row segments; the rest (row bias, bias along M, ragged last
+//                                chunk) stores straight from the accumulator row each thread holds.
 //
 // One CTA per SM; work items are walked n-fastest so an A tile is fetched from HBM once and the weight matrix
 // stays L2-resident.  When a problem has fewer output tiles than SMs (the 24x24 and 12x12 UNet levels at small
@@ -51,6 +56,8 @@ struct GemmKernelParams {
     long long ld_out;
     int geglu;
     int fast_epi;  // 1: outputs leave through the per-warp staging tile as full 128-byte row segments
+    int tma_epi;   // 1: (linear layout, no residual) the staging tile is written in the output dtype, row per thread, and
+                   //    leaves with one TMA store per 32x32 chunk: no shared-memory read-back on the epilogue's chain
 };
 
 template <int BLOCK_N>
@@ -61,10 +68,11 @@ struct GemmCfg {
     // operand ring | barriers | per-tile column bias (2 x 256 fp32) | one 32x32 fp32 staging tile per epilogue warp.
     // No alignment slack: the kernel traps if the dynamic segment is not 1024-byte aligned (it always is in practice:
     // there is no static shared memory in front of it).
-    static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
+    static constexpr int STG_OFF = STAGES * STAGE_BYTES;  // 1024-byte aligned: the staging tiles are TMA-store sources
+    static constexpr int BAR_OFF = STG_OFF + EPI_WARPS * 4096;
     static constexpr int BIAS_OFF = BAR_OFF + 256;
-    static constexpr int STG_OFF = BIAS_OFF + 2 * 256 * 4;
-    static constexpr int SMEM_BYTES = STG_OFF + EPI_WARPS * 4096;
+    static constexpr int SMEM_BYTES = BIAS_OFF + 2 * 256 * 4;
+    static_assert(STG_OFF % 1024 == 0, "staging tiles must keep the swizzle-atom alignment");
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
 
@@ -163,6 +171,22 @@ __device__ __forceinline__ void stage_rows(float* stg, int lane, const float (&v
 }
 __device__ __forceinline__ float4 stage_read(const float* stg, int row, int chunk) {
     return *reinterpret_cast<const float4*>(stg + row * 32 + ((chunk ^ (row & 7)) << 2));
+}
+// TMA-store variant: the thread writes its own row in the OUTPUT dtype, in the layout the store's tensor map expects
+// (32 fp32 = 128-byte rows, SWIZZLE_128B: chunk ^= row & 7; 32 halves = 64-byte rows, SWIZZLE_64B: chunk ^= (row >> 1) & 3).
+__device__ __forceinline__ void stage_rows_out(const GemmKernelParams& p, float* stg, int lane, const float (&v)[32]) {
+    if (p.out_dtype == B200SD_F32) {
+        stage_rows(stg, lane, v);
+    } else {
+        const bool f16 = p.out_dtype == B200SD_F16;
+        uint8_t* row = reinterpret_cast<uint8_t*>(stg) + lane * 64;
+        const int sw = (lane >> 1) & 3;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            *reinterpret_cast<uint4*>(row + ((j ^ sw) << 4)) =
+                make_uint4(pack_h2(v[8 * j], v[8 * j + 1], f16), pack_h2(v[8 * j + 2], v[8 * j + 3], f16),
+                           pack_h2(v[8 * j + 4], v[8 * j + 5], f16), pack_h2(v[8 * j + 6], v[8 * j + 7], f16));
+    }
 }
 // Transposed lane mapping.  fp32 outputs: 8 passes, row = 4*i + lane/8, columns 4*(lane%8)..+3.
 //                            16-bit outputs: 4 passes, row = 8*i + lane/4, columns 8*(lane%4)..+7.
@@ -274,7 +298,7 @@ __device__ __forceinline__ void add_col_bias32(const GemmKernelParams& p, float 
 template <int BLOCK_N>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
     gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                const GemmKernelParams p) {
+                const __grid_constant__ CUtensorMap tmOut, const GemmKernelParams p) {
     using Cfg = GemmCfg<BLOCK_N>;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -434,6 +458,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         float* stg = reinterpret_cast<float*>(smem + Cfg::STG_OFF) + (warp - 2) * 1024;
         const bool out32 = p.out_dtype == B200SD_F32;
         const bool fast = p.fast_epi != 0;
+        const bool tma = p.tma_epi != 0;
         const int row_in_tile = quad * 32 + lane;
         const int box_pix = p.bw * p.bh;
         // position of this thread's accumulator row inside the pixel box (the same for every tile)
@@ -473,6 +498,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
             for (int i = 0; i < 8; ++i)
                 mt[i] = __shfl_sync(0xffffffffu, (int)m, out32 ? 4 * i + (lane >> 3) : 8 * (i & 3) + (lane >> 2));
             const int colbase = n_tile * BLOCK_N;
+            const int row0 = m_tile * BLOCK_M + quad * 32;  // first output row of this warp (linear layout only)
             const bool use_res = fast && p.residual != nullptr;
             uint4 rbuf[8];
             if (use_res && splits == 1 && colbase + eg * 32 + 32 <= p.n_cols)
@@ -549,6 +575,39 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                     for (int c = eg; c < NC; c += 2) {
                         const int col0 = colbase + c * 32;
                         const bool more = c + 2 < NC;
+                        if (tma) {
+                            // bias reads are issued before the TMEM wait so the two latencies overlap
+                            float4 bq[8];
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) bq[j] = *reinterpret_cast<const float4*>(bs + c * 32 + 4 * j);
+                            const bool live = col0 < p.n_cols && row0 < p.img_w;
+                            tmem_ld_wait();
+                            float v[32];
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                v[4 * j + 0] = __uint_as_float(r[4 * j + 0]) + bq[j].x;
+                                v[4 * j + 1] = __uint_as_float(r[4 * j + 1]) + bq[j].y;
+                                v[4 * j + 2] = __uint_as_float(r[4 * j + 2]) + bq[j].z;
+                                v[4 * j + 3] = __uint_as_float(r[4 * j + 3]) + bq[j].w;
+                            }
+                            if (lane == 0) bulk_wait_read0();  // the store that last read this staging tile let go of it
+                            __syncwarp();
+                            stage_rows_out(p, stg, lane, v);
+                            if (more) {
+                                tmem_ld_x32(t_addr + (c + 2) * 32, r);
+                            } else {
+                                tc_fence_before();
+                                __syncwarp();
+                                if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+                            }
+                            fence_proxy_async_smem();
+                            __syncwarp();
+                            if (lane == 0 && live) {
+                                tma_store_2d(&tmOut, stg, col0, row0);  // rows / columns past the edge are clipped
+                                bulk_commit();
+                            }
+                            continue;
+                        }
                         tmem_ld_wait();
                         const bool full = fast && col0 + 32 <= p.n_cols;
                         if (full) {
@@ -611,7 +670,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                             if (lane == 0) mbar_arrive(&tmem_empty[acc]);
                         }
                         const int col0 = n_tile * HALF + c * 32;
-                        if (fast) {
+                        if (tma) {
+                            if (lane == 0) bulk_wait_read0();
+                            __syncwarp();
+                            stage_rows_out(p, stg, lane, v);
+                            fence_proxy_async_smem();
+                            __syncwarp();
+                            if (lane == 0 && row0 < p.img_w) {
+                                tma_store_2d(&tmOut, stg, col0, row0);
+                                bulk_commit();
+                            }
+                        } else if (fast) {
                             stage_rows(stg, lane, v);
                             __syncwarp();
                             staged_store(p, stg, mt, vmask, lane, col0, nullptr, false, rbuf);
@@ -625,6 +694,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
         }
+        if (tma && lane == 0) bulk_wait0();  // the staging tiles must outlive the stores that read them
     }
 
     tc_fence_before();
@@ -719,8 +789,8 @@ static int64_t ws_bytes_for(long long tiles, int splits, int block_n) {
 }
 
 template <int BLOCK_N>
-static int32_t launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmKernelParams& kp,
-                           cudaStream_t stream) {
+static int32_t launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut,
+                           const GemmKernelParams& kp, cudaStream_t stream) {
     using Cfg = GemmCfg<BLOCK_N>;
     static bool attr_set[64] = {false};
     int dev = 0;
@@ -733,7 +803,7 @@ static int32_t launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const
     }
     long long total = (long long)kp.m_tiles * kp.n_tiles * kp.splits;
     int grid = (int)(total < num_sms() ? total : num_sms());
-    gemm_kernel<BLOCK_N><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, kp);
+    gemm_kernel<BLOCK_N><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmOut, kp);
     count_launch();
     B200SD_CHECK_LAUNCH("gemm_kernel");
     return B200SD_OK;
@@ -851,6 +921,11 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
         // of out / residual rows was checked above for n_cols >= 32
         const bool res_ok = !p->residual || p->residual_dtype == p->out_dtype;
         kp.fast_epi = (n_cols >= 32 && !p->bias_along_m && !p->row_bias && res_ok) ? 1 : 0;
+        // TMA-store epilogue: plain [M, n_cols] row-major output (linear layers), no residual, unsplit
+        static const bool tma_off = getenv("B200SD_GEMM_NO_TMA_EPI") != nullptr;
+        const int osz = p->out_dtype == B200SD_F32 ? 4 : 2;
+        kp.tma_epi = (kp.fast_epi && !tma_off && !p->residual && kp.splits == 1 && p->taps == 1 && p->img_h == 1 &&
+                      p->n_img == 1 && (p->ld_out * osz) % 16 == 0) ? 1 : 0;
     }
     if (kp.splits > 1) {
         const long long tiles = (long long)kp.m_tiles * kp.n_tiles;
@@ -876,12 +951,19 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
         int32_t r = encode_tmap_bf16(&tmB, p->w, 2, dims, strides, box);
         if (r) return r;
     }
+    CUtensorMap tmOut = tmB;  // placeholder when the TMA-store epilogue is off (never dereferenced then)
+    if (kp.tma_epi) {
+        const int osz = p->out_dtype == B200SD_F32 ? 4 : 2;
+        int32_t r = encode_tmap_2d(&tmOut, p->out, osz, (uint64_t)n_cols, (uint64_t)p->img_w,
+                                   (uint64_t)p->ld_out * osz, 32, 32, osz == 4 ? 128 : 64);
+        if (r) return r;
+    }
     cudaStream_t s = as_stream(stream);
     switch (block_n) {
-        case 64: return launch_gemm<64>(tmA, tmB, kp, s);
-        case 128: return launch_gemm<128>(tmA, tmB, kp, s);
-        case 160: return launch_gemm<160>(tmA, tmB, kp, s);
-        default: return launch_gemm<256>(tmA, tmB, kp, s);
+        case 64: return launch_gemm<64>(tmA, tmB, tmOut, kp, s);
+        case 128: return launch_gemm<128>(tmA, tmB, tmOut, kp, s);
+        case 160: return launch_gemm<160>(tmA, tmB, tmOut, kp, s);
+        default: return launch_gemm<256>(tmA, tmB, tmOut, kp, s);
     }
 }
 
