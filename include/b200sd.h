@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200SD_ABI_VERSION 3
+#define B200SD_ABI_VERSION 4
 
 typedef struct CUstream_st* b200sd_stream_t; /* == cudaStream_t / CUstream */
 
@@ -87,6 +87,8 @@ typedef struct {
     int64_t workspace_bytes;
     int32_t split_k;        /* 0 = choose (splits only when the problem has fewer tiles than SMs and a workspace is
                                given), 1 = off, 2..8 = forced */
+    int32_t act;            /* 0 = none, 1 = erf-GELU applied to (acc + bias) before the residual is added: the CLIP text
+                               encoder's MLP (transformers CLIPMLP, hidden_act "gelu").  Not with geglu. */
 } b200sd_gemm_params;
 int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stream);
 /* bytes of workspace this problem would use if one were supplied (0 = it would not split K) */
@@ -108,6 +110,7 @@ typedef struct {
     int32_t batch, heads, head_dim; /* head_dim must be 64 */
     int32_t sq, skv;
     float scale;            /* softmax(scale * q.k) */
+    int32_t causal;         /* 1 = key j is visible to query i only if j <= i (text encoder); needs sq == skv */
 } b200sd_attention_params;
 int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_stream_t stream);
 
@@ -240,6 +243,20 @@ typedef struct {
     float scale;
 } b200sd_softmax_params;
 int32_t b200sd_softmax_rows(const b200sd_softmax_params* p, b200sd_stream_t stream);
+
+/* ---- text-encoder embeddings: out[b, t, :] = token_table[ids[b, t], :] + position_table[t, :] ---------------------
+ * (transformers CLIPTextEmbeddings; reached from the reference through pipe.text_encoder, app/run-sd.py:118-122).
+ * ids int32 [rows] with rows = batch * seq_len; tables fp32; out fp32 [rows, dim]; dim % 4 == 0; an id outside
+ * [0, vocab) is an error the kernel cannot report, so the caller clamps or validates. */
+typedef struct {
+    const int32_t* ids;
+    const float* token_table;     /* [vocab, dim] */
+    const float* position_table;  /* [seq_len, dim] */
+    float* out;
+    int64_t rows;
+    int32_t seq_len, dim, vocab;
+} b200sd_embed_params;
+int32_t b200sd_embed_tokens(const b200sd_embed_params* p, b200sd_stream_t stream);
 
 /* ---- K7: VaeImageProcessor.postprocess on device: (x/2+0.5).clamp(0,1)*255 round -> uint8 -------------
  * (the reference does this on the CPU after a fp32 D2H copy; app/run-sd.py:140 `.images[0]`, :177-181) */

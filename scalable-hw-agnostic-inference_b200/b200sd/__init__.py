@@ -7,11 +7,12 @@ from . import _lib
 _lib.load()  # fail loudly if the CUDA library is missing
 
 from . import ops  # noqa: E402
+from .clip import B200CLIPTextEncoder, CLIPTextConfig, HashTokenizer, PromptEncoder  # noqa: E402
 from .config import UNetConfig, VAEConfig  # noqa: E402
 from .pipeline import B200Pipeline, StandInTextEncoder, install_into  # noqa: E402
 from .scheduler import B200Scheduler  # noqa: E402
 from .unet import B200UNet  # noqa: E402
 from .vae import B200PostQuantConv, B200VAEDecoder  # noqa: E402
 
-__all__ = ["ops", "UNetConfig", "VAEConfig", "B200Pipeline", "StandInTextEncoder", "install_into", "B200Scheduler",
+__all__ = ["ops", "B200CLIPTextEncoder", "CLIPTextConfig", "HashTokenizer", "PromptEncoder", "UNetConfig", "VAEConfig", "B200Pipeline", "StandInTextEncoder", "install_into", "B200Scheduler",
            "B200UNet", "B200VAEDecoder", "B200PostQuantConv"]

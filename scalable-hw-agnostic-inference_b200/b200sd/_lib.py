@@ -7,7 +7,7 @@ from pathlib import Path
 
 _HERE = Path(__file__).resolve().parent
 LIB_PATH = _HERE / "libb200sd.so"
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 BF16, F32, F16 = 1, 2, 3
 
@@ -20,13 +20,18 @@ class GemmParams(C.Structure):
                 ("bias_along_m", c_i32), ("row_bias", c_vp), ("row_bias_stride", c_i64), ("residual", c_vp),
                 ("residual_dtype", c_i32), ("ld_res", c_i64), ("out", c_vp), ("out_dtype", c_i32), ("ld_out", c_i64),
                 ("geglu", c_i32), ("block_n", c_i32), ("workspace", c_vp), ("workspace_bytes", c_i64),
-                ("split_k", c_i32)]
+                ("split_k", c_i32), ("act", c_i32)]
 
 
 class AttentionParams(C.Structure):
     _fields_ = [("q", c_vp), ("k", c_vp), ("v", c_vp), ("ld_q", c_i64), ("ld_k", c_i64), ("ld_v", c_i64),
                 ("out", c_vp), ("ld_out", c_i64), ("dtype", c_i32), ("batch", c_i32), ("heads", c_i32),
-                ("head_dim", c_i32), ("sq", c_i32), ("skv", c_i32), ("scale", c_f32)]
+                ("head_dim", c_i32), ("sq", c_i32), ("skv", c_i32), ("scale", c_f32), ("causal", c_i32)]
+
+
+class EmbedParams(C.Structure):
+    _fields_ = [("ids", c_vp), ("token_table", c_vp), ("position_table", c_vp), ("out", c_vp), ("rows", c_i64),
+                ("seq_len", c_i32), ("dim", c_i32), ("vocab", c_i32)]
 
 
 class GroupNormParams(C.Structure):
@@ -95,6 +100,7 @@ SYMBOLS = {
     "b200sd_softmax_rows": (c_i32, [C.POINTER(SoftmaxParams), c_vp]),
     "b200sd_denorm_u8": (c_i32, [C.POINTER(DenormU8Params), c_vp]),
     "b200sd_cast": (c_i32, [C.POINTER(CastParams), c_vp]),
+    "b200sd_embed_tokens": (c_i32, [C.POINTER(EmbedParams), c_vp]),
     "b200sd_umma_selftest": (c_i32, [c_vp, c_i32, c_vp, c_i32, c_vp, c_i32, c_i32, c_i32, c_vp]),
 }
 

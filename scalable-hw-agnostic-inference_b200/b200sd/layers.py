@@ -108,8 +108,8 @@ class Kernels:
 
     def linear(self, a: torch.Tensor, w: torch.Tensor, bias, *, residual=None, out_dtype=None, geglu=False,
                out: Optional[torch.Tensor] = None, bias_along_m: bool = False, block_n: int = 0,
-               split_k: int = 0) -> torch.Tensor:
-        """a 16-bit [M, K] (any leading dims), w 16-bit [N, K]."""
+               split_k: int = 0, gelu: bool = False) -> torch.Tensor:
+        """a 16-bit [M, K] (any leading dims), w 16-bit [N, K].  gelu: erf-GELU on (a w^T + bias), before the residual."""
         k = a.shape[-1]
         m = a.numel() // k
         n_cols = w.shape[0] // 2 if geglu else w.shape[0]
@@ -117,7 +117,7 @@ class Kernels:
             out = torch.empty(*a.shape[:-1], n_cols, device=self.device, dtype=out_dtype or self.trunk_dtype)
         res2 = residual.view(m, n_cols) if residual is not None else None
         ops.gemm(a, 1, 1, m, k, 1, w, bias, bias_along_m, None, 0, res2, out.view(m, n_cols), geglu, block_n,
-                 self.gemm_ws, split_k)
+                 self.gemm_ws, split_k, 1 if gelu else 0)
         return out
 
     def im2col(self, x: torch.Tensor, n_img: int, stride: int, k_pad: int) -> torch.Tensor:
@@ -133,9 +133,10 @@ class Kernels:
         ops.upsample2x(x, n, h, w, c, out)
         return out
 
-    def attention(self, q, k, v, batch: int, heads: int, sq: int, skv: int, scale: float) -> torch.Tensor:
+    def attention(self, q, k, v, batch: int, heads: int, sq: int, skv: int, scale: float,
+                  causal: bool = False) -> torch.Tensor:
         out = torch.empty(batch * sq, heads * 64, device=self.device, dtype=q.dtype)
-        ops.attention(q, k, v, out, batch, heads, sq, skv, scale)
+        ops.attention(q, k, v, out, batch, heads, sq, skv, scale, causal)
         return out
 
 

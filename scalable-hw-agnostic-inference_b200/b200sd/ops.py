@@ -103,7 +103,7 @@ def _nbytes(*ts) -> float:
 
 # ------------------------------------------------------------------------------------------------ impls
 def _gemm(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, row_bias_stride, residual, out,
-          geglu, block_n, workspace=None, split_k=0):
+          geglu, block_n, workspace=None, split_k=0, act=0):
     p = L.GemmParams()
     p.a, p.a_dtype, p.n_img, p.img_h, p.img_w, p.cin, p.taps = _ptr(a), _dt(a), n_img, img_h, img_w, cin, taps
     p.w, p.w_dtype, p.n_out = _ptr(w), _dt(w), w.shape[0]
@@ -113,7 +113,7 @@ def _gemm(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, ro
     if residual is not None:
         p.residual, p.residual_dtype, p.ld_res = _ptr(residual), _dt(residual), residual.stride(-2)
     p.out, p.out_dtype, p.ld_out = _ptr(out), _dt(out), out.stride(-2)
-    p.geglu, p.block_n, p.split_k = int(geglu), block_n, split_k
+    p.geglu, p.block_n, p.split_k, p.act = int(geglu), block_n, split_k, act
     if workspace is not None:
         p.workspace, p.workspace_bytes = _ptr(workspace), workspace.numel() * workspace.element_size()
     m = n_img * img_h * img_w
@@ -121,12 +121,13 @@ def _gemm(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, ro
          f"M{m} N{w.shape[0]} K{taps * cin} taps{taps} img{n_img}x{img_h}x{img_w}{' geglu' if geglu else ''}")
 
 
-def _attention(q, k, v, out, batch, heads, sq, skv, scale):
+def _attention(q, k, v, out, batch, heads, sq, skv, scale, causal=False):
     assert q.dtype == k.dtype == v.dtype == out.dtype
     p = L.AttentionParams()
     p.q, p.k, p.v, p.out = _ptr(q), _ptr(k), _ptr(v), _ptr(out)
     p.ld_q, p.ld_k, p.ld_v, p.ld_out = q.stride(-2), k.stride(-2), v.stride(-2), out.stride(-2)
     p.dtype, p.batch, p.heads, p.head_dim, p.sq, p.skv, p.scale = _dt(q), batch, heads, 64, sq, skv, scale
+    p.causal = int(causal)
     _run("attention", 4.0 * batch * heads * sq * skv * 64, L.load().b200sd_attention, p,
          f"b{batch} h{heads} sq{sq} skv{skv}")
 
@@ -135,6 +136,14 @@ def groupnorm_workspace_bytes(n_img: int, hw: int, groups: int = 32) -> int:
     p = L.GroupNormParams()
     p.n_img, p.hw, p.groups = n_img, hw, groups
     return int(L.load().b200sd_groupnorm_workspace_bytes(C.byref(p)))
+
+
+def _embed_tokens(ids, token_table, position_table, out):
+    assert ids.dtype == torch.int32 and token_table.dtype == position_table.dtype == out.dtype == torch.float32
+    p = L.EmbedParams()
+    p.ids, p.token_table, p.position_table, p.out = _ptr(ids), _ptr(token_table), _ptr(position_table), _ptr(out)
+    p.rows, p.seq_len, p.dim, p.vocab = ids.numel(), ids.shape[-1], token_table.shape[1], token_table.shape[0]
+    _run("embed_tokens", _nbytes(out) * 2, L.load().b200sd_embed_tokens, p, f"rows{p.rows} dim{p.dim}")
 
 
 def _groupnorm(x1, x2, n_img, hw, groups, eps, gamma, beta, silu, y, raw, workspace):
@@ -228,9 +237,10 @@ def umma_selftest(a: torch.Tensor, b: torch.Tensor, b_mn_major: bool) -> torch.T
 _SCHEMAS = {
     "gemm": ("(Tensor a, int n_img, int img_h, int img_w, int cin, int taps, Tensor w, Tensor? bias, bool bias_along_m, "
              "Tensor? row_bias, int row_bias_stride, Tensor? residual, Tensor(a!) out, bool geglu, int block_n, "
-             "Tensor(b!)? workspace=None, int split_k=0) -> ()", _gemm),
-    "attention": ("(Tensor q, Tensor k, Tensor v, Tensor(a!) out, int batch, int heads, int sq, int skv, float scale) -> ()",
-                  _attention),
+             "Tensor(b!)? workspace=None, int split_k=0, int act=0) -> ()", _gemm),
+    "attention": ("(Tensor q, Tensor k, Tensor v, Tensor(a!) out, int batch, int heads, int sq, int skv, float scale, "
+                  "bool causal=False) -> ()", _attention),
+    "embed_tokens": ("(Tensor ids, Tensor token_table, Tensor position_table, Tensor(a!) out) -> ()", _embed_tokens),
     "groupnorm": ("(Tensor x1, Tensor? x2, int n_img, int hw, int groups, float eps, Tensor gamma, Tensor beta, bool silu, "
                   "Tensor(a!) y, Tensor(b!)? raw, Tensor(c!) workspace) -> ()", _groupnorm),
     "layernorm": ("(Tensor x, float eps, Tensor gamma, Tensor beta, Tensor(a!) y) -> ()", _layernorm),
@@ -274,3 +284,4 @@ small_linear = torch.ops.b200sd.small_linear
 softmax_rows = torch.ops.b200sd.softmax_rows
 denorm_u8 = torch.ops.b200sd.denorm_u8
 cast = torch.ops.b200sd.cast
+embed_tokens = torch.ops.b200sd.embed_tokens

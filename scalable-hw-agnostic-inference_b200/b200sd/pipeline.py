@@ -22,9 +22,9 @@ from .vae import B200PostQuantConv, B200VAEDecoder
 
 
 class StandInTextEncoder:
-    """PLACEHOLDER for CLIPTokenizer + CLIPTextModel (not built yet): no CLIP vocabulary or
-    weights exist on this box, so a prompt is mapped to a deterministic pseudo-embedding seeded by its SHA-256.
-    Callers with real embeddings pass `prompt_embeds` / `negative_prompt_embeds` and never touch this."""
+    """PLACEHOLDER used only when no text encoder is given: a prompt is mapped to a deterministic pseudo-embedding
+    seeded by its SHA-256.  The real path is `b200sd.clip.PromptEncoder(B200CLIPTextEncoder(...))` (pass it as
+    `text_encoder=`); callers with ready embeddings pass `prompt_embeds` / `negative_prompt_embeds`."""
 
     def __init__(self, dim: int = 1024, length: int = 77):
         self.dim, self.length = dim, length
@@ -208,10 +208,11 @@ class B200Pipeline:
         return SimpleNamespace(images=images, nsfw_content_detected=None)
 
 
-def install_into(pipe, unet_sd=None, vae_sd=None, scheduler_kind: str = "ddim", device="cuda"):
+def install_into(pipe, unet_sd=None, vae_sd=None, scheduler_kind: str = "ddim", device="cuda",
+                 swap_text_encoder: bool = True):
     """The reference's plugin seam (app/run-sd.py:108-134) applied to a stock diffusers pipeline:
-    replaces pipe.unet, pipe.vae.decoder, pipe.vae.post_quant_conv and pipe.scheduler by B200 modules built from the
-    pipeline's own weights."""
+    replaces pipe.unet, pipe.text_encoder, pipe.vae.decoder, pipe.vae.post_quant_conv and pipe.scheduler by B200
+    modules built from the pipeline's own weights (the same five attributes the reference reassigns)."""
     unet_sd = unet_sd or pipe.unet.state_dict()
     vae_sd = vae_sd or pipe.vae.state_dict()
     ucfg = pipe.unet.config
@@ -223,4 +224,9 @@ def install_into(pipe, unet_sd=None, vae_sd=None, scheduler_kind: str = "ddim", 
     pipe.vae.decoder = B200VAEDecoder(vae_sd, VAEConfig.from_any(pipe.vae.config), device)
     pipe.vae.post_quant_conv = B200PostQuantConv()
     pipe.scheduler = B200Scheduler(scheduler_kind, pred, device)
+    if swap_text_encoder and getattr(pipe, "text_encoder", None) is not None:
+        from .clip import B200CLIPTextEncoder, CLIPTextConfig
+        te = pipe.text_encoder
+        pipe.text_encoder = B200CLIPTextEncoder(te.state_dict(), CLIPTextConfig.from_any(te.config), device,
+                                                out_dtype=getattr(te, "dtype", None))
     return pipe

@@ -40,6 +40,7 @@ struct AttnKernelParams {
     float scale_log2;  // scale * log2(e)
     uint16_t* out;
     long long ld_out;
+    int causal;   // 1: key j is visible to query i only if j <= i
     int stagger;  // 1: Q tile B starts half a softmax period behind tile A (see the UMMA warp)
 };
 
@@ -279,6 +280,17 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                         for (int i = 0; i < 32; ++i)
                             if (c * 32 + i >= valid) s[c][i] = __float_as_uint(-INFINITY);
                 }
+                if (p.causal) {
+                    const int qrow = q0 + t * ATT_BM + row;
+                    const int kbase = j * ATT_BN + half * 64;
+                    if (kbase + 63 > qrow) {
+#pragma unroll
+                        for (int c = 0; c < 2; ++c)
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (kbase + c * 32 + i > qrow) s[c][i] = __float_as_uint(-INFINITY);
+                    }
+                }
                 float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
                 for (int c = 0; c < 2; ++c)
@@ -453,6 +465,8 @@ extern "C" int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_str
     kp.out = static_cast<uint16_t*>(p->out);
     kp.ld_out = p->ld_out;
     kp.stagger = stagger_from_env();
+    kp.causal = p->causal ? 1 : 0;
+    B200SD_CHECK_ARG(!p->causal || p->sq == p->skv, "attention: causal needs sq == skv");
     const int rows_per_cta = ATT_BM * ATT_QT;
     dim3 grid((p->sq + rows_per_cta - 1) / rows_per_cta, p->heads, p->batch);
     cudaStream_t s = as_stream(stream);

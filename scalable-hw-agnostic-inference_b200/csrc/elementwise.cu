@@ -216,6 +216,23 @@ __global__ void layernorm_kernel(const void* __restrict__ x, int dt, long long r
     }
 }
 
+// =============================================================================================== token embeddings
+// out[r, :] = token_table[ids[r], :] + position_table[r % seq_len, :]; one thread per 4 channels
+__global__ void embed_tokens_kernel(const int* __restrict__ ids, const float* __restrict__ tok,
+                                    const float* __restrict__ pos, float* __restrict__ out, long long rows, int seq_len,
+                                    int dim) {
+    const int vpr = dim >> 2;
+    const long long total = rows * vpr;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long r = i / vpr;
+        const int v = (int)(i - r * vpr);
+        const float4 a = *reinterpret_cast<const float4*>(tok + (size_t)ids[r] * dim + 4 * v);
+        const float4 b = *reinterpret_cast<const float4*>(pos + (size_t)(r % seq_len) * dim + 4 * v);
+        *reinterpret_cast<float4*>(out + (size_t)r * dim + 4 * v) = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+    }
+}
+
 // =============================================================================================== im2col 3x3
 // one thread per 8 consecutive k of one output pixel
 __global__ void im2col3x3_kernel(const void* __restrict__ x, int dt, int n_img, int n_src, int in_h, int in_w,
@@ -479,6 +496,20 @@ extern "C" int32_t b200sd_groupnorm(const b200sd_groupnorm_params* p, b200sd_str
                                            p->out_dtype == B200SD_F16, chunks);
     count_launch(2);
     B200SD_CHECK_LAUNCH("groupnorm");
+    return B200SD_OK;
+}
+
+extern "C" int32_t b200sd_embed_tokens(const b200sd_embed_params* p, b200sd_stream_t stream) {
+    B200SD_CHECK_ARG(p && p->ids && p->token_table && p->position_table && p->out, "embed_tokens: null pointer");
+    B200SD_CHECK_ARG(p->dim > 0 && p->dim % 4 == 0 && p->seq_len > 0 && p->vocab > 0 && p->rows >= 0,
+                     "embed_tokens: bad shape (dim %d must be a positive multiple of 4)", p->dim);
+    B200SD_CHECK_ARG(ALIGNED16(p->token_table) && ALIGNED16(p->position_table) && ALIGNED16(p->out),
+                     "embed_tokens: tables and output must be 16-byte aligned");
+    if (p->rows == 0) return B200SD_OK;
+    embed_tokens_kernel<<<ew_grid(p->rows * (p->dim / 4), 256), 256, 0, as_stream(stream)>>>(
+        p->ids, p->token_table, p->position_table, p->out, p->rows, p->seq_len, p->dim);
+    count_launch();
+    B200SD_CHECK_LAUNCH("embed_tokens");
     return B200SD_OK;
 }
 

@@ -55,6 +55,7 @@ struct GemmKernelParams {
     int out_dtype;
     long long ld_out;
     int geglu;
+    int act;       // 1: erf-GELU on (acc + bias), before the residual
     int fast_epi;  // 1: outputs leave through the per-warp staging tile as full 128-byte row segments
     int tma_epi;   // 1: (linear layout, no residual) the staging tile is written in the output dtype, row per thread, and
                    //    leaves with one TMA store per 32x32 chunk: no shared-memory read-back on the epilogue's chain
@@ -226,6 +227,7 @@ __device__ __forceinline__ void staged_store(const GemmKernelParams& p, const fl
             const int row = 4 * i + (lane >> 3);
             float4 a = stage_read(stg, row, cg);
             a.x += b.x, a.y += b.y, a.z += b.z, a.w += b.w;
+            if (p.act) a.x = gelu_erf(a.x), a.y = gelu_erf(a.y), a.z = gelu_erf(a.z), a.w = gelu_erf(a.w);
             if (use_res) {
                 a.x += __uint_as_float(buf[i].x), a.y += __uint_as_float(buf[i].y);
                 a.z += __uint_as_float(buf[i].z), a.w += __uint_as_float(buf[i].w);
@@ -247,6 +249,10 @@ __device__ __forceinline__ void staged_store(const GemmKernelParams& p, const fl
             float4 a0 = stage_read(stg, row, 2 * cg), a1 = stage_read(stg, row, 2 * cg + 1);
             a0.x += b0.x, a0.y += b0.y, a0.z += b0.z, a0.w += b0.w;
             a1.x += b1.x, a1.y += b1.y, a1.z += b1.z, a1.w += b1.w;
+            if (p.act) {
+                a0.x = gelu_erf(a0.x), a0.y = gelu_erf(a0.y), a0.z = gelu_erf(a0.z), a0.w = gelu_erf(a0.w);
+                a1.x = gelu_erf(a1.x), a1.y = gelu_erf(a1.y), a1.z = gelu_erf(a1.z), a1.w = gelu_erf(a1.w);
+            }
             if (use_res) {
                 a0.x += h_lo(buf[i].x, f16), a0.y += h_hi(buf[i].x, f16);
                 a0.z += h_lo(buf[i].y, f16), a0.w += h_hi(buf[i].y, f16);
@@ -558,6 +564,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                                 }
                             }
                             add_col_bias32(p, v, m, img, col0);
+                            if (p.act) {
+#pragma unroll
+                                for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+                            }
                             epilogue_store32(p, v, m, img, col0);
                         }
                     }
@@ -590,6 +600,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                                 v[4 * j + 2] = __uint_as_float(r[4 * j + 2]) + bq[j].z;
                                 v[4 * j + 3] = __uint_as_float(r[4 * j + 3]) + bq[j].w;
                             }
+                            if (p.act) {
+#pragma unroll
+                                for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+                            }
                             if (lane == 0) bulk_wait_read0();  // the store that last read this staging tile let go of it
                             __syncwarp();
                             stage_rows_out(p, stg, lane, v);
@@ -620,6 +634,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 #pragma unroll
                             for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
                             add_col_bias32(p, v, m, img, col0);
+                            if (p.act) {
+#pragma unroll
+                                for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+                            }
                             epilogue_store32(p, v, m, img, col0);
                         }
                         if (more) {
@@ -829,6 +847,8 @@ static int32_t make_plan(const b200sd_gemm_params* p, bool have_ws, GemmPlan* pl
     kp.m_tiles = kp.tiles_x * kp.tiles_y * tiles_n;
     kp.kb_per_tap = (p->cin + BLOCK_K - 1) / BLOCK_K;
     kp.geglu = p->geglu ? 1 : 0;
+    kp.act = p->act;
+    B200SD_CHECK_ARG(p->act == 0 || (p->act == 1 && !p->geglu), "gemm: act must be 0, or 1 (GELU) without geglu");
     kp.n_out = p->n_out, kp.n_cols = kp.geglu ? p->n_out / 2 : p->n_out;
     kp.a_box_bytes = (uint32_t)(kp.bw * kp.bh * kp.bn) * BLOCK_K * 2;
     B200SD_CHECK_ARG(p->block_n == 0 || p->block_n == 64 || p->block_n == 128 || p->block_n == 160 || p->block_n == 256,

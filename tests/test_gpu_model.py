@@ -168,3 +168,67 @@ def test_full_size_vae_decode_512(cuda, lib_built):
     p = O.psnr((out / 2 + 0.5).clamp(0, 1), (ref / 2 + 0.5).clamp(0, 1))
     print(f"SD2.1 VAE 512^2 decode rel L2 {err:.3e}, PSNR {p:.2f} dB")
     assert err <= 1e-2 and p >= PSNR_MIN
+
+
+# ------------------------------------------------------------------------------------------------ text encoder (8f rank 1)
+def _clip_rel(a, b):
+    return ((a.float().cpu() - b.float().cpu()).norm() / b.float().cpu().norm()).item()
+
+
+def test_clip_text_encoder_tiny_matches_oracle_and_transformers_golden(cuda, lib_built):
+    """CUDA text encoder vs the CPU oracle AND vs the committed output of the real transformers.CLIPTextModel"""
+    from pathlib import Path
+    from safetensors.torch import load_file
+    import b200sd
+    from oracle import clip_text as C
+    g = load_file(str(Path(__file__).parent / "golden" / "clip_tiny.safetensors"))
+    cfg = C.tiny_clip_config()
+    sd = C.seeded_state_dict(cfg, int(g["weights_seed"][0]))
+    enc = b200sd.B200CLIPTextEncoder(sd, vars(cfg), cuda)
+    out = enc(g["input_ids"].to(cuda))[0]
+    assert out.shape == (3, 77, 128)
+    assert _clip_rel(out, C.clip_text_forward(sd, cfg, g["input_ids"])) < 1e-2
+    assert _clip_rel(out, g["last_hidden_state"]) < 1e-2
+
+
+def test_clip_text_encoder_sd21_size_matches_oracle(cuda, lib_built):
+    """the SD2.1 configuration (23 layers x 1024, 340 M parameters), two prompts of 77 tokens, one of them padded"""
+    import b200sd
+    from oracle import clip_text as C
+    cfg = C.CLIPTextConfig()
+    sd = C.seeded_state_dict(cfg, 1)
+    ids = C.seeded_ids(cfg, 2, seed=7)
+    ids[1, 20:] = 0
+    ref = C.clip_text_forward(sd, cfg, ids)
+    enc = b200sd.B200CLIPTextEncoder(sd, vars(cfg), cuda)
+    out = enc(ids.to(cuda), attention_mask=None).last_hidden_state
+    assert out.dtype == enc.dtype and out.shape == (2, 77, 1024)
+    assert _clip_rel(out, ref) < 1e-2  # north_star tolerance for 16-bit tensor-core operands against the fp32 oracle
+
+
+def test_pipeline_runs_from_prompt_strings_through_the_cuda_text_encoder(cuda, lib_built):
+    """pipe(prompt=...) with PromptEncoder(B200CLIPTextEncoder): prompts -> ids -> CUDA CLIP -> UNet -> VAE -> uint8"""
+    import b200sd
+    from b200sd._randinit import random_state_dicts
+    from oracle import clip_text as C
+    from oracle import sd21 as O
+    ucfg = b200sd.UNetConfig.from_any(O.tiny_unet_config())
+    vcfg = b200sd.VAEConfig.from_any(O.tiny_vae_config())
+    usd, vsd = random_state_dicts(ucfg, vcfg, 0)
+    ccfg = C.CLIPTextConfig(hidden_size=ucfg.cross_attention_dim, intermediate_size=256, num_hidden_layers=2,
+                            num_attention_heads=ucfg.cross_attention_dim // 64)
+    enc = b200sd.PromptEncoder(b200sd.B200CLIPTextEncoder(C.seeded_state_dict(ccfg, 2), vars(ccfg), cuda))
+    pipe = b200sd.B200Pipeline(b200sd.B200UNet(usd, ucfg, cuda), b200sd.B200VAEDecoder(vsd, vcfg, cuda),
+                               text_encoder=enc)
+    g = torch.Generator("cpu").manual_seed(0)
+    r1 = pipe(prompt=["a red cube", "a blue sphere"], num_inference_steps=3, generator=g, output_type="uint8")
+    g = torch.Generator("cpu").manual_seed(0)
+    r2 = pipe(prompt=["a red cube", "a blue sphere"], num_inference_steps=3, generator=g, output_type="uint8")
+    s = ucfg.sample_size * 8
+    assert r1.images.shape == (2, s, s, 3) and r1.images.dtype == torch.uint8
+    assert torch.equal(r1.images, r2.images)                  # deterministic, cached prompt embeddings
+    assert not torch.equal(r1.images[0], r1.images[1])        # the prompt reaches the image
+    e = enc(["a red cube", ""])
+    ids = enc.tokenizer(["a red cube", ""])
+    ref = C.clip_text_forward(C.seeded_state_dict(ccfg, 2), ccfg, ids)
+    assert _clip_rel(e, ref) < 1e-2

@@ -338,3 +338,51 @@ def test_flash_attention_large_logits_rescale(K, cuda):
     qf, kf, vf = (t.float().view(1, s, heads, 64).transpose(1, 2) for t in (q, k, v))
     ref = (torch.softmax(qf @ kf.transpose(-1, -2) * 0.5, -1) @ vf).transpose(1, 2).reshape(s, c)
     assert rel(out, ref) < 2 * out_tol(dt)
+
+
+# ------------------------------------------------------------------------------------------------ text-encoder ops
+@pytest.mark.parametrize("batch,heads,s", [(3, 2, 77), (2, 16, 77), (1, 2, 33), (2, 2, 300), (1, 1, 640)])
+def test_flash_attention_causal(K, cuda, batch, heads, s):
+    """causal flag (text encoder): key j visible to query i iff j <= i, across one and several kv tiles"""
+    dt = K.op_dtype
+    c = heads * 64
+    qkv = rnd(batch * s, 3 * c, dev=cuda, seed=4, dtype=dt)
+    q, k, v = qkv[:, :c], qkv[:, c:2 * c], qkv[:, 2 * c:]
+    out = K.attention(q, k, v, batch, heads, s, s, 0.125, causal=True)
+    qf, kf, vf = (t.float().view(batch, s, heads, 64).transpose(1, 2) for t in (q, k, v))
+    mask = torch.full((s, s), float("-inf"), device=cuda).triu(1)
+    ref = (torch.softmax(qf @ kf.transpose(-1, -2) * 0.125 + mask, -1) @ vf).transpose(1, 2).reshape(batch * s, c)
+    assert rel(out, ref) < 2 * out_tol(dt)
+
+
+def test_attention_causal_needs_square(K, cuda):
+    dt = K.op_dtype
+    q, kv = rnd(64, 64, dev=cuda, seed=1, dtype=dt), rnd(77, 128, dev=cuda, seed=2, dtype=dt)
+    with pytest.raises(RuntimeError, match="causal"):
+        K.attention(q, kv[:, :64], kv[:, 64:], 1, 1, 64, 77, 0.125, causal=True)
+
+
+@pytest.mark.parametrize("m,n,k,res,out32", [(154, 4096, 1024, False, False), (154, 512, 128, False, True),
+                                             (300, 320, 320, True, True), (231, 520, 64, False, False)])
+def test_linear_gelu_epilogue(K, cuda, m, n, k, res, out32):
+    """act = GELU(erf) on (a w^T + bias), before the residual: TMA-store, staged and row-wise epilogues"""
+    dt = K.op_dtype
+    a, w = rnd(m, k, dev=cuda, seed=1, dtype=dt), rnd(n, k, dev=cuda, seed=2, scale=k ** -0.5, dtype=dt)
+    bias = rnd(n, dev=cuda, seed=3)
+    r = rnd(m, n, dev=cuda, seed=4) if res else None
+    out = K.linear(a, w, bias, residual=r, out_dtype=torch.float32 if out32 else dt, gelu=True)
+    ref = F.gelu(a.float() @ w.float().t() + bias)
+    if res:
+        ref = ref + r
+    assert rel(out, ref) < (2e-5 if out32 else out_tol(dt))
+
+
+def test_embed_tokens(cuda, lib_built):
+    from b200sd import ops
+    g = torch.Generator("cpu").manual_seed(3)
+    tok, pos = torch.randn(1000, 128, generator=g).to(cuda), torch.randn(77, 128, generator=g).to(cuda)
+    ids = torch.randint(0, 1000, (5, 77), generator=g).to(cuda).to(torch.int32)
+    out = torch.empty(5 * 77, 128, device=cuda)
+    ops.embed_tokens(ids, tok, pos, out)
+    ref = tok[ids.long()] + pos[None]
+    assert torch.equal(out.view(5, 77, 128), ref)  # one fp32 add per element: bit-exact

@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol(lib_built):
     lib = ctypes.CDLL(str(lib_built))
     for name in declared:
         assert hasattr(lib, name), name
-    assert _lib.load().b200sd_abi_version() == _lib.ABI_VERSION == 3
+    assert _lib.load().b200sd_abi_version() == _lib.ABI_VERSION == 4
 
 
 def test_ctypes_struct_layout_matches_c(lib_built, tmp_path):
@@ -35,7 +35,7 @@ def test_ctypes_struct_layout_matches_c(lib_built, tmp_path):
              "b200sd_im2col_params": _lib.Im2colParams, "b200sd_upsample_params": _lib.UpsampleParams,
              "b200sd_cfg_sched_params": _lib.CfgSchedParams, "b200sd_small_linear_params": _lib.SmallLinearParams,
              "b200sd_softmax_params": _lib.SoftmaxParams, "b200sd_denorm_u8_params": _lib.DenormU8Params,
-             "b200sd_cast_params": _lib.CastParams}
+             "b200sd_cast_params": _lib.CastParams, "b200sd_embed_params": _lib.EmbedParams}
     lines = ['#include <stdio.h>', '#include <stddef.h>', f'#include "{HEADER}"', "int main(void){"]
     for cname, cls in pairs.items():
         lines.append(f'printf("{cname} %zu\\n", sizeof({cname}));')
@@ -184,3 +184,16 @@ def test_stand_in_text_encoder_is_deterministic(lib_built):
     te = StandInTextEncoder(1024)
     a, b = te(["a cat", ""]), te(["a cat"])
     assert a.shape == (2, 77, 1024) and torch.equal(a[0], b[0]) and not torch.equal(a[0], a[1])
+
+
+def test_hash_tokenizer_frames_like_the_sd21_tokenizer(lib_built):
+    """placeholder tokenizer: BOS 49406, EOS 49407, pad id 0, 77 tokens, truncation; stable ids"""
+    from b200sd.clip import HashTokenizer
+    tk = HashTokenizer()
+    ids = tk(["a photo of an astronaut riding a horse on mars", "", "word " * 200])
+    assert ids.shape == (3, 77) and ids.dtype == torch.int64
+    assert ids[0, 0] == 49406 and ids[0, 11] == 49407 and (ids[0, 12:] == 0).all()
+    assert ids[1, :2].tolist() == [49406, 49407] and (ids[1, 2:] == 0).all()
+    assert ids[2, 0] == 49406 and ids[2, 76] == 49407 and (ids[2, 1:76] == ids[2, 1]).all()
+    assert torch.equal(ids, tk(["a photo of an astronaut riding a horse on mars", "", "word " * 200]))
+    assert int(ids.max()) < 49408 and int(ids.min()) >= 0

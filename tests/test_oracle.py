@@ -151,3 +151,42 @@ def test_golden_vectors():
     assert O.rel_l2(final, gold["ddim4_final_latents"]) < 1e-4
     assert O.rel_l2(img, gold["ddim4_image01"]) < 1e-4
     assert torch.equal(O.to_uint8(torch.tensor([0.0, 0.5, 1.0, 0.49803922])), torch.tensor([0, 128, 255, 127], dtype=torch.uint8))
+
+
+# ------------------------------------------------------------------------------------------------ text encoder (pinned)
+def test_clip_text_oracle_matches_transformers_golden():
+    """oracle/clip_text.py against the output of the real transformers.CLIPTextModel (tests/golden/make_clip_golden.py)"""
+    from safetensors.torch import load_file
+    from oracle import clip_text as C
+    g = load_file(str(Path(__file__).parent / "golden" / "clip_tiny.safetensors"))
+    cfg = C.tiny_clip_config()
+    sd = C.seeded_state_dict(cfg, int(g["weights_seed"][0]))
+    out = C.clip_text_forward(sd, cfg, g["input_ids"])
+    ref = g["last_hidden_state"]
+    assert out.shape == ref.shape == (3, 77, 128)
+    assert ((out - ref).norm() / ref.norm()).item() < 1e-5  # fp32 vs fp32, different op order only
+
+
+def test_clip_text_oracle_against_live_transformers_if_present():
+    """same check against transformers imported now (skipped where the package is absent)"""
+    transformers = pytest.importorskip("transformers")
+    from oracle import clip_text as C
+    cfg = C.tiny_clip_config()
+    hf = transformers.CLIPTextConfig(vocab_size=cfg.vocab_size, hidden_size=cfg.hidden_size,
+                                     intermediate_size=cfg.intermediate_size, num_hidden_layers=cfg.num_hidden_layers,
+                                     num_attention_heads=cfg.num_attention_heads, max_position_embeddings=77,
+                                     hidden_act="gelu", layer_norm_eps=cfg.layer_norm_eps, projection_dim=64)
+    model = transformers.CLIPTextModel(hf).eval()
+    sd = C.seeded_state_dict(cfg, 3)
+    model.load_state_dict(sd, strict=False)
+    ids = C.seeded_ids(cfg, 2, seed=9)[:, :33]  # a shorter sequence than the position table
+    with torch.no_grad():
+        ref = model(input_ids=ids)[0]
+    out = C.clip_text_forward(sd, cfg, ids)
+    assert ((out - ref).norm() / ref.norm()).item() < 1e-5
+
+
+def test_clip_text_param_count_is_sd21s():
+    from oracle import clip_text as C
+    n = sum(torch.Size(s).numel() for s in C.param_shapes(C.CLIPTextConfig()).values())
+    assert n == 340_387_840  # SURVEY.md 8c

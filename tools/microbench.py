@@ -79,4 +79,27 @@ for kind in ("ddim", "dpm++2m"):
     ms = timed(fn, 5)
     out[f"config1_512_20steps_{kind}"] = {"ms_per_image": round(ms, 2), "images_per_s": round(1e3 / ms, 3),
                                           "tflops": round(34.685 / (ms * 1e-3), 1)}
+
+# ---- (iv) text encoder at the SD2.1 size: 32 prompts (16 conditional + 16 unconditional rows of one batch-16 pass)
+cfgc = b200sd.CLIPTextConfig()
+g = torch.Generator("cpu").manual_seed(0)
+shapes = {"text_model.embeddings.token_embedding.weight": (cfgc.vocab_size, 1024),
+          "text_model.embeddings.position_embedding.weight": (77, 1024),
+          "text_model.final_layer_norm.weight": (1024,), "text_model.final_layer_norm.bias": (1024,)}
+for i in range(cfgc.num_hidden_layers):
+    p = f"text_model.encoder.layers.{i}."
+    for n in ("q_proj", "k_proj", "v_proj", "out_proj"):
+        shapes[p + f"self_attn.{n}.weight"], shapes[p + f"self_attn.{n}.bias"] = (1024, 1024), (1024,)
+    for n in ("layer_norm1", "layer_norm2"):
+        shapes[p + n + ".weight"], shapes[p + n + ".bias"] = (1024,), (1024,)
+    shapes[p + "mlp.fc1.weight"], shapes[p + "mlp.fc1.bias"] = (4096, 1024), (4096,)
+    shapes[p + "mlp.fc2.weight"], shapes[p + "mlp.fc2.bias"] = (1024, 4096), (1024,)
+sdc = {k: (torch.randn(v, generator=g) * (v[-1] ** -0.5 if len(v) == 2 else 0.1) + (1.0 if k.endswith("norm1.weight") or k.endswith("norm2.weight") or k.endswith("layer_norm.weight") else 0.0))
+       for k, v in shapes.items()}
+enc = b200sd.B200CLIPTextEncoder(sdc, cfgc, dev)
+ids = torch.randint(0, cfgc.vocab_size, (32, 77), generator=g).to(dev)
+ms = timed(lambda: enc.encode(ids), 10)
+flop = 32 * 77 * cfgc.num_hidden_layers * 2 * (4 * 1024 * 1024 + 2 * 1024 * 4096) + 32 * 16 * cfgc.num_hidden_layers * 4 * 77 * 77 * 64
+out["clip_text_b32"] = {"ms": round(ms, 3), "prompts_per_s": round(32 / (ms * 1e-3), 1), "tflops": round(flop / (ms * 1e-3) / 1e12, 1),
+                        "note": "eager launches (no CUDA graph): 23 layers x 7 kernels"}
 print(json.dumps(out))
