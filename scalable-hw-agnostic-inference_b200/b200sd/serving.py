@@ -119,6 +119,135 @@ class Engine:
         return image, str(time.time() - t0)
 
 
+# ---------------------------------------------------------------------------------------------------- batching
+class _Pending:
+    __slots__ = ("prompt", "steps", "event", "image", "error", "t_enqueue", "t_done")
+
+    def __init__(self, prompt: str, steps: int):
+        self.prompt, self.steps = prompt, steps
+        self.event = threading.Event()
+        self.image = self.error = None
+        self.t_enqueue, self.t_done = time.time(), None
+
+
+class BatchingEngine(Engine):
+    """dynamic batching in front of one GPU + PNG work off the GPU thread.
+
+    The reference serves one prompt per `pipe(...)` call from sync FastAPI handlers that share a stateful scheduler
+    without a lock (app/run-sd.py:137-142, 184-193).  Here handlers enqueue; one worker thread per GPU drains up to
+    `max_batch` requests that ask for the same step count (waiting at most `max_wait_ms` for the batch to fill), runs
+    ONE pipeline call with `output_type="uint8"` (K7 on the device, 4x less D2H than fp32) and hands each uint8 image
+    to a thread pool that builds the PIL image / PNG, so encoding overlaps the next batch on the GPU."""
+
+    def __init__(self, pipe, default_steps: int, max_batch: int = 16, max_wait_ms: float = 5.0, png_workers: int = 4):
+        super().__init__(pipe, default_steps)
+        from concurrent.futures import ThreadPoolExecutor
+        import queue
+        self.max_batch, self.max_wait_s = max_batch, max_wait_ms / 1e3
+        self._q: "queue.Queue[_Pending]" = queue.Queue()
+        self._pool = ThreadPoolExecutor(max_workers=png_workers, thread_name_prefix="b200sd-png")
+        self.batches: List[int] = []  # sizes of the batches run so far (observability / tests)
+        self._stop = False
+        self._worker = threading.Thread(target=self._run, name="b200sd-batcher", daemon=True)
+        self._worker.start()
+
+    @property
+    def queue_depth(self) -> int:
+        return self._q.qsize()
+
+    def close(self):
+        self._stop = True
+        self._q.put(None)  # type: ignore[arg-type]
+        self._worker.join(timeout=5)
+        self._pool.shutdown(wait=False)
+
+    def _take_batch(self) -> List[_Pending]:
+        import queue
+        first = self._q.get()
+        if first is None:
+            return []
+        batch, deadline, later = [first], time.time() + self.max_wait_s, []
+        while len(batch) < self.max_batch:
+            try:
+                nxt = self._q.get(timeout=max(0.0, deadline - time.time()))
+            except queue.Empty:
+                break
+            if nxt is None:
+                self._stop = True
+                break
+            (batch if nxt.steps == first.steps else later).append(nxt)
+        for r in later:  # different step count: next batch
+            self._q.put(r)
+        return batch
+
+    def _run(self):
+        while not self._stop:
+            batch = self._take_batch()
+            if not batch:
+                continue
+            self.batches.append(len(batch))
+            try:
+                with self._lock:
+                    out = self.pipe(prompt=[r.prompt for r in batch], num_inference_steps=batch[0].steps,
+                                    output_type="uint8").images
+                arr = out.cpu().numpy() if hasattr(out, "cpu") else out
+                for r, a in zip(batch, arr):
+                    self._pool.submit(self._finish, r, a)
+            except Exception as e:  # every waiter of the batch sees the failure (HTTP 500 in the handler)
+                for r in batch:
+                    r.error = e
+                    r.event.set()
+
+    @staticmethod
+    def _finish(r: _Pending, arr):
+        try:
+            from PIL import Image
+            r.image = Image.fromarray(arr)
+        except Exception as e:
+            r.error = e
+        r.t_done = time.time()
+        r.event.set()
+
+    def submit(self, prompt: str, steps: Optional[int] = None) -> _Pending:
+        r = _Pending(prompt, steps or self.default_steps)
+        self._q.put(r)
+        return r
+
+    def text2img(self, prompt: str, steps: Optional[int] = None):
+        r = self.submit(prompt, steps)
+        r.event.wait()
+        if r.error is not None:
+            raise r.error
+        return r.image, str(r.t_done - r.t_enqueue)
+
+
+class Dispatcher:
+    """One engine per GPU of the box, requests go to the engine with the shortest queue (ties: round-robin): the in-box
+    analogue of the reference's N one-GPU pods behind ALB round-robin (sd21-equal-routing-ing.yaml:33).  No collective."""
+
+    def __init__(self, engines: List[Engine]):
+        if not engines:
+            raise ValueError("Dispatcher needs at least one engine")
+        self.engines, self.default_steps = list(engines), engines[0].default_steps
+        self._rr, self._lock = 0, threading.Lock()
+        self.routed = [0] * len(engines)
+
+    def pick(self) -> int:
+        with self._lock:
+            n = len(self.engines)
+            order = [(self._rr + i) % n for i in range(n)]
+            best = min(order, key=lambda i: getattr(self.engines[i], "queue_depth", 0))
+            self._rr = (best + 1) % n
+            self.routed[best] += 1
+            return best
+
+    def text2img(self, prompt: str, steps: Optional[int] = None):
+        return self.engines[self.pick()].text2img(prompt, steps)
+
+    def __call__(self, **model_args):
+        return self.engines[self.pick()](**model_args)
+
+
 def build_random_init_pipeline(model_id: str, device: str = "cuda:0", seed: int = 0):
     """There are no checkpoints on this box (no network): builds the SD2.1 architecture named by `model_id`
     (`...-base` = 512^2 epsilon-prediction, otherwise 768^2 v-prediction) with seeded random weights.
@@ -134,7 +263,27 @@ def build_random_init_pipeline(model_id: str, device: str = "cuda:0", seed: int 
     usd, vsd = random_state_dicts(ucfg, VAEConfig(), seed)
     dev = torch.device(device)
     unet, vae = B200UNet(usd, ucfg, dev), B200VAEDecoder(vsd, VAEConfig(), dev)
-    return B200Pipeline(unet, vae, B200Scheduler("ddim", ucfg.prediction_type, dev))
+    text = None
+    if os.environ.get("B200SD_TEXT_ENCODER", "clip") == "clip":
+        # the SD2.1 text tower with seeded weights in transformers' layout + the placeholder tokenizer (no vocabulary here)
+        from .clip import B200CLIPTextEncoder, CLIPTextConfig, PromptEncoder
+        ccfg = CLIPTextConfig()
+        g = torch.Generator("cpu").manual_seed(seed + 2)
+        c, f = ccfg.hidden_size, ccfg.intermediate_size
+        csd = {"text_model.embeddings.token_embedding.weight": torch.randn(ccfg.vocab_size, c, generator=g),
+               "text_model.embeddings.position_embedding.weight": 0.1 * torch.randn(ccfg.max_position_embeddings, c, generator=g),
+               "text_model.final_layer_norm.weight": torch.ones(c), "text_model.final_layer_norm.bias": torch.zeros(c)}
+        for i in range(ccfg.num_hidden_layers):
+            q = f"text_model.encoder.layers.{i}."
+            for n in ("q_proj", "k_proj", "v_proj", "out_proj"):
+                csd[q + f"self_attn.{n}.weight"] = torch.randn(c, c, generator=g) * c ** -0.5
+                csd[q + f"self_attn.{n}.bias"] = torch.zeros(c)
+            for n in ("layer_norm1", "layer_norm2"):
+                csd[q + n + ".weight"], csd[q + n + ".bias"] = torch.ones(c), torch.zeros(c)
+            csd[q + "mlp.fc1.weight"], csd[q + "mlp.fc1.bias"] = torch.randn(f, c, generator=g) * c ** -0.5, torch.zeros(f)
+            csd[q + "mlp.fc2.weight"], csd[q + "mlp.fc2.bias"] = torch.randn(c, f, generator=g) * f ** -0.5, torch.zeros(c)
+        text = PromptEncoder(B200CLIPTextEncoder(csd, ccfg, dev))
+    return B200Pipeline(unet, vae, B200Scheduler("ddim", ucfg.prediction_type, dev), text_encoder=text)
 
 
 def create_app(engine: Engine, cfg: Dict[str, str], sink: Optional[MetricSink] = None):
@@ -204,11 +353,19 @@ def create_app_from_env():
     cfg = read_env()
     if cfg["DEVICE"] not in ("b200", "cuda"):
         raise RuntimeError(f"DEVICE={cfg['DEVICE']!r}: this host serves DEVICE=b200 (sm_100a) only")
-    pipe = build_random_init_pipeline(cfg["MODEL_ID"], os.environ.get("B200SD_CUDA_DEVICE", "cuda:0"))
-    pipe.enable_attention_slicing()
-    engine = Engine(pipe, cfg["NUM_OF_RUNS_INF"])
-    engine(prompt=WARMUP_PROMPT, num_inference_steps=cfg["NUM_OF_RUNS_INF"])  # readiness only after warm-up
-    return create_app(engine, cfg)
+    # B200SD_GPUS=N serves N replicas (cuda:0..N-1) behind one Dispatcher; each replica batches up to B200SD_MAX_BATCH
+    # concurrent requests into one pipeline call.  Defaults: 1 GPU (B200SD_CUDA_DEVICE), batch 16.
+    n_gpus = int(os.environ.get("B200SD_GPUS", "1"))
+    devices = [os.environ.get("B200SD_CUDA_DEVICE", "cuda:0")] if n_gpus == 1 else [f"cuda:{i}" for i in range(n_gpus)]
+    engines = []
+    for d in devices:
+        pipe = build_random_init_pipeline(cfg["MODEL_ID"], d)
+        pipe.enable_attention_slicing()
+        eng = BatchingEngine(pipe, cfg["NUM_OF_RUNS_INF"], max_batch=int(os.environ.get("B200SD_MAX_BATCH", "16")),
+                             max_wait_ms=float(os.environ.get("B200SD_BATCH_WAIT_MS", "5")))
+        eng(prompt=WARMUP_PROMPT, num_inference_steps=cfg["NUM_OF_RUNS_INF"])  # readiness only after warm-up
+        engines.append(eng)
+    return create_app(engines[0] if len(engines) == 1 else Dispatcher(engines), cfg)
 
 
 # ---------------------------------------------------------------------------------------------------- sharding

@@ -197,3 +197,88 @@ def test_hash_tokenizer_frames_like_the_sd21_tokenizer(lib_built):
     assert ids[2, 0] == 49406 and ids[2, 76] == 49407 and (ids[2, 1:76] == ids[2, 1]).all()
     assert torch.equal(ids, tk(["a photo of an astronaut riding a horse on mars", "", "word " * 200]))
     assert int(ids.max()) < 49408 and int(ids.min()) >= 0
+
+
+# ------------------------------------------------------------------------------------------------ batcher / dispatcher
+class _FakePipe:
+    """stands in for B200Pipeline on the CPU: returns one uint8 image per prompt whose pixels encode the prompt"""
+
+    def __init__(self, delay=0.0):
+        self.calls, self.delay = [], delay
+
+    def __call__(self, prompt, num_inference_steps, output_type="uint8"):
+        import time
+        from types import SimpleNamespace
+        time.sleep(self.delay)
+        self.calls.append((list(prompt), num_inference_steps, output_type))
+        imgs = torch.stack([torch.full((8, 8, 3), len(p) % 256, dtype=torch.uint8) for p in prompt])
+        return SimpleNamespace(images=imgs)
+
+
+def test_batching_engine_groups_requests_and_returns_each_callers_image(lib_built):
+    import threading
+    from b200sd.serving import BatchingEngine
+    pipe = _FakePipe(delay=0.05)
+    eng = BatchingEngine(pipe, default_steps=25, max_batch=4, max_wait_ms=200.0, png_workers=2)
+    try:
+        prompts = ["a" * n for n in range(1, 11)]
+        results = {}
+
+        def worker(p):
+            img, latency = eng.text2img(p)
+            results[p] = (img, float(latency))
+
+        ts = [threading.Thread(target=worker, args=(p,)) for p in prompts]
+        [t.start() for t in ts]
+        [t.join(timeout=20) for t in ts]
+        assert len(results) == 10
+        for p, (img, lat) in results.items():
+            assert img.size == (8, 8) and img.getpixel((0, 0)) == (len(p),) * 3 and lat >= 0  # the caller's own image
+        assert sum(eng.batches) == 10 and max(eng.batches) <= 4 and len(eng.batches) < 10  # really batched
+        assert all(c[1] == 25 and c[2] == "uint8" for c in pipe.calls)
+        # a different step count never shares a batch
+        r1, r2 = eng.submit("x", 10), eng.submit("yy", 20)
+        r1.event.wait(10), r2.event.wait(10)
+        assert {c[1] for c in pipe.calls[-2:]} == {10, 20}
+    finally:
+        eng.close()
+
+
+def test_batching_engine_propagates_pipeline_errors(lib_built):
+    from b200sd.serving import BatchingEngine
+
+    def boom(**_k):
+        raise ValueError("no device")
+
+    eng = BatchingEngine(boom, default_steps=5, max_batch=2, max_wait_ms=1.0)
+    try:
+        with pytest.raises(ValueError, match="no device"):
+            eng.text2img("p")
+    finally:
+        eng.close()
+
+
+def test_dispatcher_prefers_the_shortest_queue_and_round_robins_ties(lib_built):
+    from b200sd.serving import Dispatcher
+
+    class E:
+        default_steps = 25
+
+        def __init__(self):
+            self.queue_depth, self.seen = 0, []
+
+        def text2img(self, prompt, steps=None):
+            self.seen.append(prompt)
+            return prompt, "0"
+
+    es = [E(), E(), E()]
+    d = Dispatcher(es)
+    for i in range(6):
+        d.text2img(f"p{i}")
+    assert d.routed == [2, 2, 2]                       # ties: round-robin
+    es[0].queue_depth, es[1].queue_depth = 5, 3
+    for i in range(4):
+        d.text2img(f"q{i}")
+    assert d.routed == [2, 2, 6]                       # the idle engine takes the new work
+    with pytest.raises(ValueError):
+        Dispatcher([])
