@@ -61,9 +61,13 @@ struct GemmKernelParams {
                    //    leaves with one TMA store per 32x32 chunk: no shared-memory read-back on the epilogue's chain
 };
 
-template <int BLOCK_N>
+// PAIR: two CTAs (one cluster) share a 256-row tile through tcgen05.mma.cta_group::2; each CTA stages its own 128 rows
+// of A and only HALF of the weight tile, so the per-SM L2 traffic per k-block drops from (128 + N) to (128 + N/2) rows
+// of 128 bytes.  Measured before: every tile width moved 55-70 B/clk/SM from L2 whatever the shape -- the operand
+// fetch, not the tensor pipe, set the speed of the big convolutions.
+template <int BLOCK_N, bool PAIR = false>
 struct GemmCfg {
-    static constexpr int B_TILE_BYTES = BLOCK_N * 128;
+    static constexpr int B_TILE_BYTES = (PAIR ? BLOCK_N / 2 : BLOCK_N) * 128;
     static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
     static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
     // operand ring | barriers | per-tile column bias (2 x 256 fp32) | one 32x32 fp32 staging tile per epilogue warp.
@@ -301,11 +305,11 @@ __device__ __forceinline__ void add_col_bias32(const GemmKernelParams& p, float 
     }
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool PAIR>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
     gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmOut, const GemmKernelParams p) {
-    using Cfg = GemmCfg<BLOCK_N>;
+    using Cfg = GemmCfg<BLOCK_N, PAIR>;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     // SWIZZLE_128B tiles need 1024-byte alignment in the shared address space
@@ -333,19 +337,34 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(&tmem_full[s], 1);
-            mbar_init(&tmem_empty[s], EPI_WARPS);
+            mbar_init(&tmem_empty[s], PAIR ? 2 * EPI_WARPS : EPI_WARPS);  // pair: both CTAs' epilogues report to the leader
         }
         fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc(tmem_base_slot, TMEM_COLS);
+    if (warp == 2) {
+        if (PAIR) tmem_alloc_pair(tmem_base_slot, TMEM_COLS);
+        else tmem_alloc(tmem_base_slot, TMEM_COLS);
+    }
     tc_fence_before();
-    __syncthreads();
+    if (PAIR) cluster_sync_all();  // the peer's barriers exist before anything is signalled across the pair
+    else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_base_slot;
 
     const int splits = p.splits;
-    const int total_work = p.m_tiles * p.n_tiles * splits;  // work item w = tile * splits + split
     const int num_kb = p.taps * p.kb_per_tap;
+    // Work items.  Single CTA: w = tile * splits + split, tile = m_tile * n_tiles + n_tile.  Pair: w = pair tile, the
+    // two CTAs take m_tile = 2 * (w / n_tiles) + rank of the same n_tile.
+    const int rank = PAIR ? (int)cluster_ctarank() : 0;
+    const int w_first = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int w_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    const int total_work = PAIR ? ((p.m_tiles + 1) / 2) * p.n_tiles : p.m_tiles * p.n_tiles * splits;
+    auto m_tile_of = [&](int t) { return PAIR ? 2 * (t / p.n_tiles) + rank : t / p.n_tiles; };
+    // columns the UMMA of n_tile computes (pair mode narrows the last tile instead of multiplying zeros)
+    auto n_this_of = [&](int n_tile) {
+        const int left = p.n_out - n_tile * BLOCK_N;
+        return left >= BLOCK_N ? BLOCK_N : ((left + 31) / 32) * 32;
+    };
 
     // Warps 0 and 1 keep all 32 lanes in the (warp-uniform) control flow and predicate only the asynchronous
     // instructions on one elected lane.  Run from inside an `if (lane == 0)` region instead, every TMA / UMMA operand
@@ -360,10 +379,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         const bool res_l2_prefetch =
             p.residual != nullptr && splits == 1 && !p.geglu &&
             ((reinterpret_cast<uintptr_t>(p.residual) | (uintptr_t)(p.ld_res * res_esz)) & 15) == 0;
-        for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        for (int w = w_first; w < total_work; w += w_step) {
             const int t = w / splits, split = w - t * splits;
             const int n_tile = t % p.n_tiles;
-            const int m_tile = t / p.n_tiles;
+            const int m_tile = m_tile_of(t);
             const int tx = m_tile % p.tiles_x;
             const int ty = (m_tile / p.tiles_x) % p.tiles_y;
             const int tn = m_tile / (p.tiles_x * p.tiles_y);
@@ -404,9 +423,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                 uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
                 uint8_t* sb = sa + A_TILE_BYTES;
                 if (elect_one()) {
-                    mbar_expect_tx(&full_bar[stage], p.a_box_bytes + Cfg::B_TILE_BYTES);
-                    tma_load_4d(sa, &tmA, &full_bar[stage], c0, x0 + dx, y0 + dy, n0);
-                    tma_load_2d(sb, &tmB, &full_bar[stage], tap * p.cin + c0, n_tile * BLOCK_N);
+                    if (PAIR) {
+                        // both CTAs' bytes are counted on the leader's barrier; each CTA brings its half of the weight rows
+                        if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * (p.a_box_bytes + Cfg::B_TILE_BYTES));
+                        tma_load_4d_pair(sa, &tmA, &full_bar[stage], c0, x0 + dx, y0 + dy, n0);
+                        tma_load_2d_pair(sb, &tmB, &full_bar[stage], tap * p.cin + c0,
+                                         n_tile * BLOCK_N + rank * (n_this_of(n_tile) >> 1));
+                    } else {
+                        mbar_expect_tx(&full_bar[stage], p.a_box_bytes + Cfg::B_TILE_BYTES);
+                        tma_load_4d(sa, &tmA, &full_bar[stage], c0, x0 + dx, y0 + dy, n0);
+                        tma_load_2d(sb, &tmB, &full_bar[stage], tap * p.cin + c0, n_tile * BLOCK_N);
+                    }
                 }
                 __syncwarp();
                 if (++stage == STAGES) {
@@ -415,18 +442,19 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                 }
             }
         }
-    } else if (warp == 1) {
-        // ------------------------------------------------------------------ UMMA issuer
-        const uint32_t idesc = umma_idesc(BLOCK_M, BLOCK_N, (uint32_t)p.a_bf16, (uint32_t)p.b_bf16);
+    } else if (warp == 1 && rank == 0) {
+        // ------------------------------------------------------------------ UMMA issuer (pair: the leader CTA only)
+        uint32_t idesc = umma_idesc(BLOCK_M, BLOCK_N, (uint32_t)p.a_bf16, (uint32_t)p.b_bf16);
         const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
         const uint32_t smem_u = __shfl_sync(0xffffffffu, smem_u32(smem), 0);
         int stage = 0;
         uint32_t phase = 0;
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        for (int w = w_first; w < total_work; w += w_step) {
             const int split = w % splits;
             const int nkb = (int)((long long)(split + 1) * num_kb / splits) - (int)((long long)split * num_kb / splits);
+            if (PAIR) idesc = umma_idesc(2 * BLOCK_M, n_this_of(w % p.n_tiles), (uint32_t)p.a_bf16, (uint32_t)p.b_bf16);
             mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
             tc_fence_after();
             const uint32_t d_tmem = tmem_u + acc * ACC_STRIDE;
@@ -440,10 +468,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 #pragma unroll
                     for (int k = 0; k < BLOCK_K / 16; ++k) {
                         // +32 bytes along K inside the 128-byte swizzle row = +2 in the (addr >> 4) field
-                        umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                        if (PAIR) umma_bf16_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                        else umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
                     }
-                    umma_commit(&empty_bar[stage]);
-                    if (kb == nkb - 1) umma_commit(&tmem_full[acc]);
+                    if (PAIR) {
+                        // the stage is free, and the accumulator ready, in BOTH CTAs
+                        umma_commit_pair(&empty_bar[stage], 0b11);
+                        if (kb == nkb - 1) umma_commit_pair(&tmem_full[acc], 0b11);
+                    } else {
+                        umma_commit(&empty_bar[stage]);
+                        if (kb == nkb - 1) umma_commit(&tmem_full[acc]);
+                    }
                 }
                 __syncwarp();
                 if (++stage == STAGES) {
@@ -454,7 +489,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
         }
-    } else {
+    } else if (warp >= 2) {
         // ------------------------------------------------------------------ epilogue (warps 2..9)
         // The epilogue is bound by bytes in flight (residual reads) or by ALU work (GEGLU), not by TMEM bandwidth, so
         // two warps share each lane quadrant: warp group `eg` takes the 32-column chunks c = eg, eg + 2, ...
@@ -477,13 +512,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
             const int col = ((w / splits) % p.n_tiles) * BLOCK_N + et;
             return (col_bias && et < BLOCK_N && w < total_work && col < p.n_out) ? __ldg(p.bias + col) : 0.f;
         };
-        float bias_cur = bias_fetch(blockIdx.x);
+        float bias_cur = bias_fetch(w_first);
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        for (int w = w_first; w < total_work; w += w_step) {
             const int t = w / splits;
             const int n_tile = t % p.n_tiles;
-            const int m_tile = t / p.n_tiles;
+            const int m_tile = m_tile_of(t);
             const int tx = m_tile % p.tiles_x;
             const int ty = (m_tile / p.tiles_x) % p.tiles_y;
             const int tn = m_tile / (p.tiles_x * p.tiles_y);
@@ -496,7 +531,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
             // column bias of this tile -> shared memory (read back as broadcasts); double-buffered with the accumulator
             float* bs = bias_s + acc * 256;
             if (et < BLOCK_N) bs[et] = bias_cur;
-            bias_cur = bias_fetch(w + gridDim.x);
+            bias_cur = bias_fetch(w + w_step);
             // rows this lane handles in the transposed (staged) mapping
             const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
             int mt[8];
@@ -530,7 +565,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                 }
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+                if (lane == 0) { if (PAIR) mbar_arrive_leader(&tmem_empty[acc]); else mbar_arrive(&tmem_empty[acc]); }
                 named_bar_sync(1, 32 * EPI_WARPS);  // all 128 rows of the partial tile are written ...
                 if (row_in_tile == 0 && eg == 0) {
                     __threadfence();     // ... and (fence cumulativity) visible device-wide before the count goes up
@@ -612,7 +647,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                             } else {
                                 tc_fence_before();
                                 __syncwarp();
-                                if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+                                if (lane == 0) { if (PAIR) mbar_arrive_leader(&tmem_empty[acc]); else mbar_arrive(&tmem_empty[acc]); }
                             }
                             fence_proxy_async_smem();
                             __syncwarp();
@@ -645,7 +680,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                         } else {
                             tc_fence_before();
                             __syncwarp();
-                            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+                            if (lane == 0) { if (PAIR) mbar_arrive_leader(&tmem_empty[acc]); else mbar_arrive(&tmem_empty[acc]); }
                         }
                         __syncwarp();
                         if (full) {
@@ -658,7 +693,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                     if (eg >= NC) {  // BLOCK_N = 32 * odd: the second warp group may have no chunk at all
                         tc_fence_before();
                         __syncwarp();
-                        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+                        if (lane == 0) { if (PAIR) mbar_arrive_leader(&tmem_empty[acc]); else mbar_arrive(&tmem_empty[acc]); }
                     }
                 } else {
                     constexpr int HALF = BLOCK_N / 2;
@@ -685,7 +720,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                         } else {
                             tc_fence_before();
                             __syncwarp();
-                            if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+                            if (lane == 0) { if (PAIR) mbar_arrive_leader(&tmem_empty[acc]); else mbar_arrive(&tmem_empty[acc]); }
                         }
                         const int col0 = n_tile * HALF + c * 32;
                         if (tma) {
@@ -716,8 +751,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     }
 
     tc_fence_before();
-    __syncthreads();
-    if (warp == 2) tmem_dealloc(tmem_base, TMEM_COLS);
+    if (PAIR) cluster_sync_all();  // neither CTA frees TMEM or exits while the other may still signal it
+    else __syncthreads();
+    if (warp == 2) {
+        if (PAIR) tmem_dealloc_pair(tmem_base, TMEM_COLS);
+        else tmem_dealloc(tmem_base, TMEM_COLS);
+    }
 }
 
 // ------------------------------------------------------------------------------------------ host side
@@ -814,21 +853,54 @@ static int32_t launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BLOCK_N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::SMEM_BYTES);
         if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "gemm smem attribute: %s", cudaGetErrorString(e));
         attr_set[dev] = true;
     }
     long long total = (long long)kp.m_tiles * kp.n_tiles * kp.splits;
     int grid = (int)(total < num_sms() ? total : num_sms());
-    gemm_kernel<BLOCK_N><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmOut, kp);
+    gemm_kernel<BLOCK_N, false><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmOut, kp);
     count_launch();
     B200SD_CHECK_LAUNCH("gemm_kernel");
     return B200SD_OK;
 }
 
+// CTA-pair variant (BLOCK_N = 256, tcgen05.mma.cta_group::2): launched as 2-CTA clusters
+static int32_t launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut,
+                                const GemmKernelParams& kp, cudaStream_t stream) {
+    using Cfg = GemmCfg<256, true>;
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_kernel<256, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "gemm (pair) smem attribute: %s", cudaGetErrorString(e));
+        attr_set[dev] = true;
+    }
+    const long long pairs = (long long)((kp.m_tiles + 1) / 2) * kp.n_tiles;
+    const int max_clusters = num_sms() / 2;
+    const int clusters = (int)(pairs < max_clusters ? pairs : max_clusters);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * clusters, 1, 1);
+    cfg.blockDim = dim3(GEMM_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2, attr[0].val.clusterDim.y = 1, attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr, cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_kernel<256, true>, tmA, tmB, tmOut, kp);
+    if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "gemm (pair) launch: %s", cudaGetErrorString(e));
+    count_launch();
+    B200SD_CHECK_LAUNCH("gemm_kernel<pair>");
+    return B200SD_OK;
+}
+
 struct GemmPlan {
     GemmKernelParams kp;
+    int pair;  // 1: CTA-pair kernel (block_n = 256)
     int block_n;
     int64_t ws_bytes;
 };
@@ -863,6 +935,18 @@ static int32_t make_plan(const b200sd_gemm_params* p, bool have_ws, GemmPlan* pl
                          "gemm: GEGLU needs block_n in {128,256} dividing n_out (%d)", p->n_out);
         B200SD_CHECK_ARG(!p->bias_along_m, "gemm: GEGLU with bias_along_m is not supported");
     }
+    // CTA pairs: wide outputs with enough 256-row tiles to fill the machine; B200SD_GEMM_PAIR=0 switches them off
+    static const char* pair_env = getenv("B200SD_GEMM_PAIR");
+    const bool pair_allowed = !(pair_env && pair_env[0] == '0');
+    const bool wide = kp.geglu ? (p->n_out % 256 == 0) : (p->n_out >= 512 || p->n_out % 256 == 0);
+    const long long pair_tiles = (long long)((kp.m_tiles + 1) / 2) * ((p->n_out + 255) / 256);
+    // ... and long enough to pay for the cluster start-up: at least one full wave of clusters and >= 64 k-blocks per
+    // cluster in total (measured at batch 1: launches of 20-50 us lost 1-5 us each as pairs, the long ones gained 10-18 %)
+    const long long clusters = num_sms() / 2;
+    const long long num_kb_total = (long long)p->taps * kp.kb_per_tap;
+    plan->pair = (pair_allowed && wide && splits == 1 && (p->block_n == 0 || p->block_n == 256) && kp.m_tiles >= 2 &&
+                  pair_tiles >= clusters && pair_tiles * num_kb_total >= 64 * clusters) ? 1 : 0;
+    if (plan->pair) block_n = 256;
     kp.n_tiles = (p->n_out + block_n - 1) / block_n;
     kp.splits = splits;
     plan->block_n = block_n;
@@ -967,7 +1051,7 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
         const uint64_t k_total = (uint64_t)p->taps * p->cin;
         uint64_t dims[2] = {k_total, (uint64_t)p->n_out};
         uint64_t strides[1] = {k_total * 2};
-        uint32_t box[2] = {BLOCK_K, (uint32_t)block_n};
+        uint32_t box[2] = {BLOCK_K, (uint32_t)(plan.pair ? 128 : block_n)};  // a pair's CTA stages half of the tile's rows
         int32_t r = encode_tmap_bf16(&tmB, p->w, 2, dims, strides, box);
         if (r) return r;
     }
@@ -979,6 +1063,7 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
         if (r) return r;
     }
     cudaStream_t s = as_stream(stream);
+    if (plan.pair) return launch_gemm_pair(tmA, tmB, tmOut, kp, s);
     switch (block_n) {
         case 64: return launch_gemm<64>(tmA, tmB, tmOut, kp, s);
         case 128: return launch_gemm<128>(tmA, tmB, tmOut, kp, s);
