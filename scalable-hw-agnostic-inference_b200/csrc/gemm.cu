@@ -508,9 +508,19 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         const int lx = row_in_tile - ln * box_pix - ly * p.bw;
         // the column bias of a tile is fetched one tile ahead (one value per epilogue thread)
         const bool col_bias = p.bias != nullptr && !p.bias_along_m;
+        // (a per-image row bias joins it when every tile lies inside one image -- the staged epilogue then needs no
+        // per-row lookup; fast_epi is only set with a row bias if bn == 1)
+        const bool row_bias_in_tile = fast && p.row_bias != nullptr;
         auto bias_fetch = [&](int w) -> float {
-            const int col = ((w / splits) % p.n_tiles) * BLOCK_N + et;
-            return (col_bias && et < BLOCK_N && w < total_work && col < p.n_out) ? __ldg(p.bias + col) : 0.f;
+            const int t2 = w / splits;
+            const int col = (t2 % p.n_tiles) * BLOCK_N + et;
+            if (!(et < BLOCK_N && w < total_work && col < p.n_out)) return 0.f;
+            float b = col_bias ? __ldg(p.bias + col) : 0.f;
+            if (row_bias_in_tile) {
+                const int img = m_tile_of(t2) / (p.tiles_x * p.tiles_y);
+                if (img < p.n_img) b += __ldg(p.row_bias + (long long)img * p.row_bias_stride + col);
+            }
+            return b;
         };
         float bias_cur = bias_fetch(w_first);
         int acc = 0;
@@ -866,15 +876,16 @@ static int32_t launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const
     return B200SD_OK;
 }
 
-// CTA-pair variant (BLOCK_N = 256, tcgen05.mma.cta_group::2): launched as 2-CTA clusters
+// CTA-pair variant (tcgen05.mma.cta_group::2, 256 x BLOCK_N tiles): launched as 2-CTA clusters
+template <int BLOCK_N>
 static int32_t launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut,
                                 const GemmKernelParams& kp, cudaStream_t stream) {
-    using Cfg = GemmCfg<256, true>;
+    using Cfg = GemmCfg<BLOCK_N, true>;
     static bool attr_set[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_kernel<256, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BLOCK_N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::SMEM_BYTES);
         if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "gemm (pair) smem attribute: %s", cudaGetErrorString(e));
         attr_set[dev] = true;
@@ -891,7 +902,7 @@ static int32_t launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, 
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2, attr[0].val.clusterDim.y = 1, attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr, cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_kernel<256, true>, tmA, tmB, tmOut, kp);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_kernel<BLOCK_N, true>, tmA, tmB, tmOut, kp);
     if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "gemm (pair) launch: %s", cudaGetErrorString(e));
     count_launch();
     B200SD_CHECK_LAUNCH("gemm_kernel<pair>");
@@ -900,7 +911,7 @@ static int32_t launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, 
 
 struct GemmPlan {
     GemmKernelParams kp;
-    int pair;  // 1: CTA-pair kernel (block_n = 256)
+    int pair;  // 1: CTA-pair kernel (block_n = 256 or 160)
     int block_n;
     int64_t ws_bytes;
 };
@@ -939,14 +950,18 @@ static int32_t make_plan(const b200sd_gemm_params* p, bool have_ws, GemmPlan* pl
     static const char* pair_env = getenv("B200SD_GEMM_PAIR");
     const bool pair_allowed = !(pair_env && pair_env[0] == '0');
     const bool wide = kp.geglu ? (p->n_out % 256 == 0) : (p->n_out >= 512 || p->n_out % 256 == 0);
-    const long long pair_tiles = (long long)((kp.m_tiles + 1) / 2) * ((p->n_out + 255) / 256);
+    // 320 output channels (the 96x96 level) pair up on 160-column tiles
+    const bool wide160 = !kp.geglu && !wide && p->n_out >= 320 && p->n_out % 160 == 0;
+    const int pair_bn = wide160 ? 160 : 256;
+    const long long pair_tiles = (long long)((kp.m_tiles + 1) / 2) * ((p->n_out + pair_bn - 1) / pair_bn);
     // ... and long enough to pay for the cluster start-up: at least one full wave of clusters and >= 64 k-blocks per
     // cluster in total (measured at batch 1: launches of 20-50 us lost 1-5 us each as pairs, the long ones gained 10-18 %)
     const long long clusters = num_sms() / 2;
     const long long num_kb_total = (long long)p->taps * kp.kb_per_tap;
-    plan->pair = (pair_allowed && wide && splits == 1 && (p->block_n == 0 || p->block_n == 256) && kp.m_tiles >= 2 &&
+    plan->pair = (pair_allowed && (wide || wide160) && splits == 1 && (p->block_n == 0 || p->block_n == pair_bn) &&
+                  kp.m_tiles >= 2 &&
                   pair_tiles >= clusters && pair_tiles * num_kb_total >= 64 * clusters) ? 1 : 0;
-    if (plan->pair) block_n = 256;
+    if (plan->pair) block_n = pair_bn;
     kp.n_tiles = (p->n_out + block_n - 1) / block_n;
     kp.splits = splits;
     plan->block_n = block_n;
@@ -1024,7 +1039,8 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
         // staged (transposed) epilogue: column bias only, residual of the output's dtype; 16-byte alignment
         // of out / residual rows was checked above for n_cols >= 32
         const bool res_ok = !p->residual || p->residual_dtype == p->out_dtype;
-        kp.fast_epi = (n_cols >= 32 && !p->bias_along_m && !p->row_bias && res_ok) ? 1 : 0;
+        // (a row bias is folded into the tile's column bias when a tile never spans two images)
+        kp.fast_epi = (n_cols >= 32 && !p->bias_along_m && (!p->row_bias || kp.bn == 1) && res_ok) ? 1 : 0;
         // TMA-store epilogue: plain [M, n_cols] row-major output (linear layers), no residual, unsplit
         static const bool tma_off = getenv("B200SD_GEMM_NO_TMA_EPI") != nullptr;
         const int osz = p->out_dtype == B200SD_F32 ? 4 : 2;
@@ -1051,7 +1067,7 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
         const uint64_t k_total = (uint64_t)p->taps * p->cin;
         uint64_t dims[2] = {k_total, (uint64_t)p->n_out};
         uint64_t strides[1] = {k_total * 2};
-        uint32_t box[2] = {BLOCK_K, (uint32_t)(plan.pair ? 128 : block_n)};  // a pair's CTA stages half of the tile's rows
+        uint32_t box[2] = {BLOCK_K, (uint32_t)(plan.pair ? block_n / 2 : block_n)};  // a pair's CTA stages half of the tile's rows
         int32_t r = encode_tmap_bf16(&tmB, p->w, 2, dims, strides, box);
         if (r) return r;
     }
@@ -1063,7 +1079,8 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
         if (r) return r;
     }
     cudaStream_t s = as_stream(stream);
-    if (plan.pair) return launch_gemm_pair(tmA, tmB, tmOut, kp, s);
+    if (plan.pair)
+        return block_n == 160 ? launch_gemm_pair<160>(tmA, tmB, tmOut, kp, s) : launch_gemm_pair<256>(tmA, tmB, tmOut, kp, s);
     switch (block_n) {
         case 64: return launch_gemm<64>(tmA, tmB, tmOut, kp, s);
         case 128: return launch_gemm<128>(tmA, tmB, tmOut, kp, s);
