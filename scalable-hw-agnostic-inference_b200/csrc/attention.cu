@@ -59,6 +59,42 @@ __device__ __forceinline__ float exp2_poly(float x) {
     const float p = fmaf(fmaf(fmaf(0.055171668f, f, 0.24261112f), f, 0.69326099f), f, 0.99992807f);
     return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
 }
+// packed fp32 pairs (sm_100 FFMA2 / FADD2): the softmax warps are short of issue slots, not of FMA lanes
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+// exp2_poly on a pair, with the additions and the polynomial on FFMA2 / FADD2: 5 issue slots per value, no MUFU
+__device__ __forceinline__ void exp2_poly2(uint64_t x2, float& e0, float& e1) {
+    float x0, x1;
+    unpack2(x2, x0, x1);
+    x2 = pack2(fmaxf(x0, -30.f), fmaxf(x1, -30.f));
+    const uint64_t magic = pack2(12582912.f, 12582912.f), nmagic = pack2(-12582912.f, -12582912.f);
+    const uint64_t t2 = add2(x2, magic);                       // low mantissa bits = round(x)
+    const uint64_t f2 = fma2(add2(t2, nmagic), pack2(-1.f, -1.f), x2);  // x - round(x) in [-0.5, 0.5]
+    uint64_t p2 = fma2(pack2(0.055171668f, 0.055171668f), f2, pack2(0.24261112f, 0.24261112f));
+    p2 = fma2(p2, f2, pack2(0.69326099f, 0.69326099f));
+    p2 = fma2(p2, f2, pack2(0.99992807f, 0.99992807f));
+    float p0, p1, t0, t1;
+    unpack2(p2, p0, p1);
+    unpack2(t2, t0, t1);
+    e0 = __int_as_float(__float_as_int(p0) + (__float_as_int(t0) << 23));
+    e1 = __int_as_float(__float_as_int(p1) + (__float_as_int(t1) << 23));
+}
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
     float d;
     asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
@@ -88,7 +124,7 @@ __device__ __forceinline__ void tmem_st_x32(uint32_t taddr, const uint32_t (&r)[
         : "memory");
 }
 
-// EMU_MASK: bit i set = pair i of every four pairs of exponentials is evaluated by exp2_poly instead of the MUFU.
+// EMU_MASK: bit i set = pair i of every eight pairs of exponentials is evaluated by exp2_poly2 instead of the MUFU.
 template <bool F16, int EMU_MASK>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
     attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
@@ -318,24 +354,29 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                 // exponentials (registers only); they hide the tail of PV(j-1)
                 const float neg_m = -m_used;
                 uint32_t pk[32];
-                float ls0 = 0.f, ls1 = 0.f;
+                const uint64_t sc2 = pack2(sc, sc), negm2 = pack2(neg_m, neg_m);
+                uint64_t ls2 = pack2(0.f, 0.f);
 #pragma unroll
                 for (int c = 0; c < 2; ++c) {
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
                         // -inf * sc stays -inf (sc > 0) and both exponentials return 0 for it
-                        const float x0 = fmaf(__uint_as_float(s[c][2 * i]), sc, neg_m);
-                        const float x1 = fmaf(__uint_as_float(s[c][2 * i + 1]), sc, neg_m);
+                        const uint64_t x2 =
+                            fma2(pack2(__uint_as_float(s[c][2 * i]), __uint_as_float(s[c][2 * i + 1])), sc2, negm2);
                         float e0, e1;
-                        if ((EMU_MASK >> (i & 3)) & 1) {
-                            e0 = exp2_poly(x0), e1 = exp2_poly(x1);
+                        if ((EMU_MASK >> (i & 7)) & 1) {
+                            exp2_poly2(x2, e0, e1);
                         } else {
+                            float x0, x1;
+                            unpack2(x2, x0, x1);
                             e0 = ex2_ftz(x0), e1 = ex2_ftz(x1);
                         }
-                        ls0 += e0, ls1 += e1;
+                        ls2 = add2(ls2, pack2(e0, e1));
                         pk[c * 16 + i] = pack_h2(e0, e1, F16);
                     }
                 }
+                float ls0, ls1;
+                unpack2(ls2, ls0, ls1);
                 // PV(j-1) must be complete before P_t is overwritten or O_t rescaled
                 if (j > 0) {
                     mbar_wait(&pv_done[t], (j - 1) & 1);
@@ -420,7 +461,7 @@ static int emu_mask_from_env() {
     static int cached = -1;
     if (cached < 0) {
         const char* e = getenv("B200SD_ATTN_EXP_EMU");
-        cached = (e && e[0] == '1') ? 1 : 0;
+        cached = (e && e[0] >= '0' && e[0] <= '3') ? e[0] - '0' : 2;  // default: a quarter of the exponentials
     }
     return cached;
 }
@@ -470,10 +511,20 @@ extern "C" int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_str
     const int rows_per_cta = ATT_BM * ATT_QT;
     dim3 grid((p->sq + rows_per_cta - 1) / rows_per_cta, p->heads, p->batch);
     cudaStream_t s = as_stream(stream);
-    const bool emu = emu_mask_from_env() != 0;
-    if (p->dtype == B200SD_F16)
-        return emu ? launch_attention<true, 0b1010>(tmQ, tmK, tmV, kp, grid, s)
-                   : launch_attention<true, 0>(tmQ, tmK, tmV, kp, grid, s);
-    return emu ? launch_attention<false, 0b1010>(tmQ, tmK, tmV, kp, grid, s)
-               : launch_attention<false, 0>(tmQ, tmK, tmV, kp, grid, s);
+    // share of the exponentials evaluated on the FMA pipe instead of the MUFU: 0 none, 1 = 50 %, 2 = 25 %, 3 = 37.5 %
+    const int emu = emu_mask_from_env();
+    if (p->dtype == B200SD_F16) {
+        switch (emu) {
+            case 1: return launch_attention<true, 0b10101010>(tmQ, tmK, tmV, kp, grid, s);
+            case 2: return launch_attention<true, 0b10001000>(tmQ, tmK, tmV, kp, grid, s);
+            case 3: return launch_attention<true, 0b10010010>(tmQ, tmK, tmV, kp, grid, s);
+            default: return launch_attention<true, 0>(tmQ, tmK, tmV, kp, grid, s);
+        }
+    }
+    switch (emu) {
+        case 1: return launch_attention<false, 0b10101010>(tmQ, tmK, tmV, kp, grid, s);
+        case 2: return launch_attention<false, 0b10001000>(tmQ, tmK, tmV, kp, grid, s);
+        case 3: return launch_attention<false, 0b10010010>(tmQ, tmK, tmV, kp, grid, s);
+        default: return launch_attention<false, 0>(tmQ, tmK, tmV, kp, grid, s);
+    }
 }
