@@ -271,6 +271,10 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                 // that does not touch the MUFU (TMEM loads, row max, exchange, P store).  Started together they stay in
                 // step and fight over the MUFU, then leave it idle together; tile B's first Q K^T therefore waits until
                 // tile A has entered its first exponential phase, and the offset persists (the loops are self-paced).
+                // (Measured with clock stamps afterwards: per kv step a group spends ~1850 of ~2780 cycles in its
+                // exponentials whether or not the other group is in them too -- run strictly in turns, each phase still
+                // took ~1450 cycles, twice the MUFU time of its 2 warps per scheduler: the phase is bound by per-warp
+                // latency, and four warps in it at once fill the MUFU better than two.  So no hand-over barrier.)
                 bool go = j < kv_ready;
                 if (go && j == 0) go = (t == 0 || !p.stagger) || __all_sync(FULL, mbar_test_wait(b_go, 0));
                 else if (go) go = __all_sync(FULL, mbar_test_wait(&s_free[t], (j - 1) & 1));
@@ -307,25 +311,21 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&s_free[t]);
 
+                // Masking (ragged last kv tile, causal diagonal) touches every score, so it must stay OFF the common path:
+                // the guard is warp-uniform and the block holds a convergent __syncwarp, which keeps the compiler from
+                // flattening it into 128 unconditional compare+select pairs (measured: they were more instructions than
+                // the softmax itself).
                 const int valid = p.skv - j * ATT_BN - half * 64;  // live kv columns among this thread's 64
-                if (valid < 64) {
-                    // ragged last tile: dead columns get a score whose exponential is exactly 0
+                const int kbase = j * ATT_BN + half * 64;
+                const bool diag = p.causal && (kbase + 63 > q0 + t * ATT_BM + quad * 32);  // some lane of this warp is cut
+                if (valid < 64 || diag) {
+                    __syncwarp();
+                    const int qrow = p.causal ? q0 + t * ATT_BM + row : 0x7fffffff;
 #pragma unroll
                     for (int c = 0; c < 2; ++c)
 #pragma unroll
                         for (int i = 0; i < 32; ++i)
-                            if (c * 32 + i >= valid) s[c][i] = __float_as_uint(-INFINITY);
-                }
-                if (p.causal) {
-                    const int qrow = q0 + t * ATT_BM + row;
-                    const int kbase = j * ATT_BN + half * 64;
-                    if (kbase + 63 > qrow) {
-#pragma unroll
-                        for (int c = 0; c < 2; ++c)
-#pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                if (kbase + c * 32 + i > qrow) s[c][i] = __float_as_uint(-INFINITY);
-                    }
+                            if (c * 32 + i >= valid || kbase + c * 32 + i > qrow) s[c][i] = __float_as_uint(-INFINITY);
                 }
                 float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
