@@ -781,15 +781,18 @@ static void choose_box(int n_img, int h, int w, int* bw, int* bh, int* bn) {
     for (int cw = maxw; cw >= 1; --cw) {
         const int maxh = (128 / cw) < h ? (128 / cw) : h;
         for (int ch = maxh; ch >= 1; --ch) {
+            // full-width boxes may take the same rows of several images (the 4-D TMA box is n x h x w x c, and a row
+            // outside the image is outside the tensor for every image of the box, so the zero padding still holds):
+            // a 12x12 image is 2 tiles at 56 % as 12x10 + 12x2, but 2 rows x 5 images fill 120 of 128 rows
             int cn = 1;
-            if (cw == w && ch == h) {
+            if (cw == w) {
                 cn = 128 / (cw * ch);
                 if (cn > n_img) cn = n_img;
                 if (cn < 1) cn = 1;
             }
             const long long tiles = (long long)((w + cw - 1) / cw) * ((h + ch - 1) / ch) * ((n_img + cn - 1) / cn);
-            // efficiency, with a mild preference for long contiguous rows
-            const double eff = (double)w * h * n_img / (double)(tiles * 128) + 1e-4 * cw;
+            // efficiency, with a mild preference for long contiguous rows and for boxes inside one image
+            const double eff = (double)w * h * n_img / (double)(tiles * 128) + 1e-4 * cw - (cn > 1 ? 1e-3 : 0.0);
             if (eff > best) best = eff, b_w = cw, b_h = ch, b_n = cn;
         }
     }
