@@ -59,25 +59,6 @@ __device__ __forceinline__ float exp2_poly(float x) {
     const float p = fmaf(fmaf(fmaf(0.055171668f, f, 0.24261112f), f, 0.69326099f), f, 0.99992807f);
     return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
 }
-// packed fp32 pairs (sm_100 FFMA2 / FADD2): the softmax warps are short of issue slots, not of FMA lanes
-__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
-    uint64_t r;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-    return r;
-}
-__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) {
-    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
-}
-__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
-    uint64_t d;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-    return d;
-}
-__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
-    uint64_t d;
-    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-    return d;
-}
 // exp2_poly on a pair, with the additions and the polynomial on FFMA2 / FADD2: 5 issue slots per value, no MUFU
 __device__ __forceinline__ void exp2_poly2(uint64_t x2, float& e0, float& e1) {
     float x0, x1;

@@ -99,6 +99,26 @@ __device__ __forceinline__ float gelu_erf(float x) {
     return x * (x < 0.f ? e : 1.0f - e);
 }
 
+// GEGLU on two (value, gate) pairs at once, polynomial and products on packed fp32 (FFMA2 / FMUL2): ~10 issue slots per
+// output instead of ~17.  Same arithmetic as gelu_erf element by element.
+__device__ __forceinline__ void geglu_pair(float v0, float v1, float g0, float g1, float& o0, float& o1) {
+    const uint64_t u2 = pack2(fminf(fabsf(g0), 6.0f), fminf(fabsf(g1), 6.0f));
+    uint64_t q2 = pack2(-1.889626233e-06f, -1.889626233e-06f);
+    q2 = fma2(q2, u2, pack2(6.268140101e-05f, 6.268140101e-05f));
+    q2 = fma2(q2, u2, pack2(-9.388679333e-04f, -9.388679333e-04f));
+    q2 = fma2(q2, u2, pack2(8.539461332e-03f, 8.539461332e-03f));
+    q2 = fma2(q2, u2, pack2(-5.402068712e-02f, -5.402068712e-02f));
+    q2 = fma2(q2, u2, pack2(-4.584097768e-01f, -4.584097768e-01f));
+    q2 = fma2(q2, u2, pack2(-1.151269147e+00f, -1.151269147e+00f));
+    q2 = fma2(q2, u2, pack2(-9.999943403e-01f, -9.999943403e-01f));
+    float q0, q1, e0, e1;
+    unpack2(q2, q0, q1);
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(q0));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(q1));
+    const uint64_t phi2 = pack2(g0 < 0.f ? e0 : 1.0f - e0, g1 < 0.f ? e1 : 1.0f - e1);
+    unpack2(mul2(mul2(pack2(g0, g1), phi2), pack2(v0, v1)), o0, o1);
+}
+
 // Applies the epilogue to 32 consecutive output columns [col0, col0+32) of one row and stores them.
 __device__ __forceinline__ void epilogue_store32(const GemmKernelParams& p, float (&v)[32], long long m, int img,
                                                  int col0) {
@@ -719,10 +739,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                         for (int j = 0; j < 8; ++j) {
                             const float4 bv = *reinterpret_cast<const float4*>(bs + c * 32 + 4 * j);
                             const float4 bg = *reinterpret_cast<const float4*>(bs + HALF + c * 32 + 4 * j);
-                            v[4 * j + 0] = (__uint_as_float(rv[4 * j + 0]) + bv.x) * gelu_erf(__uint_as_float(rg[4 * j + 0]) + bg.x);
-                            v[4 * j + 1] = (__uint_as_float(rv[4 * j + 1]) + bv.y) * gelu_erf(__uint_as_float(rg[4 * j + 1]) + bg.y);
-                            v[4 * j + 2] = (__uint_as_float(rv[4 * j + 2]) + bv.z) * gelu_erf(__uint_as_float(rg[4 * j + 2]) + bg.z);
-                            v[4 * j + 3] = (__uint_as_float(rv[4 * j + 3]) + bv.w) * gelu_erf(__uint_as_float(rg[4 * j + 3]) + bg.w);
+                            geglu_pair(__uint_as_float(rv[4 * j + 0]) + bv.x, __uint_as_float(rv[4 * j + 1]) + bv.y,
+                                       __uint_as_float(rg[4 * j + 0]) + bg.x, __uint_as_float(rg[4 * j + 1]) + bg.y,
+                                       v[4 * j + 0], v[4 * j + 1]);
+                            geglu_pair(__uint_as_float(rv[4 * j + 2]) + bv.z, __uint_as_float(rv[4 * j + 3]) + bv.w,
+                                       __uint_as_float(rg[4 * j + 2]) + bg.z, __uint_as_float(rg[4 * j + 3]) + bg.w,
+                                       v[4 * j + 2], v[4 * j + 3]);
                         }
                         if (more) {
                             tmem_ld_x32(t_addr + (c + 2) * 32, rv);
