@@ -47,7 +47,7 @@ def timed(fn, reps):
     return e0.elapsed_time(e1) / reps
 
 
-with torch.no_grad():
+with torch.no_grad(), torch.autocast(device_type="cuda", dtype=torch.bfloat16):
     unet = O.seeded_init_(O.UNet2DCondition(O.sd21_unet_config(sample_size=96)), 0).eval().to(dev, torch.bfloat16)
     vae = O.seeded_init_(O.VAEDecoder(O.VAEConfig()), 1).eval().to(dev, torch.bfloat16)
     x = torch.randn(2 * B, 4, 96, 96, device=dev, dtype=torch.bfloat16)
