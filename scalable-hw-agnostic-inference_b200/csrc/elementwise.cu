@@ -37,16 +37,45 @@ __device__ __forceinline__ void store8_h(void* base, size_t idx, const float (&v
 // =============================================================================================== GroupNorm
 // Pass 1: per (image, pixel-split) partial sums per group, written (not accumulated) to scratch so the result
 // is deterministic.  Pass 2 reduces the splits in a fixed order, then normalises.
-// Thread layout: blockDim = vpp * lanes, vpp = C/4 vectors per pixel; thread -> fixed 4 channels.
+// Thread layout: blockDim = vpp * lanes, vpp = C/VEC vectors per pixel; thread -> fixed VEC channels (VEC = 8 when the
+// channel counts allow: 16-byte loads of 16-bit inputs and 16-byte stores of the 16-bit outputs).
+template <int VEC>
+__device__ __forceinline__ void loadv(const void* base, size_t idx, int dt, float (&v)[VEC]) {
+    if (VEC == 4) {
+        const float4 a = load4(base, idx, dt);
+        v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w;
+    } else if (dt == B200SD_F32) {
+        const float4 a = *reinterpret_cast<const float4*>(static_cast<const float*>(base) + idx);
+        const float4 b = *reinterpret_cast<const float4*>(static_cast<const float*>(base) + idx + 4);
+        v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w, v[4] = b.x, v[5] = b.y, v[6] = b.z, v[7] = b.w;
+    } else {
+        const uint4 t = *reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(base) + idx);
+        const bool f16 = dt == B200SD_F16;
+        v[0] = h_lo(t.x, f16), v[1] = h_hi(t.x, f16), v[2] = h_lo(t.y, f16), v[3] = h_hi(t.y, f16);
+        v[4] = h_lo(t.z, f16), v[5] = h_hi(t.z, f16), v[6] = h_lo(t.w, f16), v[7] = h_hi(t.w, f16);
+    }
+}
+template <int VEC>
+__device__ __forceinline__ void storev_h(void* base, size_t idx, const float (&v)[VEC], bool f16) {
+    if (VEC == 4) {
+        store4_h(base, idx, make_float4(v[0], v[1], v[2], v[3]), f16);
+    } else {
+        *reinterpret_cast<uint4*>(static_cast<uint16_t*>(base) + idx) =
+            make_uint4(pack_h2(v[0], v[1], f16), pack_h2(v[2], v[3], f16), pack_h2(v[4], v[5], f16),
+                       pack_h2(v[6], v[7], f16));
+    }
+}
+
+template <int VEC>
 __global__ void gn_stats_kernel(const void* __restrict__ x1, int c1, const void* __restrict__ x2, int c2, int dt,
                                 int hw, int groups, int splits, float* __restrict__ partial) {
     extern __shared__ float sm[];  // [lanes][C] sums, then [lanes][C] sums of squares
     const int C = c1 + c2;
-    const int vpp = C >> 2;
+    const int vpp = C / VEC;
     const int lanes = blockDim.x / vpp;
     const int pl = threadIdx.x / vpp;  // pixel lane
     const int vec = threadIdx.x - pl * vpp;
-    const int ch = vec << 2;
+    const int ch = vec * VEC;
     const int n = blockIdx.y, split = blockIdx.x;
     const int per = (hw + splits - 1) / splits;
     const int p0 = split * per;
@@ -55,28 +84,31 @@ __global__ void gn_stats_kernel(const void* __restrict__ x1, int c1, const void*
     const void* src = second ? x2 : x1;
     const int cs = second ? c2 : c1;
     const size_t off = (size_t)n * hw * cs + (second ? ch - c1 : ch);
-    float s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
+    float s[VEC], q[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) s[j] = 0.f, q[j] = 0.f;
+    constexpr int U = VEC == 4 ? 4 : 2;  // independent loads in flight per thread (64 / 32-64 bytes; 4 x 8 measured no better)
     int p = p0 + pl;
-    // four independent loads in flight per thread: these tensors are read once, so latency hiding is all that matters
-    for (; p + 3 * lanes < p1; p += 4 * lanes) {
-        float4 v[4];
+    // these tensors are read once, so latency hiding is all that matters
+    for (; p + (U - 1) * lanes < p1; p += U * lanes) {
+        float v[U][VEC];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = load4(src, off + (size_t)(p + u * lanes) * cs, dt);
+        for (int u = 0; u < U; ++u) loadv<VEC>(src, off + (size_t)(p + u * lanes) * cs, dt, v[u]);
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            s[0] += v[u].x, s[1] += v[u].y, s[2] += v[u].z, s[3] += v[u].w;
-            q[0] += v[u].x * v[u].x, q[1] += v[u].y * v[u].y, q[2] += v[u].z * v[u].z, q[3] += v[u].w * v[u].w;
-        }
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) s[j] += v[u][j], q[j] += v[u][j] * v[u][j];
     }
     for (; p < p1; p += lanes) {
-        const float4 v = load4(src, off + (size_t)p * cs, dt);
-        s[0] += v.x, s[1] += v.y, s[2] += v.z, s[3] += v.w;
-        q[0] += v.x * v.x, q[1] += v.y * v.y, q[2] += v.z * v.z, q[3] += v.w * v.w;
+        float v[VEC];
+        loadv<VEC>(src, off + (size_t)p * cs, dt, v);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) s[j] += v[j], q[j] += v[j] * v[j];
     }
     float* ss = sm + pl * C + ch;
     float* qq = sm + lanes * C + pl * C + ch;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) ss[j] = s[j], qq[j] = q[j];
+    for (int j = 0; j < VEC; ++j) ss[j] = s[j], qq[j] = q[j];
     __syncthreads();
     const int cpg = C / groups;
     for (int g = threadIdx.x; g < groups; g += blockDim.x) {
@@ -88,17 +120,18 @@ __global__ void gn_stats_kernel(const void* __restrict__ x1, int c1, const void*
     }
 }
 
+template <int VEC>
 __global__ void gn_apply_kernel(const void* __restrict__ x1, int c1, const void* __restrict__ x2, int c2, int dt,
                                 int hw, int groups, int splits, const float* __restrict__ partial, float eps,
                                 const float* __restrict__ gamma, const float* __restrict__ beta, int silu,
                                 void* __restrict__ y, void* __restrict__ raw, int out_f16, int chunks) {
     __shared__ float s_mean[64], s_rstd[64];
     const int C = c1 + c2;
-    const int vpp = C >> 2;
+    const int vpp = C / VEC;
     const int lanes = blockDim.x / vpp;
     const int pl = threadIdx.x / vpp;
     const int vec = threadIdx.x - pl * vpp;
-    const int ch = vec << 2;
+    const int ch = vec * VEC;
     const int n = blockIdx.y;
     const int cpg = C / groups;
     // fixed-order reduction of the split statistics: 8 strided partial sums per group, then those 8 in order
@@ -123,9 +156,9 @@ __global__ void gn_apply_kernel(const void* __restrict__ x1, int c1, const void*
         s_mean[g] = mean, s_rstd[g] = rsqrtf(var + eps);
     }
     __syncthreads();
-    float sc[4], sh[4];
+    float sc[VEC], sh[VEC];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < VEC; ++j) {
         const int g = (ch + j) / cpg;
         const float w = gamma[ch + j] * s_rstd[g];
         sc[j] = w, sh[j] = beta[ch + j] - s_mean[g] * w;
@@ -138,22 +171,31 @@ __global__ void gn_apply_kernel(const void* __restrict__ x1, int c1, const void*
     const int p0 = blockIdx.x * per;
     const int p1 = min(hw, p0 + per);
     const bool f16 = out_f16 != 0;
-    auto emit = [&](int p, const float4& v) {
+    auto emit = [&](int p, const float (&v)[VEC]) {
         const size_t o = ((size_t)n * hw + p) * C + ch;
-        if (raw) store4_h(raw, o, v, f16);
-        float4 r = make_float4(v.x * sc[0] + sh[0], v.y * sc[1] + sh[1], v.z * sc[2] + sh[2], v.w * sc[3] + sh[3]);
-        if (silu) r = make_float4(silu_f(r.x), silu_f(r.y), silu_f(r.z), silu_f(r.w));
-        store4_h(y, o, r, f16);
+        if (raw) storev_h<VEC>(raw, o, v, f16);
+        float r[VEC];
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            r[j] = v[j] * sc[j] + sh[j];
+            if (silu) r[j] = silu_f(r[j]);
+        }
+        storev_h<VEC>(y, o, r, f16);
     };
+    constexpr int U = VEC == 4 ? 4 : 2;
     int p = p0 + pl;
-    for (; p + 3 * lanes < p1; p += 4 * lanes) {
-        float4 v[4];
+    for (; p + (U - 1) * lanes < p1; p += U * lanes) {
+        float v[U][VEC];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = load4(src, off + (size_t)(p + u * lanes) * cs, dt);
+        for (int u = 0; u < U; ++u) loadv<VEC>(src, off + (size_t)(p + u * lanes) * cs, dt, v[u]);
 #pragma unroll
-        for (int u = 0; u < 4; ++u) emit(p + u * lanes, v[u]);
+        for (int u = 0; u < U; ++u) emit(p + u * lanes, v[u]);
     }
-    for (; p < p1; p += lanes) emit(p, load4(src, off + (size_t)p * cs, dt));
+    for (; p < p1; p += lanes) {
+        float v[VEC];
+        loadv<VEC>(src, off + (size_t)p * cs, dt, v);
+        emit(p, v);
+    }
 }
 
 static int gn_splits(int n_img, int hw) {
@@ -481,7 +523,8 @@ extern "C" int32_t b200sd_groupnorm(const b200sd_groupnorm_params* p, b200sd_str
     if (p->workspace_bytes < need)
         return set_error(B200SD_ERR_WORKSPACE, "groupnorm: workspace %lld < %lld bytes", (long long)p->workspace_bytes,
                          (long long)need);
-    const int vpp = C / 4;
+    const bool vec8 = p->c1 % 8 == 0 && c2 % 8 == 0;  // 8 channels per thread: 16-byte accesses on the 16-bit side
+    const int vpp = C / (vec8 ? 8 : 4);
     int lanes = 256 / vpp;
     if (lanes < 1) lanes = 1;
     const int threads = vpp * lanes;
@@ -489,11 +532,19 @@ extern "C" int32_t b200sd_groupnorm(const b200sd_groupnorm_params* p, b200sd_str
     cudaStream_t s = as_stream(stream);
     const int chunks = splits * 2;
     dim3 g1(splits, p->n_img), g2(chunks, p->n_img);
-    gn_stats_kernel<<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits,
-                                              p->workspace);
-    gn_apply_kernel<<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits,
-                                           p->workspace, p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
-                                           p->out_dtype == B200SD_F16, chunks);
+    if (vec8) {
+        gn_stats_kernel<8><<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits,
+                                                     p->workspace);
+        gn_apply_kernel<8><<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits,
+                                                  p->workspace, p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
+                                                  p->out_dtype == B200SD_F16, chunks);
+    } else {
+        gn_stats_kernel<4><<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits,
+                                                     p->workspace);
+        gn_apply_kernel<4><<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits,
+                                                  p->workspace, p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
+                                                  p->out_dtype == B200SD_F16, chunks);
+    }
     count_launch(2);
     B200SD_CHECK_LAUNCH("groupnorm");
     return B200SD_OK;
@@ -714,7 +765,8 @@ extern "C" int32_t b200sd_groupnorm_static_scratch(const b200sd_groupnorm_params
     float* scratch = nullptr;
     const int32_t rc = gn_static_scratch_address(&scratch);
     if (rc != B200SD_OK) return rc;
-    const int vpp = C / 4;
+    const bool vec8 = p->c1 % 8 == 0 && c2 % 8 == 0;  // 8 channels per thread: 16-byte accesses on the 16-bit side
+    const int vpp = C / (vec8 ? 8 : 4);
     int lanes = 256 / vpp;
     if (lanes < 1) lanes = 1;
     const int threads = vpp * lanes;
@@ -722,10 +774,17 @@ extern "C" int32_t b200sd_groupnorm_static_scratch(const b200sd_groupnorm_params
     cudaStream_t s = as_stream(stream);
     const int chunks = splits * 2;
     dim3 g1(splits, p->n_img), g2(chunks, p->n_img);
-    gn_stats_kernel<<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch);
-    gn_apply_kernel<<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch,
-                                           p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
-                                           p->out_dtype == B200SD_F16, chunks);
+    if (vec8) {
+        gn_stats_kernel<8><<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch);
+        gn_apply_kernel<8><<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch,
+                                                  p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
+                                                  p->out_dtype == B200SD_F16, chunks);
+    } else {
+        gn_stats_kernel<4><<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch);
+        gn_apply_kernel<4><<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch,
+                                                  p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
+                                                  p->out_dtype == B200SD_F16, chunks);
+    }
     count_launch(2);
     B200SD_CHECK_LAUNCH("groupnorm_static_scratch");
     return B200SD_OK;
