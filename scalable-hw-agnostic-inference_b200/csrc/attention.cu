@@ -30,13 +30,14 @@ constexpr int ATT_D = 64;
 constexpr int ATT_STAGES = 4;
 constexpr int ATT_TILE = 128 * 128;  // bytes of a [128 x 64] 16-bit tile
 constexpr int ATT_THREADS = 32 * (2 + 8 * ATT_QT);  // TMA, UMMA, then 8 softmax warps per Q tile
-constexpr int ATT_XCH = 2 * ATT_QT * 256 * 4;       // row-max exchange [parity][tile][half][128] fp32
+constexpr int ATT_XCH = 3 * ATT_QT * 256 * 4;       // row-max exchange [parity][tile][half][128] fp32 + row-sum exchange [tile][half][128]
 constexpr int ATT_SMEM = ATT_QT * ATT_TILE /*Q*/ + ATT_STAGES * 2 * ATT_TILE /*K,V*/ + ATT_XCH + 1024 + 256;
 // TMEM columns: S_A 0..127, S_B 128..255, O_A 256..319, O_B 320..383, P_A 384..447, P_B 448..511 (16-bit pairs)
 constexpr uint32_t ATT_TMEM_S = 0, ATT_TMEM_O = 256, ATT_TMEM_P = 384;
 
 struct AttnKernelParams {
     int sq, skv, n_kv_tiles;
+    int heads, n_qpairs, items;  // work items = (batch, head, pair of 128-row Q tiles), walked by persistent CTAs
     float scale_log2;  // scale * log2(e)
     uint16_t* out;
     long long ld_out;
@@ -106,7 +107,7 @@ __device__ __forceinline__ void tmem_st_x32(uint32_t taddr, const uint32_t (&r)[
 }
 
 // EMU_MASK: bit i set = pair i of every eight pairs of exponentials is evaluated by exp2_poly2 instead of the MUFU.
-template <bool F16, int EMU_MASK>
+template <bool F16, int EMU_MASK, bool PERSIST>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
     attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                      const __grid_constant__ CUtensorMap tmV, const AttnKernelParams p) {
@@ -126,13 +127,18 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
     uint64_t* p_full = s_free + ATT_QT;        // [QT] softmax -> UMMA : P tile in TMEM (and O rescaled)
     uint64_t* pv_done = p_full + ATT_QT;       // [QT] UMMA -> softmax : O += P V finished
     uint64_t* b_go = pv_done + ATT_QT;         // softmax(A) -> UMMA : tile A entered its first exponential phase
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(b_go + 1);
+    uint64_t* q_empty = b_go + 1;              // UMMA -> TMA : every Q K^T of the work item has read the Q tiles
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_empty + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int q0 = blockIdx.x * (ATT_BM * ATT_QT);
-    const int head = blockIdx.y, b = blockIdx.z;
     const int n_tiles = p.n_kv_tiles;
-    const bool has_b = q0 + ATT_BM < p.sq;  // second Q tile holds at least one live row
+    // Persistent CTAs: work item `it` = (batch b, head, pair of Q tiles at row q0).  Short problems (cross-attention with
+    // 77 keys, the 24x24 level) are dominated by per-CTA set-up -- barrier init, TMEM allocation, the first TMA round
+    // trip -- and one CTA per SM cannot overlap two of them, so a CTA keeps its barriers and TMEM and walks several items;
+    // the Q tiles of the next item are requested as soon as the last Q K^T of the current one has been issued.
+    auto item_q0 = [&](int it) { return (it % p.n_qpairs) * (ATT_BM * ATT_QT); };
+    auto item_head = [&](int it) { return (it / p.n_qpairs) % p.heads; };
+    auto item_b = [&](int it) { return it / (p.n_qpairs * p.heads); };
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmQ);
@@ -149,6 +155,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
             mbar_init(&pv_done[t], 1);
         }
         mbar_init(b_go, 8);
+        mbar_init(q_empty, 1);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_slot, 512);
@@ -164,30 +171,35 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
     // the one issuing thread -- the whole kernel ran at the speed of that thread.
     constexpr uint32_t FULL = 0xffffffffu;
     if (warp == 0) {
-        if (elect_one()) {
-            mbar_expect_tx(q_full, (has_b ? 2 : 1) * ATT_TILE);
-            tma_load_2d(sQ, &tmQ, q_full, head * ATT_D, b * p.sq + q0);
-            if (has_b) tma_load_2d(sQ + ATT_TILE, &tmQ, q_full, head * ATT_D, b * p.sq + q0 + ATT_BM);
-        }
-        __syncwarp();
         int stage = 0;
         uint32_t phase = 0;
-        for (int j = 0; j < n_tiles; ++j) {
-            mbar_wait(&kv_empty[stage], phase ^ 1);
-            uint8_t* sk = sKV + stage * 2 * ATT_TILE;
+        int n_it = 0;
+        for (int it = blockIdx.x; it < p.items; it += (PERSIST ? (int)gridDim.x : p.items), ++n_it) {
+            const int q0 = item_q0(it), head = item_head(it), b = item_b(it);
+            const bool has_b = q0 + ATT_BM < p.sq;  // second Q tile holds at least one live row
+            if (PERSIST && n_it > 0) mbar_wait(q_empty, (n_it - 1) & 1);
             if (elect_one()) {
-                mbar_expect_tx(&kv_full[stage], 2 * ATT_TILE);
-                tma_load_2d(sk, &tmK, &kv_full[stage], head * ATT_D, b * p.skv + j * ATT_BN);
-                tma_load_2d(sk + ATT_TILE, &tmV, &kv_full[stage], head * ATT_D, b * p.skv + j * ATT_BN);
+                mbar_expect_tx(q_full, (has_b ? 2 : 1) * ATT_TILE);
+                tma_load_2d(sQ, &tmQ, q_full, head * ATT_D, b * p.sq + q0);
+                if (has_b) tma_load_2d(sQ + ATT_TILE, &tmQ, q_full, head * ATT_D, b * p.sq + q0 + ATT_BM);
             }
             __syncwarp();
-            if (++stage == ATT_STAGES) stage = 0, phase ^= 1;
+            for (int j = 0; j < n_tiles; ++j) {
+                mbar_wait(&kv_empty[stage], phase ^ 1);
+                uint8_t* sk = sKV + stage * 2 * ATT_TILE;
+                if (elect_one()) {
+                    mbar_expect_tx(&kv_full[stage], 2 * ATT_TILE);
+                    tma_load_2d(sk, &tmK, &kv_full[stage], head * ATT_D, b * p.skv + j * ATT_BN);
+                    tma_load_2d(sk + ATT_TILE, &tmV, &kv_full[stage], head * ATT_D, b * p.skv + j * ATT_BN);
+                }
+                __syncwarp();
+                if (++stage == ATT_STAGES) stage = 0, phase ^= 1;
+            }
         }
     } else if (warp == 1) {
         constexpr uint32_t bf = F16 ? 0u : 1u;
         constexpr uint32_t idesc_qk = umma_idesc(128, ATT_BN, bf, bf, 0, 0);
         constexpr uint32_t idesc_pv = umma_idesc(128, ATT_D, bf, bf, 0, 1);  // A = P (TMEM, K-major), B = V MN-major
-        const int nq = has_b ? 2 : 1;
         const uint32_t tmem_u = __shfl_sync(FULL, tmem_base, 0);
         const uint32_t q_u = __shfl_sync(FULL, smem_u32(sQ), 0);
         const uint32_t kv_u = __shfl_sync(FULL, smem_u32(sKV), 0);
@@ -221,29 +233,36 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
         };
         // Event-driven issue: the two Q tiles advance independently.  Whatever is ready goes next, P V first (the
         // softmax group of that tile needs its completion before it may overwrite P), then the next Q K^T.
-        mbar_wait(q_full, 0);
+        // Barrier parities run over the whole life of the CTA: gk0 = kv tiles of all earlier items (the K/V ring),
+        // gt0[t] = kv steps Q tile t has done before this item (tile B sits out items whose second tile is empty).
+        int gk0 = 0, gt0[ATT_QT] = {0, 0}, n_it = 0;
+        for (int it = blockIdx.x; it < p.items; it += (PERSIST ? (int)gridDim.x : p.items), ++n_it) {
+        const int nq = item_q0(it) + ATT_BM < p.sq ? 2 : 1;
+        const int NI = PERSIST ? n_it : 0, GK = PERSIST ? gk0 : 0;
+        const int GT[ATT_QT] = {PERSIST ? gt0[0] : 0, PERSIST ? gt0[1] : 0};
+        mbar_wait(q_full, NI & 1);
         tc_fence_after();
         int next_qk[ATT_QT] = {0, 0}, next_pv[ATT_QT] = {0, 0};
-        int kv_ready = 0;  // kv tiles [0, kv_ready) have landed in shared memory
-        int released = 0;  // kv tiles [0, released) have been handed back to the producer
+        int kv_ready = 0;  // kv tiles [0, kv_ready) of this item have landed in shared memory
+        int released = 0;  // kv tiles [0, released) of this item have been handed back to the producer
         int pending = nq * n_tiles;
         while (pending > 0) {
-            while (kv_ready < n_tiles &&
-                   __all_sync(FULL, mbar_test_wait(&kv_full[kv_ready % ATT_STAGES], (kv_ready / ATT_STAGES) & 1)))
+            while (kv_ready < n_tiles && __all_sync(FULL, mbar_test_wait(&kv_full[(GK + kv_ready) % ATT_STAGES],
+                                                                          ((GK + kv_ready) / ATT_STAGES) & 1)))
                 ++kv_ready;
 #pragma unroll
             for (int t = 0; t < ATT_QT; ++t) {
                 if (t >= nq) continue;
                 int j = next_pv[t];
-                if (j < next_qk[t] && __all_sync(FULL, mbar_test_wait(&p_full[t], j & 1))) {
+                if (j < next_qk[t] && __all_sync(FULL, mbar_test_wait(&p_full[t], (GT[t] + j) & 1))) {
                     tc_fence_after();
-                    issue_pv(t, j, j % ATT_STAGES);
+                    issue_pv(t, j, (GK + j) % ATT_STAGES);
                     next_pv[t] = j + 1;
                     --pending;
                     int mn = next_pv[0];
                     if (nq > 1 && next_pv[1] < mn) mn = next_pv[1];
                     for (; released < mn; ++released) {
-                        if (elect_one()) umma_commit(&kv_empty[released % ATT_STAGES]);
+                        if (elect_one()) umma_commit(&kv_empty[(GK + released) % ATT_STAGES]);
                         __syncwarp();
                     }
                 }
@@ -257,20 +276,34 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                 // took ~1450 cycles, twice the MUFU time of its 2 warps per scheduler: the phase is bound by per-warp
                 // latency, and four warps in it at once fill the MUFU better than two.  So no hand-over barrier.)
                 bool go = j < kv_ready;
-                if (go && j == 0) go = (t == 0 || !p.stagger) || __all_sync(FULL, mbar_test_wait(b_go, 0));
-                else if (go) go = __all_sync(FULL, mbar_test_wait(&s_free[t], (j - 1) & 1));
+                // the S tile must have been read by the softmax group (also the last one of this tile's previous item)
+                if (go && GT[t] + j > 0) go = __all_sync(FULL, mbar_test_wait(&s_free[t], (GT[t] + j - 1) & 1));
+                if (go && j == 0 && t == 1 && p.stagger) go = __all_sync(FULL, mbar_test_wait(b_go, NI & 1));
                 if (go) {
                     tc_fence_after();
-                    issue_qk(t, j % ATT_STAGES);
+                    issue_qk(t, (GK + j) % ATT_STAGES);
                     next_qk[t] = j + 1;
                 }
             }
+        }
+        // every Q K^T of this item is issued: once they complete, the Q tiles may be overwritten by the next item's
+        if (PERSIST) {
+            if (elect_one()) umma_commit(q_empty);
+            __syncwarp();
+        }
+        gk0 += n_tiles;
+        for (int t = 0; t < nq; ++t) gt0[t] += n_tiles;
         }
     } else {
         // ---------------------------------------------------------------- softmax + output
         // 8 warps per Q tile: tile t = (warp-2)/8; inside a tile warps 0..3 own score columns 0..63 of their 32 rows,
         // warps 4..7 own columns 64..127 of the same rows (TMEM lane quadrant = warp % 4 either way).
         const int t = (warp - 2) >> 3;
+        int gt = 0, n_it = 0;  // kv steps this Q tile has done in earlier items; items this CTA has started
+        for (int it = blockIdx.x; it < p.items; it += (PERSIST ? (int)gridDim.x : p.items), ++n_it) {
+        const int q0 = item_q0(it), head = item_head(it), b = item_b(it);
+        const bool has_b = q0 + ATT_BM < p.sq;
+        const int GTS = PERSIST ? gt : 0;  // parity base of this tile's barriers
         if (t == 0 || has_b) {
             const int half = ((warp - 2) >> 2) & 1;
             const int quad = warp & 3;
@@ -282,7 +315,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
             const float sc = p.scale_log2;
             float m_used = 0.f, l = 0.f;
             for (int j = 0; j < n_tiles; ++j) {
-                mbar_wait(&s_full[t], j & 1);
+                mbar_wait(&s_full[t], (GTS + j) & 1);
                 tc_fence_after();
                 uint32_t s[2][32];
 #pragma unroll
@@ -318,7 +351,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                     }
                 // the other half of this row lives in the warp 4 further on (or back): exchange through shared memory,
                 // double-buffered by tile parity so one named barrier per tile suffices
-                float* xch = xchg + ((j & 1) * ATT_QT + t) * 256;
+                float* xch = xchg + (((GTS + j) & 1) * ATT_QT + t) * 256;
                 xch[half * 128 + row] = fmaxf(mx0, mx1);
                 named_bar_sync(2 + t, 256);
                 if (t == 0 && j == 0 && lane == 0) mbar_arrive(b_go);
@@ -360,7 +393,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                 unpack2(ls2, ls0, ls1);
                 // PV(j-1) must be complete before P_t is overwritten or O_t rescaled
                 if (j > 0) {
-                    mbar_wait(&pv_done[t], (j - 1) & 1);
+                    mbar_wait(&pv_done[t], (GTS + j - 1) & 1);
                     tc_fence_after();
                 }
                 if (__any_sync(0xffffffffu, need)) {
@@ -382,11 +415,12 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                 if (lane == 0) mbar_arrive(&p_full[t]);
             }
             // ---- epilogue: O / l -> 16-bit (this thread's 32 of the 64 head-dim columns)
-            float* xch = xchg + (n_tiles & 1) * ATT_QT * 256 + t * 256;  // the buffer the last tile did not use
+            float* xch = xchg + (2 * ATT_QT + t) * 256;  // its own buffer: the next item's first row max may already be
+                                                         // on its way into the parity buffers
             xch[half * 128 + row] = l;
             named_bar_sync(2 + t, 256);
             const float inv = 1.0f / (xch[row] + xch[128 + row]);
-            mbar_wait(&pv_done[t], (n_tiles - 1) & 1);
+            mbar_wait(&pv_done[t], (GTS + n_tiles - 1) & 1);
             tc_fence_after();
             const int qrow = q0 + t * ATT_BM + row;
             uint16_t* orow = p.out + ((long long)b * p.sq + qrow) * p.ld_out + head * ATT_D + half * 32;
@@ -404,6 +438,8 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                     *reinterpret_cast<uint4*>(orow + c * 16 + 8) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                 }
             }
+            gt += n_tiles;
+        }
         }
     }
     tc_fence_before();
@@ -411,19 +447,19 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
     if (warp == 2) tmem_dealloc(tmem_base, 512);
 }
 
-template <bool F16, int EMU_MASK>
+template <bool F16, int EMU_MASK, bool PERSIST>
 static int32_t launch_attention(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                                 const AttnKernelParams& kp, dim3 grid, cudaStream_t stream) {
     static bool attr_set[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(attention_kernel<F16, EMU_MASK>,
+        cudaError_t e = cudaFuncSetAttribute(attention_kernel<F16, EMU_MASK, PERSIST>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM);
         if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "attention smem attribute: %s", cudaGetErrorString(e));
         attr_set[dev] = true;
     }
-    attention_kernel<F16, EMU_MASK><<<grid, ATT_THREADS, ATT_SMEM, stream>>>(tmQ, tmK, tmV, kp);
+    attention_kernel<F16, EMU_MASK, PERSIST><<<grid, ATT_THREADS, ATT_SMEM, stream>>>(tmQ, tmK, tmV, kp);
     count_launch();
     B200SD_CHECK_LAUNCH("attention_kernel");
     return B200SD_OK;
@@ -490,22 +526,32 @@ extern "C" int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_str
     kp.causal = p->causal ? 1 : 0;
     B200SD_CHECK_ARG(!p->causal || p->sq == p->skv, "attention: causal needs sq == skv");
     const int rows_per_cta = ATT_BM * ATT_QT;
-    dim3 grid((p->sq + rows_per_cta - 1) / rows_per_cta, p->heads, p->batch);
+    kp.heads = p->heads;
+    kp.n_qpairs = (p->sq + rows_per_cta - 1) / rows_per_cta;
+    const long long items = (long long)kp.n_qpairs * p->heads * p->batch;
+    B200SD_CHECK_ARG(items < (1LL << 31), "attention: too many work items");
+    kp.items = (int)items;
+    // Short kv loops are dominated by per-CTA set-up: there one CTA per SM walks the items.  Long ones (measured at 72 kv
+    // tiles: -4 % as persistent CTAs, the static round-robin loses to the hardware's dynamic CTA scheduling) get a CTA each.
+    const bool persistent = kp.n_kv_tiles <= 18;
+    dim3 grid((unsigned)(persistent && items > num_sms() ? num_sms() : items), 1, 1);
     cudaStream_t s = as_stream(stream);
     // share of the exponentials evaluated on the FMA pipe instead of the MUFU: 0 none, 1 = 50 %, 2 = 25 %, 3 = 37.5 %
     const int emu = emu_mask_from_env();
+#define B200SD_ATTN_DISPATCH(F)                                                                              \
+    switch (emu) {                                                                                            \
+        case 1: return persistent ? launch_attention<F, 0b10101010, true>(tmQ, tmK, tmV, kp, grid, s)          \
+                                  : launch_attention<F, 0b10101010, false>(tmQ, tmK, tmV, kp, grid, s);        \
+        case 2: return persistent ? launch_attention<F, 0b10001000, true>(tmQ, tmK, tmV, kp, grid, s)          \
+                                  : launch_attention<F, 0b10001000, false>(tmQ, tmK, tmV, kp, grid, s);        \
+        case 3: return persistent ? launch_attention<F, 0b10010010, true>(tmQ, tmK, tmV, kp, grid, s)          \
+                                  : launch_attention<F, 0b10010010, false>(tmQ, tmK, tmV, kp, grid, s);        \
+        default: return persistent ? launch_attention<F, 0, true>(tmQ, tmK, tmV, kp, grid, s)                  \
+                                   : launch_attention<F, 0, false>(tmQ, tmK, tmV, kp, grid, s);                \
+    }
     if (p->dtype == B200SD_F16) {
-        switch (emu) {
-            case 1: return launch_attention<true, 0b10101010>(tmQ, tmK, tmV, kp, grid, s);
-            case 2: return launch_attention<true, 0b10001000>(tmQ, tmK, tmV, kp, grid, s);
-            case 3: return launch_attention<true, 0b10010010>(tmQ, tmK, tmV, kp, grid, s);
-            default: return launch_attention<true, 0>(tmQ, tmK, tmV, kp, grid, s);
-        }
+        B200SD_ATTN_DISPATCH(true)
     }
-    switch (emu) {
-        case 1: return launch_attention<false, 0b10101010>(tmQ, tmK, tmV, kp, grid, s);
-        case 2: return launch_attention<false, 0b10001000>(tmQ, tmK, tmV, kp, grid, s);
-        case 3: return launch_attention<false, 0b10010010>(tmQ, tmK, tmV, kp, grid, s);
-        default: return launch_attention<false, 0>(tmQ, tmK, tmV, kp, grid, s);
-    }
+    B200SD_ATTN_DISPATCH(false)
+#undef B200SD_ATTN_DISPATCH
 }
