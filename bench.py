@@ -162,7 +162,7 @@ def run_reference(args):
                              "unet_step_s": info["unet_step_s"], "vae_decode_s": info["vae_decode_s"]},
             "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 def workload_config(args, batch):
@@ -375,7 +375,7 @@ def run_b200(args):
                                 "sample": f"2 UNet forwards (CFG batch 2, best taken) + 1 VAE decode at {args.size}^2 fp32, "
                                           f"extrapolated to {args.denoise_steps} steps/image",
                                 "unet_step_s": round(info["unet_step_s"], 3), "vae_decode_s": round(info["vae_decode_s"], 3)}
-    print(json.dumps(line), flush=True)
+    _emit(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -403,8 +403,26 @@ def classes_share_vae(prof, pipe) -> float:
     return t_vae / (t_vae + t_den)
 
 
+_REAL_STDOUT = None
+
+
+def _emit(line: dict) -> None:
+    """the ONE JSON line, on the process's real stdout"""
+    sys.stdout.flush()
+    if _REAL_STDOUT is not None:
+        os.dup2(_REAL_STDOUT, 1)
+    print(json.dumps(line), flush=True)
+
+
 def main():
+    global _REAL_STDOUT
     args = parse()
+    # Libraries print to file descriptor 1 behind Python's back (NCCL's "NCCL version ..." banner at communicator
+    # creation): everything but the JSON line goes to stderr, so stdout carries exactly one line.
+    if not (args.profile_only or args.shape_profile):
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
