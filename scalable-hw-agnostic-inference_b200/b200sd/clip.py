@@ -106,10 +106,10 @@ class B200CLIPTextEncoder(torch.nn.Module):
             a = K.layernorm(hs, ly.ln1[0], ly.ln1[1], eps)
             qkv = K.linear(a, ly.qkv_w, ly.qkv_b, out_dtype=K.op_dtype)  # [B*L, 3c]
             o = K.attention(qkv[:, :c], qkv[:, c:2 * c], qkv[:, 2 * c:], B, nh, L, L, 0.125, causal=True)
-            hs = K.linear(o, ly.out_w, ly.out_b, residual=hs, out_dtype=torch.float32)
+            hs = K.linear(o, ly.out_w, ly.out_b, residual=hs, out=hs)
             a = K.layernorm(hs, ly.ln2[0], ly.ln2[1], eps)
             a = K.linear(a, ly.fc1_w, ly.fc1_b, out_dtype=K.op_dtype, gelu=True)
-            hs = K.linear(a, ly.fc2_w, ly.fc2_b, residual=hs, out_dtype=torch.float32)
+            hs = K.linear(a, ly.fc2_w, ly.fc2_b, residual=hs, out=hs)
         # the LayerNorm kernel emits the 16-bit operand format (what the UNet's cross-attention K/V GEMM consumes);
         # a caller that asked for another dtype gets that result converted
         out = K.layernorm(hs, self.final_ln[0], self.final_ln[1], eps)

@@ -171,7 +171,10 @@ class B200UNet(torch.nn.Module):
         ln = K.layernorm(t, *T.ln[2])
         g = K.linear(ln, T.ff1_w, T.ff1_b, out_dtype=BF, geglu=True, block_n=T.ff_block_n)
         t2 = K.linear(g, T.ff2_w, T.ff2_b, residual=t, out_dtype=BF)
-        return K.linear(t2, T.pout_w, T.pout_b, residual=x.view(m, c)).view(n, h, w, c)
+        # in place on the block's input (nothing else reads it): an fp32 residual that is also the output is added by a TMA
+        # reduce in L2 instead of being read by the epilogue
+        xr = x.view(m, c)
+        return K.linear(t2, T.pout_w, T.pout_b, residual=xr, out=xr).view(n, h, w, c)
 
     # ---- the whole forward on NHWC tensors ---------------------------------------------------------------
     def forward_nhwc(self, latent: torch.Tensor, n_img: int, t: torch.Tensor, ctx_kv: List[torch.Tensor],

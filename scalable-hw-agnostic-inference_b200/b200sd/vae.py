@@ -98,7 +98,8 @@ class B200VAEDecoder(torch.nn.Module):
             K.linear(q[i], k[i], None, out=scores)
             ops.softmax_rows(scores, probs, s, s, float(c) ** -0.5)
             K.linear(probs, vt, None, out=o[i])
-        return K.linear(o.view(n * s, c), self.wo, self.bo, residual=h.view(n * s, c)).view(n, hh, ww, c)
+        hr = h.view(n * s, c)  # in place on the block's input (dead after this)
+        return K.linear(o.view(n * s, c), self.wo, self.bo, residual=hr, out=hr).view(n, hh, ww, c)
 
     def decode_nhwc(self, z: torch.Tensor) -> torch.Tensor:
         """z fp32 NHWC [B, h, w, 4] (already divided by scaling_factor) -> fp32 NHWC [B, 8h, 8w, 3]."""

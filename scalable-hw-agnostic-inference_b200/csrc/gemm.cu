@@ -57,6 +57,7 @@ struct GemmKernelParams {
     int geglu;
     int act;       // 1: erf-GELU on (acc + bias), before the residual
     int fast_epi;  // 1: outputs leave through the per-warp staging tile as full 128-byte row segments
+    int tma_reduce;  // 1: (with tma_epi) out IS the fp32 residual: the chunk is added to it by a TMA reduce, no residual read
     int tma_epi;   // 1: (linear layout, no residual) the staging tile is written in the output dtype, row per thread, and
                    //    leaves with one TMA store per 32x32 chunk: no shared-memory read-back on the epilogue's chain
 };
@@ -226,6 +227,18 @@ __device__ __forceinline__ void res_request(const GemmKernelParams& p, const int
                 buf[i] = *reinterpret_cast<const uint4*>(static_cast<const float*>(p.residual) +
                                                          (long long)mt[i] * p.ld_res + col0 + 4 * (lane & 7));
         }
+    } else if (p.res_dtype == B200SD_F32) {
+        // 16-bit output, fp32 residual (the feed-forward's second linear): 8 fp32 per lane and pass
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int row = 8 * i + (lane >> 2);
+            buf[2 * i] = buf[2 * i + 1] = make_uint4(0, 0, 0, 0);
+            if ((vmask >> row) & 1) {
+                const uint4* src = reinterpret_cast<const uint4*>(static_cast<const float*>(p.residual) +
+                                                                  (long long)mt[i] * p.ld_res + col0 + 8 * (lane & 3));
+                buf[2 * i] = src[0], buf[2 * i + 1] = src[1];
+            }
+        }
     } else {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -277,7 +290,12 @@ __device__ __forceinline__ void staged_store(const GemmKernelParams& p, const fl
                 a0.x = gelu_erf(a0.x), a0.y = gelu_erf(a0.y), a0.z = gelu_erf(a0.z), a0.w = gelu_erf(a0.w);
                 a1.x = gelu_erf(a1.x), a1.y = gelu_erf(a1.y), a1.z = gelu_erf(a1.z), a1.w = gelu_erf(a1.w);
             }
-            if (use_res) {
+            if (use_res && p.res_dtype == B200SD_F32) {
+                a0.x += __uint_as_float(buf[2 * i].x), a0.y += __uint_as_float(buf[2 * i].y);
+                a0.z += __uint_as_float(buf[2 * i].z), a0.w += __uint_as_float(buf[2 * i].w);
+                a1.x += __uint_as_float(buf[2 * i + 1].x), a1.y += __uint_as_float(buf[2 * i + 1].y);
+                a1.z += __uint_as_float(buf[2 * i + 1].z), a1.w += __uint_as_float(buf[2 * i + 1].w);
+            } else if (use_res) {
                 a0.x += h_lo(buf[i].x, f16), a0.y += h_hi(buf[i].x, f16);
                 a0.z += h_lo(buf[i].y, f16), a0.w += h_hi(buf[i].y, f16);
                 a1.x += h_lo(buf[i].z, f16), a1.y += h_hi(buf[i].z, f16);
@@ -570,7 +588,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                 mt[i] = __shfl_sync(0xffffffffu, (int)m, out32 ? 4 * i + (lane >> 3) : 8 * (i & 3) + (lane >> 2));
             const int colbase = n_tile * BLOCK_N;
             const int row0 = m_tile * BLOCK_M + quad * 32;  // first output row of this warp (linear layout only)
-            const bool use_res = fast && p.residual != nullptr;
+            const bool use_res = fast && !tma && p.residual != nullptr;  // (a TMA reduce needs no residual read)
             uint4 rbuf[8];
             if (use_res && splits == 1 && colbase + eg * 32 + 32 <= p.n_cols)
                 res_request(p, mt, vmask, lane, colbase + eg * 32, rbuf);
@@ -682,7 +700,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                             fence_proxy_async_smem();
                             __syncwarp();
                             if (lane == 0 && live) {
-                                tma_store_2d(&tmOut, stg, col0, row0);  // rows / columns past the edge are clipped
+                                // rows / columns past the edge are clipped; with tma_reduce the tile is added to the
+                                // residual that already sits in `out`
+                                if (p.tma_reduce) tma_reduce_add_2d(&tmOut, stg, col0, row0);
+                                else tma_store_2d(&tmOut, stg, col0, row0);
                                 bulk_commit();
                             }
                             continue;
@@ -985,7 +1006,9 @@ static int32_t make_plan(const b200sd_gemm_params* p, bool have_ws, GemmPlan* pl
     const long long num_kb_total = (long long)p->taps * kp.kb_per_tap;
     plan->pair = (pair_allowed && (wide || wide160) && splits == 1 && (p->block_n == 0 || p->block_n == pair_bn) &&
                   kp.m_tiles >= 2 &&
-                  pair_tiles >= clusters && pair_tiles * num_kb_total >= 64 * clusters) ? 1 : 0;
+                  pair_tiles >= clusters && pair_tiles * num_kb_total >= 64 * clusters &&
+                  (num_kb_total >= 12 || kp.geglu)) ? 1 : 0;  // K < 768 with a residual epilogue: measured 10-20 % slower
+                                                              // as pairs (the epilogue, not the operand fetch, is the bound)
     if (plan->pair) block_n = pair_bn;
     kp.n_tiles = (p->n_out + block_n - 1) / block_n;
     kp.splits = splits;
@@ -1063,14 +1086,21 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
     {
         // staged (transposed) epilogue: column bias only, residual of the output's dtype; 16-byte alignment
         // of out / residual rows was checked above for n_cols >= 32
-        const bool res_ok = !p->residual || p->residual_dtype == p->out_dtype;
+        const bool res_ok = !p->residual || p->residual_dtype == p->out_dtype ||
+                            (p->residual_dtype == B200SD_F32 && p->out_dtype != B200SD_F32);
         // (a row bias is folded into the tile's column bias when a tile never spans two images)
         kp.fast_epi = (n_cols >= 32 && !p->bias_along_m && (!p->row_bias || kp.bn == 1) && res_ok) ? 1 : 0;
         // TMA-store epilogue: plain [M, n_cols] row-major output (linear layers), no residual, unsplit
         static const bool tma_off = getenv("B200SD_GEMM_NO_TMA_EPI") != nullptr;
         const int osz = p->out_dtype == B200SD_F32 ? 4 : 2;
-        kp.tma_epi = (kp.fast_epi && !tma_off && !p->residual && kp.splits == 1 && p->taps == 1 && p->img_h == 1 &&
-                      p->n_img == 1 && (p->ld_out * osz) % 16 == 0) ? 1 : 0;
+        // An fp32 residual that IS the output (h += linear(x), the transformer's projections back onto the trunk) needs no
+        // residual read at all: the chunk (acc + bias) is added to it in L2 by a TMA reduce -- same fp32 sum, same order.
+        static const bool red_off = getenv("B200SD_GEMM_NO_TMA_REDUCE") != nullptr;
+        const bool inplace32 = p->residual == p->out && p->ld_res == p->ld_out && p->out_dtype == B200SD_F32 &&
+                               p->residual_dtype == B200SD_F32 && !p->act && !red_off;
+        kp.tma_epi = (kp.fast_epi && !tma_off && (!p->residual || inplace32) && kp.splits == 1 && p->taps == 1 &&
+                      p->img_h == 1 && p->n_img == 1 && (p->ld_out * osz) % 16 == 0) ? 1 : 0;
+        kp.tma_reduce = (kp.tma_epi && p->residual) ? 1 : 0;
     }
     if (kp.splits > 1) {
         const long long tiles = (long long)kp.m_tiles * kp.n_tiles;

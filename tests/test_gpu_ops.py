@@ -386,3 +386,28 @@ def test_embed_tokens(cuda, lib_built):
     ops.embed_tokens(ids, tok, pos, out)
     ref = tok[ids.long()] + pos[None]
     assert torch.equal(out.view(5, 77, 128), ref)  # one fp32 add per element: bit-exact
+
+
+@pytest.mark.parametrize("m,n,k", [(700, 640, 640), (4096, 320, 320), (333, 520, 128)])
+def test_linear_inplace_fp32_residual_by_tma_reduce_equals_the_read_path(K, cuda, m, n, k):
+    """out == residual (fp32): the chunk is added in L2 by a TMA reduce; the same fp32 sum as reading the residual"""
+    dt = K.op_dtype
+    a, w = rnd(m, k, dev=cuda, seed=1, dtype=dt), rnd(n, k, dev=cuda, seed=2, scale=k ** -0.5, dtype=dt)
+    bias = rnd(n, dev=cuda, seed=3)
+    res = rnd(m, n, dev=cuda, seed=4)
+    t = res.clone()
+    K.linear(a, w, bias, residual=t, out=t)                      # reduce-add path
+    sep = K.linear(a, w, bias, residual=res, out_dtype=torch.float32)  # residual read by the epilogue
+    assert torch.equal(t, sep)
+    assert rel(t, a.float() @ w.float().t() + bias + res) < 2e-5
+
+
+@pytest.mark.parametrize("m,n,k", [(600, 320, 1280), (257, 640, 256)])
+def test_linear_fp32_residual_with_16bit_output(K, cuda, m, n, k):
+    """the feed-forward's second linear: fp32 trunk residual, 16-bit result for the next GEMM (staged epilogue)"""
+    dt = K.op_dtype
+    a, w = rnd(m, k, dev=cuda, seed=1, dtype=dt), rnd(n, k, dev=cuda, seed=2, scale=k ** -0.5, dtype=dt)
+    bias = rnd(n, dev=cuda, seed=3)
+    res = rnd(m, n, dev=cuda, seed=4)
+    out = K.linear(a, w, bias, residual=res, out_dtype=dt)
+    assert out.dtype == dt and rel(out, a.float() @ w.float().t() + bias + res) < out_tol(dt)

@@ -23,6 +23,8 @@ CASES = {  # name: (M, K, N, residual, geglu, out fp32)
     "geglu640": (73728, 640, 5120, False, True, False),
     "qkv320": (294912, 320, 320, False, False, False),
     "ff2_320": (294912, 1280, 320, True, False, True),
+    "ff2_320_out16": (294912, 1280, 320, True, False, False),   # fp32 residual, 16-bit output (the UNet's ff2)
+    "res320_inplace": (294912, 320, 320, True, False, True),    # out is the residual: TMA reduce-add
 }
 M, Kd, N, has_res, geglu, out32 = CASES[case]
 a = torch.randn(M, Kd, device=dev).to(dt)
@@ -31,6 +33,8 @@ bias = torch.randn(N, device=dev)
 res = torch.randn(M, N, device=dev) if has_res else None
 n_cols = N // 2 if geglu else N
 out = torch.empty(M, n_cols, device=dev, dtype=torch.float32 if out32 else dt)
+if case.endswith("_inplace"):
+    out = res
 flush = torch.empty(256 << 20, device=dev, dtype=torch.uint8)
 
 
