@@ -411,3 +411,78 @@ def test_linear_fp32_residual_with_16bit_output(K, cuda, m, n, k):
     res = rnd(m, n, dev=cuda, seed=4)
     out = K.linear(a, w, bias, residual=res, out_dtype=dt)
     assert out.dtype == dt and rel(out, a.float() @ w.float().t() + bias + res) < out_tol(dt)
+
+
+# ------------------------------------------------------------------------------------------------ guard bands
+def _guarded(m, n, dtype, dev, sentinel=512.0):
+    """an [m, n] view in the middle of a larger buffer filled with a sentinel (4 guard rows, 16/48 guard columns)"""
+    buf = torch.full((m + 8, n + 64), sentinel, device=dev, dtype=dtype)
+    return buf, buf[4:4 + m, 16:16 + n]
+
+
+def _guards_intact(buf, m, n, sentinel=512.0):
+    mask = torch.ones_like(buf, dtype=torch.bool)
+    mask[4:4 + m, 16:16 + n] = False
+    return bool((buf[mask].float() == sentinel).all())
+
+
+@pytest.mark.parametrize("m,n,k", [(300, 320, 320), (1000, 520, 128), (129, 96, 64), (20001, 1280, 1280)])
+@pytest.mark.parametrize("mode", ["plain16", "plain32", "residual32", "inplace32", "mixed", "gelu16"])
+def test_linear_epilogues_write_only_their_output(K, cuda, m, n, k, mode):
+    """every epilogue path (TMA store, TMA reduce, staged, row-wise; single CTA and CTA pair) against ragged M and N with
+    a sentinel band around the output: nothing outside [m, n] may change, and the inside must be right"""
+    dt = K.op_dtype
+    a, w = rnd(m, k, dev=cuda, seed=1, dtype=dt), rnd(n, k, dev=cuda, seed=2, scale=k ** -0.5, dtype=dt)
+    bias = rnd(n, dev=cuda, seed=3)
+    res = rnd(m, n, dev=cuda, seed=4)
+    ref = a.float() @ w.float().t() + bias
+    odt = dt if mode in ("plain16", "mixed", "gelu16") else torch.float32
+    buf, out = _guarded(m, n, odt, cuda)
+    if mode == "inplace32":
+        out.copy_(res)
+        K.linear(a, w, bias, residual=out, out=out)
+        ref = ref + res
+    elif mode in ("residual32", "mixed"):
+        K.linear(a, w, bias, residual=res, out=out)
+        ref = ref + res
+    elif mode == "gelu16":
+        K.linear(a, w, bias, out=out, gelu=True)
+        ref = F.gelu(ref)
+    else:
+        K.linear(a, w, bias, out=out)
+    assert _guards_intact(buf, m, n)
+    assert rel(out, ref) < (2e-5 if odt == torch.float32 else out_tol(dt))
+
+
+@pytest.mark.parametrize("n_img,h,w,cin,cout", [(3, 12, 12, 64, 320), (2, 24, 24, 128, 640), (5, 6, 6, 64, 96)])
+def test_conv_epilogue_writes_only_its_output(K, cuda, n_img, h, w, cin, cout):
+    from b200sd import ops
+    from b200sd.layers import pack_conv3x3
+    dt = K.op_dtype
+    x = rnd(n_img, h, w, cin, dev=cuda, seed=1, dtype=dt)
+    wt = rnd(cout, cin, 3, 3, dev=cuda, seed=2, scale=(9 * cin) ** -0.5)
+    bias = rnd(cout, dev=cuda, seed=3)
+    m = n_img * h * w
+    buf, out = _guarded(m, cout, torch.float32, cuda)
+    ops.gemm(x, n_img, h, w, cin, 9, pack_conv3x3(wt, dt), bias, False, None, 0, None, out, False, 0, K.gemm_ws, 0)
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), wt.to(dt).float(), bias, padding=1).permute(0, 2, 3, 1).reshape(m, cout)
+    assert _guards_intact(buf, m, cout)
+    assert rel(out, ref) < 2e-5
+
+
+@pytest.mark.parametrize("batch,heads,sq,skv", [(2, 2, 300, 300), (1, 3, 130, 77), (3, 1, 576, 576)])
+def test_attention_writes_only_its_output(K, cuda, batch, heads, sq, skv):
+    from b200sd import ops
+    dt = K.op_dtype
+    c = heads * 64
+    q = rnd(batch * sq, c, dev=cuda, seed=1, dtype=dt)
+    kv = rnd(batch * skv, 2 * c, dev=cuda, seed=2, dtype=dt)
+    k, v = kv[:, :c], kv[:, c:]
+    buf, out = _guarded(batch * sq, c, dt, cuda)
+    ops.attention(q, k, v, out, batch, heads, sq, skv, 0.125)
+    qf = q.float().view(batch, sq, heads, 64).transpose(1, 2)
+    kf = k.float().view(batch, skv, heads, 64).transpose(1, 2)
+    vf = v.float().view(batch, skv, heads, 64).transpose(1, 2)
+    ref = (torch.softmax(qf @ kf.transpose(-1, -2) * 0.125, -1) @ vf).transpose(1, 2).reshape(batch * sq, c)
+    assert _guards_intact(buf, batch * sq, c)
+    assert rel(out, ref) < 2 * out_tol(dt)
