@@ -56,7 +56,7 @@ def test_tiny_unet_per_sample_timesteps_and_bf16_trunk(tiny, cuda):
 def test_tiny_unet_bf16_operands_floor(tiny, cuda):
     """bf16 tensor-core operands (the reference's storage dtype) are a supported mode.  Their error floor against the
     fp32 oracle is set by bf16's 8-bit significand, not by the kernels: emulating bf16 rounding of weights and
-    activations in the fp32 oracle itself gives 1.08e-2 on the real SD2.1 widths (tools/precision_probe.py), which is
+    activations in the fp32 oracle itself gives 1.08e-2 on the real SD2.1 widths (tests/precision_probe.py), which is
     why fp16 operands (same tensor throughput, 11-bit significand) are the default parity path."""
     import b200sd
     ou, _, _, _ = tiny
