@@ -232,3 +232,43 @@ def test_pipeline_runs_from_prompt_strings_through_the_cuda_text_encoder(cuda, l
     ids = enc.tokenizer(["a red cube", ""])
     ref = C.clip_text_forward(C.seeded_state_dict(ccfg, 2), ccfg, ids)
     assert _clip_rel(e, ref) < 1e-2
+
+
+def test_install_into_swaps_the_reference_seam(tiny, cuda):
+    """`b200sd.install_into(pipe)` on an object shaped like the reference's diffusers pipeline (app/run-sd.py:108-134):
+    unet, text_encoder, vae.decoder, vae.post_quant_conv and scheduler are replaced, built from the pipeline's own
+    weights, and keep the call signatures the pipeline uses (diffusers itself is not installable here)."""
+    from types import SimpleNamespace
+    import b200sd
+    from oracle import clip_text as C
+    ou, ov, _, _ = tiny
+    ccfg = C.CLIPTextConfig(hidden_size=128, intermediate_size=256, num_hidden_layers=2, num_attention_heads=2)
+    csd = C.seeded_state_dict(ccfg, 4)
+    unet = SimpleNamespace(state_dict=ou.state_dict, config=ou.cfg)
+    vae = SimpleNamespace(state_dict=ov.state_dict, config=ov.cfg, decoder=None, post_quant_conv=None)
+    text = SimpleNamespace(state_dict=lambda: csd, config=vars(ccfg), dtype=torch.float16)
+    pipe = SimpleNamespace(unet=unet, vae=vae, text_encoder=text,
+                           scheduler=SimpleNamespace(config=SimpleNamespace(prediction_type="v_prediction")))
+    pipe = b200sd.install_into(pipe, scheduler_kind="ddim", device=cuda)
+    assert isinstance(pipe.unet, b200sd.B200UNet) and isinstance(pipe.vae.decoder, b200sd.B200VAEDecoder)
+    assert isinstance(pipe.vae.post_quant_conv, b200sd.B200PostQuantConv)
+    assert isinstance(pipe.scheduler, b200sd.B200Scheduler) and isinstance(pipe.text_encoder, b200sd.B200CLIPTextEncoder)
+    pipe.unet.set_attention_slice("auto")  # what pipe.enable_attention_slicing() reaches (app/run-sd.py:135): a no-op
+    # the calls diffusers' pipeline makes on the swapped modules
+    ids = C.seeded_ids(ccfg, 2, seed=3)
+    emb = pipe.text_encoder(ids.to(cuda), attention_mask=None)[0]
+    assert emb.shape == (2, 77, 128) and emb.dtype == torch.float16
+    assert _clip_rel(emb, C.clip_text_forward(csd, ccfg, ids)) < 1e-2
+    lat1, ctx = O.seeded_inputs(1, 16, 128)  # one image: CFG batch 2 (uncond + cond rows of ctx)
+    lat = torch.cat([lat1, lat1])
+    with torch.no_grad():
+        eps = pipe.unet(lat.to(cuda), 961.0, ctx.to(cuda), return_dict=False)[0]
+        ref = ou(lat, 961.0, ctx)
+        z = pipe.vae.post_quant_conv(lat.to(cuda) / 0.18215)
+        img = pipe.vae.decoder(z)
+        ref_img = ov.decode(lat / 0.18215)
+    assert O.rel_l2(eps.float().cpu(), ref) <= UNET_TOL
+    assert O.rel_l2(img.float().cpu(), ref_img) <= UNET_TOL
+    pipe.scheduler.set_timesteps(4)
+    x = pipe.scheduler.step(eps, pipe.scheduler.timesteps[0], lat.to(cuda), return_dict=False)[0]
+    assert x.shape == lat.shape
