@@ -146,8 +146,10 @@ int32_t b200sd_groupnorm(const b200sd_groupnorm_params* p, b200sd_stream_t strea
  * Same params and result as b200sd_groupnorm, but `workspace` / `workspace_bytes` are ignored: the split statistics
  * go to a 256 KiB array built into the library (held by every GPU that loads it, until process exit).
  *   - allocates nothing (no cudaMalloc / cudaFree or allocating library call);
- *   - limit: n_img * splits * groups * 2 floats <= 65536, splits as in b200sd_groupnorm_workspace_bytes; beyond that
- *     it returns B200SD_ERR_WORKSPACE and the message says to use b200sd_groupnorm;
+ *   - limit: the statistics (n_img * splits * groups * 2 floats) must fit the array's 65536 floats.  The entry point
+ *     lowers its split count, down to one per image, until they do (a large batch then runs its statistics pass in
+ *     fewer, larger CTAs: slower than b200sd_groupnorm, same result up to the summation order); only when
+ *     n_img * groups * 2 > 65536 does it return B200SD_ERR_WORKSPACE, and the message says to use b200sd_groupnorm;
  *   - the first call on a device looks up the array's device address; issue that first call before any stream
  *     capture on that device;
  *   - every call on a device shares the array, which keeps the previous call's contents; nothing needs clearing

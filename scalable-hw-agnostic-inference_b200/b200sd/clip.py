@@ -165,11 +165,15 @@ class PromptEncoder:
 
     def __call__(self, prompts) -> torch.Tensor:
         prompts = list(prompts)
-        todo = [p for p in dict.fromkeys(prompts) if p not in self._cache]
+        # this call's embeddings are collected locally, so evicting the cache can never lose one of them
+        got = {p: self._cache[p] for p in dict.fromkeys(prompts) if p in self._cache}
+        todo = [p for p in dict.fromkeys(prompts) if p not in got]
         if todo:
             emb = self.encoder.encode(self._ids(todo))
-            if len(self._cache) + len(todo) > self._cache_size:
-                self._cache.clear()
             for p, e in zip(todo, emb):
-                self._cache[p] = e
-        return torch.stack([self._cache[p] for p in prompts])
+                got[p] = e
+            if len(self._cache) + len(todo) > self._cache_size:
+                self._cache = {p: e for p, e in got.items() if p in self._cache}  # keep what this call still uses
+            for p in todo[: max(0, self._cache_size - len(self._cache))]:
+                self._cache[p] = got[p]
+        return torch.stack([got[p] for p in prompts])

@@ -28,11 +28,20 @@ def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
         return None
     if not t.is_cuda:
         raise RuntimeError("b200sd ops are CUDA-only (no CPU fallback); got a CPU tensor")
+    _check_current(t)
     return t.data_ptr()
 
 
 def _stream() -> int:
+    """torch's current stream on the CURRENT device.  Every launch in libb200sd goes to the current device, so callers
+    that own a replica on another GPU enter `torch.cuda.device(replica_device)` first (serving.Engine does)."""
     return torch.cuda.current_stream().cuda_stream
+
+
+def _check_current(t: torch.Tensor) -> None:
+    if t.is_cuda and t.device.index != torch.cuda.current_device():
+        raise RuntimeError(f"b200sd: tensor lives on {t.device} but the current CUDA device is "
+                           f"cuda:{torch.cuda.current_device()}; wrap the call in torch.cuda.device({t.device.index})")
 
 
 def launch_count() -> int:
@@ -76,15 +85,7 @@ def profile_end(by_shape: bool = False):
 _taglog = None  # when a list: (kind, tag, work) of every launch in order (tools/ncu_by_shape.py joins it with ncu)
 
 
-import os as _os
-
-# timing experiments only (tools/ablate.sh): kernel classes named here are NOT launched, so results are garbage
-_SKIP = frozenset(k for k in _os.environ.get("B200SD_DEBUG_SKIP", "").split(",") if k)
-
-
 def _run(kind: str, work: float, fn, p, tag: str = "") -> None:
-    if _SKIP and kind in _SKIP:
-        return
     if _taglog is not None:
         _taglog.append((kind, tag, work))
     if _prof is None:

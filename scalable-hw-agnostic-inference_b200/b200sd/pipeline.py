@@ -73,7 +73,9 @@ class B200Pipeline:
         dev = self.device
         sch = self.scheduler
         sch.set_timesteps(steps, dev)
-        key = (B, h, w, steps, g, sch.kind, tuple(ctx2.shape))
+        coef = sch.coef_table(g)
+        # the captured graph holds the addresses of the static buffers and of the scheduler's coefficient table
+        key = (B, h, w, steps, g, sch.kind, tuple(ctx2.shape), coef.data_ptr())
         if self._graph_key != key:
             st = {"B": B, "g": g, "ctx_len": ctx2.shape[1],
                   "x": torch.zeros(B, h, w, 4, device=dev, dtype=torch.float32),
@@ -90,7 +92,6 @@ class B200Pipeline:
             st["in_scale"].copy_(scale)
         else:
             st["in_scale"] = scale.to(dev)
-        sch.coef_table(g)
         st["ctx2"].copy_(ctx2, non_blocking=True)
         # step-invariant cross-attention K/V, recomputed per prompt batch into static buffers
         kv = self.unet.project_context(st["ctx2"])

@@ -30,6 +30,14 @@ def _alphas_cumprod() -> List[float]:
     return out
 
 
+def _norm_device(device) -> torch.device:
+    """'cuda' -> 'cuda:<current>': torch.device('cuda') != torch.device('cuda:0'), and tensors always report an index"""
+    d = torch.device(device)
+    if d.type == "cuda" and d.index is None and torch.cuda.is_available():
+        d = torch.device("cuda", torch.cuda.current_device())
+    return d
+
+
 class B200Scheduler:
     order = 1
 
@@ -39,7 +47,7 @@ class B200Scheduler:
         if prediction_type not in ("v_prediction", "epsilon"):
             raise ValueError(prediction_type)
         self.kind, self.prediction_type = kind, prediction_type
-        self.device = torch.device(device)
+        self.device = _norm_device(device)
         self.acp = _alphas_cumprod()
         self.config = SimpleNamespace(num_train_timesteps=1000, beta_start=0.00085, beta_end=0.012,
                                       beta_schedule="scaled_linear", prediction_type=prediction_type,
@@ -51,6 +59,7 @@ class B200Scheduler:
         self._rows: List[List[float]] = []
         self._in_scale: List[float] = []
         self._coef_dev: Optional[torch.Tensor] = None
+        self.coef_generation = 0
         self._guidance = None
         self._step_of_t = {}
         self._x0_prev = None
@@ -63,7 +72,7 @@ class B200Scheduler:
     def set_timesteps(self, num_inference_steps: int, device=None):
         n = int(num_inference_steps)
         if device is not None:
-            self.device = torch.device(device)
+            self.device = _norm_device(device)
         ratio = 1000 // n
         ts = [i * ratio + 1 for i in range(n)][::-1]  # "leading" spacing, steps_offset = 1
         self.num_inference_steps = n
@@ -128,10 +137,12 @@ class B200Scheduler:
         """device fp32 [n_steps, 6] = {g, cx, cm, cp, ax, am}; uploaded once per (set_timesteps, guidance)."""
         if self._coef_dev is None or self._guidance != guidance:
             host = torch.tensor([[guidance] + r for r in self._rows], dtype=torch.float64).to(torch.float32)
+            # The buffer is rewritten in place whenever the shape allows: captured CUDA graphs hold its address.
             if self._coef_dev is not None and self._coef_dev.shape == host.shape and self._coef_dev.device == self.device:
                 self._coef_dev.copy_(host)
             else:
                 self._coef_dev = host.to(self.device)
+                self.coef_generation += 1  # a new address: graphs captured against the old buffer must be re-captured
             self._guidance = guidance
         return self._coef_dev
 

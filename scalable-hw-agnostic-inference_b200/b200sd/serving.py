@@ -109,8 +109,19 @@ class Engine:
         self.pipe, self.default_steps = pipe, default_steps
         self._lock = threading.Lock()
 
+    def _on_device(self):
+        """Context that makes the pipeline's GPU the current CUDA device of the calling thread.  libb200sd launches on
+        the current device and torch's current stream is per device and per thread, so every thread that drives a
+        replica (FastAPI threadpool workers, the batcher thread, the warm-up call) must enter this first."""
+        import contextlib
+        dev = getattr(self.pipe, "device", None)
+        if dev is None or getattr(dev, "type", None) != "cuda":
+            return contextlib.nullcontext()
+        import torch
+        return torch.cuda.device(dev)
+
     def __call__(self, **model_args):
-        with self._lock:
+        with self._lock, self._on_device():
             return self.pipe(**model_args)
 
     def text2img(self, prompt: str, steps: Optional[int] = None):
@@ -147,6 +158,7 @@ class BatchingEngine(Engine):
         self._q: "queue.Queue[_Pending]" = queue.Queue()
         self._pool = ThreadPoolExecutor(max_workers=png_workers, thread_name_prefix="b200sd-png")
         self.batches: List[int] = []  # sizes of the batches run so far (observability / tests)
+        self._pinned = None
         self._stop = False
         self._worker = threading.Thread(target=self._run, name="b200sd-batcher", daemon=True)
         self._worker.start()
@@ -187,16 +199,32 @@ class BatchingEngine(Engine):
                 continue
             self.batches.append(len(batch))
             try:
-                with self._lock:
+                with self._lock, self._on_device():
                     out = self.pipe(prompt=[r.prompt for r in batch], num_inference_steps=batch[0].steps,
                                     output_type="uint8").images
-                arr = out.cpu().numpy() if hasattr(out, "cpu") else out
+                    arr = self._to_host(out)
                 for r, a in zip(batch, arr):
                     self._pool.submit(self._finish, r, a)
             except Exception as e:  # every waiter of the batch sees the failure (HTTP 500 in the handler)
                 for r in batch:
                     r.error = e
                     r.event.set()
+
+    def _to_host(self, out):
+        """device uint8 images -> numpy through a pinned staging buffer (async copy + one stream sync, no pageable
+        bounce); fake pipelines in the CPU tests hand back arrays already"""
+        if not hasattr(out, "cpu"):
+            return out
+        if not out.is_cuda:
+            return out.numpy()
+        import torch
+        if self._pinned is None or self._pinned.shape[1:] != out.shape[1:] or self._pinned.shape[0] < out.shape[0]:
+            self._pinned = torch.empty((max(out.shape[0], self.max_batch),) + tuple(out.shape[1:]), dtype=out.dtype,
+                                       pin_memory=True)
+        host = self._pinned[: out.shape[0]]
+        host.copy_(out, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return host.numpy().copy()  # the staging buffer is reused by the next batch while PNG workers still read this one
 
     @staticmethod
     def _finish(r: _Pending, arr):

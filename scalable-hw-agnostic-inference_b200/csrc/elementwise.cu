@@ -506,48 +506,63 @@ extern "C" int64_t b200sd_groupnorm_workspace_bytes(const b200sd_groupnorm_param
     return (int64_t)p->n_img * gn_splits(p->n_img, p->hw) * p->groups * 2 * sizeof(float);
 }
 
-extern "C" int32_t b200sd_groupnorm(const b200sd_groupnorm_params* p, b200sd_stream_t stream) {
-    B200SD_CHECK_ARG(p && p->x1 && p->y && p->gamma && p->beta && p->workspace, "groupnorm: null pointer");
+namespace b200sd {
+
+// argument checks shared by the two GroupNorm entry points
+static int32_t gn_check(const b200sd_groupnorm_params* p, const char* who) {
+    B200SD_CHECK_ARG(p && p->x1 && p->y && p->gamma && p->beta, "%s: null pointer", who);
     const int c2 = p->x2 ? p->c2 : 0;
     const int C = p->c1 + c2;
-    B200SD_CHECK_ARG(p->groups > 0 && p->groups <= 64 && C % p->groups == 0, "groupnorm: C=%d groups=%d", C,
-                     p->groups);
-    B200SD_CHECK_ARG(p->c1 % 4 == 0 && c2 % 4 == 0 && C / 4 <= 1024,
-                     "groupnorm: channels must be multiples of 4, C<=4096");
-    B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype) && H_DTYPE(p->out_dtype), "groupnorm: bad in_dtype / out_dtype");
-    B200SD_CHECK_ARG(ALIGNED16(p->x1) && (!p->x2 || ALIGNED16(p->x2)) && ALIGNED16(p->y) &&
-                         (!p->raw || ALIGNED16(p->raw)),
-                     "groupnorm: pointers must be 16-byte aligned");
-    const int splits = gn_splits(p->n_img, p->hw);
-    const int64_t need = (int64_t)p->n_img * splits * p->groups * 2 * sizeof(float);
-    if (p->workspace_bytes < need)
-        return set_error(B200SD_ERR_WORKSPACE, "groupnorm: workspace %lld < %lld bytes", (long long)p->workspace_bytes,
-                         (long long)need);
+    B200SD_CHECK_ARG(p->n_img > 0 && p->hw > 0, "%s: bad shape", who);
+    B200SD_CHECK_ARG(p->groups > 0 && p->groups <= 64 && C % p->groups == 0, "%s: C=%d groups=%d", who, C, p->groups);
+    B200SD_CHECK_ARG(p->c1 % 4 == 0 && c2 % 4 == 0 && C / 4 <= 1024, "%s: channels must be multiples of 4, C<=4096", who);
+    B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype) && H_DTYPE(p->out_dtype), "%s: bad in_dtype / out_dtype", who);
+    B200SD_CHECK_ARG(ALIGNED16(p->x1) && (!p->x2 || ALIGNED16(p->x2)) && ALIGNED16(p->y) && (!p->raw || ALIGNED16(p->raw)),
+                     "%s: pointers must be 16-byte aligned", who);
+    return B200SD_OK;
+}
+
+// the two launches of GroupNorm: split statistics into `scratch` (n_img * splits * groups * 2 floats), then
+// reduce + normalise.  Both kernels accept any split count >= 1.
+static int32_t gn_launch(const b200sd_groupnorm_params* p, int splits, float* scratch, cudaStream_t s, const char* who) {
+    const int c2 = p->x2 ? p->c2 : 0;
+    const int C = p->c1 + c2;
     const bool vec8 = p->c1 % 8 == 0 && c2 % 8 == 0;  // 8 channels per thread: 16-byte accesses on the 16-bit side
     const int vpp = C / (vec8 ? 8 : 4);
     int lanes = 256 / vpp;
     if (lanes < 1) lanes = 1;
     const int threads = vpp * lanes;
     const size_t smem = (size_t)2 * lanes * C * sizeof(float);
-    cudaStream_t s = as_stream(stream);
     const int chunks = splits * 2;
     dim3 g1(splits, p->n_img), g2(chunks, p->n_img);
     if (vec8) {
-        gn_stats_kernel<8><<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits,
-                                                     p->workspace);
-        gn_apply_kernel<8><<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits,
-                                                  p->workspace, p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
+        gn_stats_kernel<8><<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch);
+        gn_apply_kernel<8><<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch,
+                                                  p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
                                                   p->out_dtype == B200SD_F16, chunks);
     } else {
-        gn_stats_kernel<4><<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits,
-                                                     p->workspace);
-        gn_apply_kernel<4><<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits,
-                                                  p->workspace, p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
+        gn_stats_kernel<4><<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch);
+        gn_apply_kernel<4><<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch,
+                                                  p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
                                                   p->out_dtype == B200SD_F16, chunks);
     }
     count_launch(2);
-    B200SD_CHECK_LAUNCH("groupnorm");
+    B200SD_CHECK_LAUNCH(who);
     return B200SD_OK;
+}
+
+}  // namespace b200sd
+
+extern "C" int32_t b200sd_groupnorm(const b200sd_groupnorm_params* p, b200sd_stream_t stream) {
+    const int32_t rc = gn_check(p, "groupnorm");
+    if (rc != B200SD_OK) return rc;
+    B200SD_CHECK_ARG(p->workspace, "groupnorm: null workspace");
+    const int splits = gn_splits(p->n_img, p->hw);
+    const int64_t need = (int64_t)p->n_img * splits * p->groups * 2 * sizeof(float);
+    if (p->workspace_bytes < need)
+        return set_error(B200SD_ERR_WORKSPACE, "groupnorm: workspace %lld < %lld bytes", (long long)p->workspace_bytes,
+                         (long long)need);
+    return gn_launch(p, splits, p->workspace, as_stream(stream), "groupnorm");
 }
 
 extern "C" int32_t b200sd_embed_tokens(const b200sd_embed_params* p, b200sd_stream_t stream) {
@@ -642,10 +657,12 @@ extern "C" int32_t b200sd_small_linear(const b200sd_small_linear_params* p, b200
     const int wpb = 8;
     const int grid = (p->n + wpb - 1) / wpb;
     const size_t smem = (size_t)8 * p->k * sizeof(float);
-    static bool attr_set = false;
-    if (smem > 48 * 1024 && !attr_set) {
+    static bool attr_set[64] = {false};  // the attribute is per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (smem > 48 * 1024 && dev >= 0 && dev < 64 && !attr_set[dev]) {
         cudaFuncSetAttribute(small_linear_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4096 * 4);
-        attr_set = true;
+        attr_set[dev] = true;
     }
     small_linear_kernel<<<grid, wpb * 32, smem, as_stream(stream)>>>(
         p->x, p->rows, p->k, p->n, p->sinusoid_dim, p->silu_in, p->silu_out, (const uint16_t*)p->w,
@@ -664,10 +681,12 @@ extern "C" int32_t b200sd_softmax_rows(const b200sd_softmax_params* p, b200sd_st
                      (long long)p->ld_in, (long long)p->ld_out);
     if (p->rows <= 0) return B200SD_OK;
     const size_t smem = (size_t)p->cols * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {false};  // the attribute is per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
         cudaFuncSetAttribute(softmax_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 49152 * 4);
-        attr_set = true;
+        attr_set[dev] = true;
     }
     softmax_rows_kernel<<<(unsigned)p->rows, 256, smem, as_stream(stream)>>>(
         p->x, p->in_dtype, p->ld_in, p->y, p->out_dtype == B200SD_F16, p->ld_out, p->cols, p->scale);
@@ -735,57 +754,29 @@ static int32_t gn_static_scratch_address(float** out) {
 
 // Same computation and same two kernels as b200sd_groupnorm; `workspace` / `workspace_bytes` of the params are ignored.
 //  * Allocates nothing: no cudaMalloc / cudaFree, no allocating library call.
-//  * Limit: n_img * splits * groups * 2 floats <= 65536 (256 KiB), splits as chosen by b200sd_groupnorm_workspace_bytes;
-//    larger problems are refused with B200SD_ERR_WORKSPACE.  With 32 groups that is n_img * splits <= 1024, which covers
-//    the whole SD2.1 UNet at CFG batch 32 and the VAE at 768^2.
+//  * Limit: the split statistics, n_img * splits * groups * 2 floats, must fit the 65536 floats (256 KiB) of the array.
+//    This entry point lowers the split count (down to 1) until they do, so it only refuses a problem when even one
+//    split per image is too much: n_img * groups > 32768 (more than 1024 images at 32 groups).  Fewer splits mean fewer,
+//    larger CTAs in the statistics pass: a large batch (n_img = 32 at 96x96) runs somewhat slower here than through
+//    b200sd_groupnorm, with the same result up to the summation order of the split statistics.
 //  * The first call on each device resolves the array's device address (cudaGetSymbolAddress); make that first call
 //    before starting any stream capture on that device.
 //  * All calls on a device share the one array and it keeps whatever the previous call left there.  Nothing has to be
 //    cleared: the statistics kernel overwrites every slot the normalising kernel later reads.  Two calls whose
 //    kernels overlap on the GPU (different streams, no dependency between them) race on it -- serialise them.
 extern "C" int32_t b200sd_groupnorm_static_scratch(const b200sd_groupnorm_params* p, b200sd_stream_t stream) {
-    B200SD_CHECK_ARG(p && p->x1 && p->y && p->gamma && p->beta, "groupnorm_static_scratch: null pointer");
-    const int c2 = p->x2 ? p->c2 : 0;
-    const int C = p->c1 + c2;
-    B200SD_CHECK_ARG(p->n_img > 0 && p->hw > 0, "groupnorm_static_scratch: bad shape");
-    B200SD_CHECK_ARG(p->groups > 0 && p->groups <= 64 && C % p->groups == 0, "groupnorm_static_scratch: C=%d groups=%d",
-                     C, p->groups);
-    B200SD_CHECK_ARG(p->c1 % 4 == 0 && c2 % 4 == 0 && C / 4 <= 1024,
-                     "groupnorm_static_scratch: channels must be multiples of 4, C<=4096");
-    B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype) && H_DTYPE(p->out_dtype), "groupnorm_static_scratch: bad in_dtype / out_dtype");
-    B200SD_CHECK_ARG(ALIGNED16(p->x1) && (!p->x2 || ALIGNED16(p->x2)) && ALIGNED16(p->y) && (!p->raw || ALIGNED16(p->raw)),
-                     "groupnorm_static_scratch: pointers must be 16-byte aligned");
-    const int splits = gn_splits(p->n_img, p->hw);
-    const long long need = (long long)p->n_img * splits * p->groups * 2;
-    if (need > GN_STATIC_SCRATCH_FLOATS)
-        return set_error(B200SD_ERR_WORKSPACE,
-                         "groupnorm_static_scratch: needs %lld floats of scratch (n_img=%d x splits=%d x groups=%d x 2) but the "
-                         "built-in array holds %lld; use b200sd_groupnorm with a caller-owned workspace",
-                         need, p->n_img, splits, p->groups, GN_STATIC_SCRATCH_FLOATS);
-    float* scratch = nullptr;
-    const int32_t rc = gn_static_scratch_address(&scratch);
+    int32_t rc = gn_check(p, "groupnorm_static_scratch");
     if (rc != B200SD_OK) return rc;
-    const bool vec8 = p->c1 % 8 == 0 && c2 % 8 == 0;  // 8 channels per thread: 16-byte accesses on the 16-bit side
-    const int vpp = C / (vec8 ? 8 : 4);
-    int lanes = 256 / vpp;
-    if (lanes < 1) lanes = 1;
-    const int threads = vpp * lanes;
-    const size_t smem = (size_t)2 * lanes * C * sizeof(float);
-    cudaStream_t s = as_stream(stream);
-    const int chunks = splits * 2;
-    dim3 g1(splits, p->n_img), g2(chunks, p->n_img);
-    if (vec8) {
-        gn_stats_kernel<8><<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch);
-        gn_apply_kernel<8><<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch,
-                                                  p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
-                                                  p->out_dtype == B200SD_F16, chunks);
-    } else {
-        gn_stats_kernel<4><<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch);
-        gn_apply_kernel<4><<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch,
-                                                  p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
-                                                  p->out_dtype == B200SD_F16, chunks);
-    }
-    count_launch(2);
-    B200SD_CHECK_LAUNCH("groupnorm_static_scratch");
-    return B200SD_OK;
+    int splits = gn_splits(p->n_img, p->hw);
+    const long long per_split = (long long)p->n_img * p->groups * 2;
+    if (per_split > GN_STATIC_SCRATCH_FLOATS)
+        return set_error(B200SD_ERR_WORKSPACE,
+                         "groupnorm_static_scratch: needs %lld floats of scratch (n_img=%d x groups=%d x 2, one split) but the "
+                         "built-in array holds %lld; use b200sd_groupnorm with a caller-owned workspace",
+                         per_split, p->n_img, p->groups, GN_STATIC_SCRATCH_FLOATS);
+    if ((long long)splits * per_split > GN_STATIC_SCRATCH_FLOATS) splits = (int)(GN_STATIC_SCRATCH_FLOATS / per_split);
+    float* scratch = nullptr;
+    rc = gn_static_scratch_address(&scratch);
+    if (rc != B200SD_OK) return rc;
+    return gn_launch(p, splits, scratch, as_stream(stream), "groupnorm_static_scratch");
 }
