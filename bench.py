@@ -48,6 +48,10 @@ def parse():
     ap.add_argument("--scheduler", default="ddim", choices=["ddim", "dpm++2m", "euler"])
     ap.add_argument("--operand-dtype", default=None, choices=[None, "fp16", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-comparator", action="store_true",
+                    help="skip the same-box stock-torch bf16 comparator (tests/torch_gpu_baseline.py) and the bf16-operand sub-line")
+    ap.add_argument("--comparator-compile", default="auto", choices=["auto", "on", "off"],
+                    help="torch.compile arm of the comparator (the reference's DEVICE=triton); auto = on, under a wall-clock limit")
     ap.add_argument("--profile-only", action="store_true", help="one eager profiled pass, no timing (for ncu runs)")
     ap.add_argument("--shape-profile", action="store_true", help="per-(kernel, shape) CUDA-event times of one eager pass")
     return ap.parse_args()
@@ -134,32 +138,56 @@ def cpu_oracle_sample(size: int, denoise_steps: int, n_unet: int = 1):
 
 def run_reference(args):
     """`--impl reference`: the reference's own implementation of the path is diffusers on torch, which cannot be
-    installed here (no network, not in the wheelhouse); the timed stand-in is the fp32 CPU oracle, all host threads."""
+    installed here (no network, not in the wheelhouse); the timed stand-in is the fp32 CPU oracle, all host threads.
+
+    A "step" of this arm is a BOUNDED SAMPLE of the workload: one UNet forward of one image (CFG batch 2) at the
+    workload's resolution.  `steps` / `warmup` / `ms_per_step` on the line describe exactly those timed forwards (capped
+    by a wall-clock budget), `value` is the images/s they imply for the full workload (denoise_steps forwards + one
+    timed VAE decode per image) and is flagged `extrapolated`."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    budget_s = 200.0
-    t0 = time.perf_counter()
-    n = max(1, args.warmup + args.steps)
-    # first forward doubles as warm-up; cap the number of timed UNet forwards by the time budget
-    ips, info = cpu_oracle_sample(args.size, args.denoise_steps, n_unet=2)
-    est = info["unet_step_s"]
-    extra = int(max(0, min(args.steps - 1, (budget_s - (time.perf_counter() - t0)) / max(est, 1e-3) - 1)))
-    if extra > 0:
-        ips2, info2 = cpu_oracle_sample(args.size, args.denoise_steps, n_unet=extra)
-        info["unet_times_s"] += info2["unet_times_s"]
-        info["unet_step_s"] = min(info["unet_step_s"], info2["unet_step_s"])
-        ips = 1.0 / (args.denoise_steps * info["unet_step_s"] + info["vae_decode_s"])
-    sample = (f"{len(info['unet_times_s'])} UNet forwards (CFG batch 2, best taken) + 1 VAE decode at {args.size}^2 fp32, "
-              f"extrapolated to {args.denoise_steps} steps/image")
+    import torch
+    from oracle import sd21 as O
+    budget_s = float(os.environ.get("B200SD_REF_BUDGET_S", "200"))
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    hw = args.size // 8
+    t_begin = time.perf_counter()
+    unet = O.seeded_init_(O.UNet2DCondition(O.sd21_unet_config(sample_size=hw)), 0).eval()
+    vae = O.seeded_init_(O.VAEDecoder(O.VAEConfig()), 1).eval()
+    lat, ctx = O.seeded_inputs(1, hw, 1024)
+    x2 = torch.cat([lat, lat])
+    times, n_warm = [], 0
+    with torch.no_grad():
+        t0 = time.perf_counter()
+        vae.decode(lat / 0.18215)
+        t_vae = time.perf_counter() - t0
+        n_warm = min(2, max(1, args.warmup))  # at most two untimed forwards: each costs seconds of host time
+        for _ in range(n_warm):
+            unet(x2, 961.0, ctx)
+        for _ in range(max(1, args.steps)):
+            t0 = time.perf_counter()
+            unet(x2, 961.0, ctx)
+            times.append(time.perf_counter() - t0)
+            if time.perf_counter() - t_begin + 1.5 * times[-1] > budget_s:
+                break
+    tu = statistics.mean(times)
+    per_image = args.denoise_steps * tu + t_vae
+    ips = 1.0 / per_image
+    sample = (f"{len(times)} timed UNet forwards of one image (CFG batch 2, mean taken; {n_warm} untimed before) + 1 VAE "
+              f"decode at {args.size}^2 fp32; images/s = 1 / ({args.denoise_steps} x forward + decode)")
     line = {"impl": "reference", "metric": "sd21_images_per_sec", "value": ips, "unit": "images/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 / ips, "higher_is_better": True,
+            "steps": len(times), "warmup": n_warm, "ms_per_step": 1000.0 * tu, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+            "extrapolated": True,
+            "step_is": "one fp32 UNet forward of one image (CFG batch 2) on the host cores -- a bounded sample, not a pass",
+            "requested": {"steps": args.steps, "warmup": args.warmup, "budget_s": budget_s},
             # same workload as the B200 arm; the bounded CPU sample runs one image (CFG batch 2) at a time -- the
             # oracle's images/s does not depend on how many prompts are queued
             "config": dict(workload_config(args, args.batch), cpu_sample_batch=1),
-            "cpu_baseline": {"value": ips, "unit": "images/s", "cores": info["cores"], "kind": "port", "sample": sample,
-                             "unet_step_s": info["unet_step_s"], "vae_decode_s": info["vae_decode_s"]},
+            "cpu_baseline": {"value": ips, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample,
+                             "unet_step_s": tu, "unet_step_s_min": min(times), "vae_decode_s": t_vae},
             "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     _emit(line)
@@ -369,16 +397,89 @@ def run_b200(args):
         torch.cuda.synchronize()
         line["single_request"] = {"batch": 1, "ms_per_image": round(e0.elapsed_time(e1) / 3, 3),
                                   "images_per_s": round(3000.0 / e0.elapsed_time(e1), 4)}
+        # UNet step alone at batch 1 (the graph-replayed denoising loop without the VAE decode)
+        e0.record()
+        pipe.denoise(lat1, ctx1, args.denoise_steps)
+        e1.record()
+        torch.cuda.synchronize()
+        line["single_request"]["unet_step_ms"] = round(e0.elapsed_time(e1) / args.denoise_steps, 3)
+        # self check: image 0 of the batch-B pass against the same prompt/latent run alone at batch 1 -- other tilings
+        # (no CTA pairs, split-K at the low levels), so not bit-equal: the two differ by fp32 summation order and the
+        # 16-bit roundings that flips, compounded over the schedule.  PSNR on the uint8 images, peak 255.
+        img_b = one_pass_device()[0].float()
+        img_1 = pipe.decode(pipe.denoise(lat1, ctx1, args.denoise_steps), "uint8")[0].float()
+        mse = float(((img_b - img_1) ** 2).mean())
+        psnr = 99.0 if mse == 0 else 10.0 * __import__("math").log10(255.0 ** 2 / mse)
+        spread = float(img_b.std())
+        ok = psnr >= 40.0 and spread > 1.0   # (a constant image would also "match")
+        line["self_check"] = "ok" if ok else "FAILED"
+        line["self_check_detail"] = {"what": f"image 0 of the batch-{B} pass vs the same request at batch 1 (uint8 PSNR >= 40 dB)",
+                                     "psnr_db": round(psnr, 2), "max_abs_u8": int((img_b - img_1).abs().max()),
+                                     "image_std_u8": round(spread, 2)}
+    if not args.no_comparator and world == 1:
+        # ---- the same throughput with the reference's storage dtype (bf16 operands): driver-observed, not asserted
+        usd2, _ = random_state_dicts(ucfg, vcfg, 0)
+        unet_bf = b200sd.B200UNet(usd2, ucfg, dev, op_dtype=torch.bfloat16)
+        del usd2
+        pipe_bf = b200sd.B200Pipeline(unet_bf, vae, b200sd.B200Scheduler(args.scheduler, ucfg.prediction_type, dev))
+        ctx_bf = ctx2_dev.to(torch.bfloat16)
+        for _ in range(2):
+            pipe_bf.decode(pipe_bf.denoise(lat_dev, ctx_bf, args.denoise_steps), "uint8")
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            pipe_bf.decode(pipe_bf.denoise(lat_dev, ctx_bf, args.denoise_steps), "uint8")
+        e1.record()
+        torch.cuda.synchronize()
+        line["bf16_operands"] = {"value": round(B * 3000.0 / e0.elapsed_time(e1), 4), "unit": "images/s",
+                                 "ms_per_step": round(e0.elapsed_time(e1) / 3, 3), "passes": 3,
+                                 "note": "same kernels with bf16 tensor-core operands (the reference's DTYPE, app/run-sd.py:39)"}
+        del pipe_bf, unet_bf
     if not args.no_cpu_baseline and world == 1:
         ips, info = cpu_oracle_sample(args.size, args.denoise_steps, n_unet=2)
         line["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": info["cores"], "kind": "port",
                                 "sample": f"2 UNet forwards (CFG batch 2, best taken) + 1 VAE decode at {args.size}^2 fp32, "
                                           f"extrapolated to {args.denoise_steps} steps/image",
                                 "unet_step_s": round(info["unet_step_s"], 3), "vae_decode_s": round(info["vae_decode_s"], 3)}
+    if not args.no_comparator and world == 1:
+        # free this process's GPU memory first: the comparator builds its own fp32 -> bf16 copy of the model
+        del pipe, unet, vae
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
+        line["gpu_comparator"] = gpu_comparator(args, local)
     _emit(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def gpu_comparator(args, gpu_index: int) -> dict:
+    """Same box, same run: stock PyTorch bf16 on the same architecture -- eager (cuDNN / cuBLAS / fused SDPA: the
+    reference's DEVICE=cuda, app/run-sd.py:106-107) and torch.compile(mode="max-autotune-no-cudagraphs") of the UNet
+    (DEVICE=triton, app/run-sd.py:109-116).  Runs tests/torch_gpu_baseline.py in a subprocess (it is test
+    infrastructure: it moves the fp32 oracle's modules to the GPU); a leg that fails or runs out of time reports why."""
+    out = {"what": "stock torch bf16 on the oracle's modules, same GPU, same process tree", "unit": "images/s"}
+    script = str(ROOT / "tests" / "torch_gpu_baseline.py")
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", str(gpu_index)))
+    legs = [("batch16_eager", [str(args.batch)], 240), ("batch1_eager", ["1"], 180)]
+    if args.comparator_compile != "off":
+        legs += [("batch16_compile", [str(args.batch), "--compile"], 600), ("batch1_compile", ["1", "--compile"], 420)]
+    for name, extra, limit in legs:
+        t0 = time.perf_counter()
+        try:
+            r = subprocess.run([sys.executable, script, *extra, "--size", str(args.size), "--steps", str(args.denoise_steps)],
+                               capture_output=True, text=True, timeout=limit, env=env)
+            last = [ln for ln in r.stdout.strip().splitlines() if ln.startswith("{")]
+            out[name] = json.loads(last[-1]) if r.returncode == 0 and last else \
+                {"unavailable": f"exit {r.returncode}: {(r.stderr or r.stdout).strip().splitlines()[-1][:200] if (r.stderr or r.stdout).strip() else ''}"}
+        except subprocess.TimeoutExpired:
+            out[name] = {"unavailable": f"timed out after {limit} s"}
+        except Exception as e:  # noqa: BLE001
+            out[name] = {"unavailable": repr(e)[:200]}
+        out[name]["wall_s"] = round(time.perf_counter() - t0, 1)
+    return out
 
 
 def classes_share_vae(prof, pipe) -> float:

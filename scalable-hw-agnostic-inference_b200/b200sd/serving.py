@@ -276,6 +276,26 @@ class Dispatcher:
         return self.engines[self.pick()](**model_args)
 
 
+def _random_clip_state_dict(ccfg, seed: int):
+    """seeded text-tower weights in transformers' CLIPTextModel layout"""
+    import torch
+    g = torch.Generator("cpu").manual_seed(seed)
+    c, f = ccfg.hidden_size, ccfg.intermediate_size
+    csd = {"text_model.embeddings.token_embedding.weight": torch.randn(ccfg.vocab_size, c, generator=g),
+           "text_model.embeddings.position_embedding.weight": 0.1 * torch.randn(ccfg.max_position_embeddings, c, generator=g),
+           "text_model.final_layer_norm.weight": torch.ones(c), "text_model.final_layer_norm.bias": torch.zeros(c)}
+    for i in range(ccfg.num_hidden_layers):
+        q = f"text_model.encoder.layers.{i}."
+        for n in ("q_proj", "k_proj", "v_proj", "out_proj"):
+            csd[q + f"self_attn.{n}.weight"] = torch.randn(c, c, generator=g) * c ** -0.5
+            csd[q + f"self_attn.{n}.bias"] = torch.zeros(c)
+        for n in ("layer_norm1", "layer_norm2"):
+            csd[q + n + ".weight"], csd[q + n + ".bias"] = torch.ones(c), torch.zeros(c)
+        csd[q + "mlp.fc1.weight"], csd[q + "mlp.fc1.bias"] = torch.randn(f, c, generator=g) * c ** -0.5, torch.zeros(f)
+        csd[q + "mlp.fc2.weight"], csd[q + "mlp.fc2.bias"] = torch.randn(c, f, generator=g) * f ** -0.5, torch.zeros(c)
+    return csd
+
+
 def build_random_init_pipeline(model_id: str, device: str = "cuda:0", seed: int = 0):
     """There are no checkpoints on this box (no network): builds the SD2.1 architecture named by `model_id`
     (`...-base` = 512^2 epsilon-prediction, otherwise 768^2 v-prediction) with seeded random weights.
@@ -296,22 +316,29 @@ def build_random_init_pipeline(model_id: str, device: str = "cuda:0", seed: int 
         # the SD2.1 text tower with seeded weights in transformers' layout + the placeholder tokenizer (no vocabulary here)
         from .clip import B200CLIPTextEncoder, CLIPTextConfig, PromptEncoder
         ccfg = CLIPTextConfig()
-        g = torch.Generator("cpu").manual_seed(seed + 2)
-        c, f = ccfg.hidden_size, ccfg.intermediate_size
-        csd = {"text_model.embeddings.token_embedding.weight": torch.randn(ccfg.vocab_size, c, generator=g),
-               "text_model.embeddings.position_embedding.weight": 0.1 * torch.randn(ccfg.max_position_embeddings, c, generator=g),
-               "text_model.final_layer_norm.weight": torch.ones(c), "text_model.final_layer_norm.bias": torch.zeros(c)}
-        for i in range(ccfg.num_hidden_layers):
-            q = f"text_model.encoder.layers.{i}."
-            for n in ("q_proj", "k_proj", "v_proj", "out_proj"):
-                csd[q + f"self_attn.{n}.weight"] = torch.randn(c, c, generator=g) * c ** -0.5
-                csd[q + f"self_attn.{n}.bias"] = torch.zeros(c)
-            for n in ("layer_norm1", "layer_norm2"):
-                csd[q + n + ".weight"], csd[q + n + ".bias"] = torch.ones(c), torch.zeros(c)
-            csd[q + "mlp.fc1.weight"], csd[q + "mlp.fc1.bias"] = torch.randn(f, c, generator=g) * c ** -0.5, torch.zeros(f)
-            csd[q + "mlp.fc2.weight"], csd[q + "mlp.fc2.bias"] = torch.randn(c, f, generator=g) * f ** -0.5, torch.zeros(c)
+        csd = _random_clip_state_dict(ccfg, seed + 2)
         text = PromptEncoder(B200CLIPTextEncoder(csd, ccfg, dev))
     return B200Pipeline(unet, vae, B200Scheduler("ddim", ucfg.prediction_type, dev), text_encoder=text)
+
+
+def build_tiny_pipeline(model_id: str, device: str = "cuda:0", seed: int = 0):
+    """B200SD_MODEL_SIZE=tiny: the same modules on a small UNet / VAE / text tower (16x16 latents, 128 x 128 images), so a
+    test can bring the whole host up -- warm-up, batcher, routes -- in seconds.  Not a serving configuration."""
+    import torch
+
+    from . import B200Pipeline, B200Scheduler, B200UNet, B200VAEDecoder, UNetConfig, VAEConfig
+    from ._randinit import random_state_dicts
+    from .clip import B200CLIPTextEncoder, CLIPTextConfig, PromptEncoder
+
+    ucfg = UNetConfig(sample_size=16, block_out_channels=(64, 128, 128, 128), attention_head_dim=(1, 2, 2, 2),
+                      cross_attention_dim=128)
+    vcfg = VAEConfig(block_out_channels=(64, 64, 128, 128))
+    usd, vsd = random_state_dicts(ucfg, vcfg, seed)
+    dev = torch.device(device)
+    ccfg = CLIPTextConfig(hidden_size=128, intermediate_size=256, num_hidden_layers=2, num_attention_heads=2)
+    text = PromptEncoder(B200CLIPTextEncoder(_random_clip_state_dict(ccfg, seed + 2), ccfg, dev))
+    return B200Pipeline(B200UNet(usd, ucfg, dev), B200VAEDecoder(vsd, vcfg, dev),
+                        B200Scheduler("ddim", ucfg.prediction_type, dev), text_encoder=text)
 
 
 def create_app(engine: Engine, cfg: Dict[str, str], sink: Optional[MetricSink] = None):
@@ -386,8 +413,11 @@ def create_app_from_env():
     n_gpus = int(os.environ.get("B200SD_GPUS", "1"))
     devices = [os.environ.get("B200SD_CUDA_DEVICE", "cuda:0")] if n_gpus == 1 else [f"cuda:{i}" for i in range(n_gpus)]
     engines = []
+    import torch
+    builder = build_tiny_pipeline if os.environ.get("B200SD_MODEL_SIZE", "full") == "tiny" else build_random_init_pipeline
     for d in devices:
-        pipe = build_random_init_pipeline(cfg["MODEL_ID"], d)
+        with torch.cuda.device(torch.device(d)):  # weights, workspaces and the lazily set kernel attributes land on GPU d
+            pipe = builder(cfg["MODEL_ID"], d)
         pipe.enable_attention_slicing()
         eng = BatchingEngine(pipe, cfg["NUM_OF_RUNS_INF"], max_batch=int(os.environ.get("B200SD_MAX_BATCH", "16")),
                              max_wait_ms=float(os.environ.get("B200SD_BATCH_WAIT_MS", "5")))

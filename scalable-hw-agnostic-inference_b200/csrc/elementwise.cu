@@ -464,11 +464,14 @@ __global__ void denorm_u8_kernel(const void* __restrict__ x, int dt, uint8_t* __
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
          i += (long long)gridDim.x * blockDim.x) {
         const float4 v = load4(x, (size_t)i * 4, dt);
+        // ((x / 2 + 0.5).clamp(0, 1) * 255).round(): one rounding per operation as in the reference's fp32 tensor ops
+        // (explicit _rn intrinsics keep the compiler from contracting anything), rintf = round half to even = torch.round
+        auto q = [](float x) {
+            const float t = fminf(fmaxf(__fadd_rn(__fmul_rn(x, 0.5f), 0.5f), 0.f), 1.f);
+            return (unsigned char)rintf(__fmul_rn(t, 255.f));
+        };
         uchar4 o;
-        o.x = (unsigned char)rintf(fminf(fmaxf(v.x * 0.5f + 0.5f, 0.f), 1.f) * 255.f);
-        o.y = (unsigned char)rintf(fminf(fmaxf(v.y * 0.5f + 0.5f, 0.f), 1.f) * 255.f);
-        o.z = (unsigned char)rintf(fminf(fmaxf(v.z * 0.5f + 0.5f, 0.f), 1.f) * 255.f);
-        o.w = (unsigned char)rintf(fminf(fmaxf(v.w * 0.5f + 0.5f, 0.f), 1.f) * 255.f);
+        o.x = q(v.x), o.y = q(v.y), o.z = q(v.z), o.w = q(v.w);
         *reinterpret_cast<uchar4*>(out + i * 4) = o;
     }
 }

@@ -13,6 +13,7 @@ for p in (str(ROOT), str(PKG)):
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (B200, sm_100a)")
+    config.addinivalue_line("markers", "slow: minutes of host CPU time in the fp32 oracle (full-size, full-schedule parity)")
 
 
 @pytest.fixture(scope="session")
