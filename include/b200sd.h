@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200SD_ABI_VERSION 4
+#define B200SD_ABI_VERSION 5
 
 typedef struct CUstream_st* b200sd_stream_t; /* == cudaStream_t / CUstream */
 
@@ -89,8 +89,19 @@ typedef struct {
                                given), 1 = off, 2..8 = forced */
     int32_t act;            /* 0 = none, 1 = erf-GELU applied to (acc + bias) before the residual is added: the CLIP text
                                encoder's MLP (transformers CLIPMLP, hidden_act "gelu").  Not with geglu. */
+    float* tile_sums;       /* optional: the epilogue also writes, per 32-row slice of every 128-row output tile and per
+                               output column, (sum, sum of squares) of the values it stores (fp32, before the 16-bit
+                               rounding): [n_img][parts][n_out][2] with parts = b200sd_gemm_tile_sum_parts(p).  This is
+                               torch.nn.GroupNorm's statistics pass for the NEXT GroupNorm, taken while the tensor is
+                               still in registers (b200sd_gn_tile_sums reduces it); NULL = off */
+    int32_t rows_per_image; /* only with tile_sums on a plain [M, K] problem (img_h == 1, n_img == 1): rows of `out`
+                               that belong to one image; must be a multiple of 128.  0 for NHWC problems. */
 } b200sd_gemm_params;
 int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stream);
+/* slices per image that `tile_sums` would hold for this problem, or 0 if this problem cannot emit them (a tile that
+ * spans two images, GEGLU, split K, bias along M, a ragged last column chunk ...): the caller then runs the
+ * GroupNorm statistics pass as usual */
+int32_t b200sd_gemm_tile_sum_parts(const b200sd_gemm_params* p);
 /* bytes of workspace this problem would use if one were supplied (0 = it would not split K) */
 int64_t b200sd_gemm_workspace_bytes(const b200sd_gemm_params* p);
 /* the block_n the library would choose for this problem (weight packers for GEGLU need it) */
@@ -136,9 +147,28 @@ typedef struct {
     int32_t out_dtype;      /* B200SD_BF16 or B200SD_F16 */
     float* workspace;
     int64_t workspace_bytes;
+    const float* sums;      /* optional fp32 [n_img, groups, 2] = (sum, sum of squares) per image and group: when given,
+                               the statistics pass is skipped and these are normalised with (no workspace needed) */
+    int64_t stat_hw;        /* with `sums`: pixels per image the sums were taken over (0 = hw).  Larger than hw when the
+                               image is split over several GPUs and the sums were all-reduced */
+    float* sums_out;        /* optional fp32 [n_img, groups, 2]: when given, ONLY the statistics are computed and
+                               written here (y may be NULL) -- the first half of a GroupNorm whose sums are combined
+                               across GPUs before b200sd_groupnorm is called again with `sums` */
 } b200sd_groupnorm_params;
 int64_t b200sd_groupnorm_workspace_bytes(const b200sd_groupnorm_params* p);
 int32_t b200sd_groupnorm(const b200sd_groupnorm_params* p, b200sd_stream_t stream);
+/* Reduces the per-tile column sums a producing GEMM left in `tile_sums` (see b200sd_gemm_params) to per-(image, group)
+ * sums for b200sd_groupnorm's `sums`.  The normalised tensor may be the channel concat of two producers' outputs
+ * (torch.cat([h, skip], dim=1) in the up blocks): groups then run over the concatenation.  Fixed reduction order. */
+typedef struct {
+    const float* tile_sums1; /* [n_img, parts1, c1, 2] */
+    int32_t parts1, c1;
+    const float* tile_sums2; /* [n_img, parts2, c2, 2] or NULL */
+    int32_t parts2, c2;
+    int32_t n_img, groups;
+    float* sums;             /* out: fp32 [n_img, groups, 2] */
+} b200sd_gn_tile_sums_params;
+int32_t b200sd_gn_tile_sums(const b200sd_gn_tile_sums_params* p, b200sd_stream_t stream);
 /* GroupNorm for hosts that cannot supply scratch memory -- it has no counterpart in the reference.
  * Who needs it: an FFI front end (cgo, JNI, ctypes) that is handed device pointers for its tensors by some other
  * component and links no CUDA runtime of its own, so it has nothing to allocate a workspace with; and a server whose

@@ -7,7 +7,7 @@ from pathlib import Path
 
 _HERE = Path(__file__).resolve().parent
 LIB_PATH = _HERE / "libb200sd.so"
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 BF16, F32, F16 = 1, 2, 3
 
@@ -20,7 +20,7 @@ class GemmParams(C.Structure):
                 ("bias_along_m", c_i32), ("row_bias", c_vp), ("row_bias_stride", c_i64), ("residual", c_vp),
                 ("residual_dtype", c_i32), ("ld_res", c_i64), ("out", c_vp), ("out_dtype", c_i32), ("ld_out", c_i64),
                 ("geglu", c_i32), ("block_n", c_i32), ("workspace", c_vp), ("workspace_bytes", c_i64),
-                ("split_k", c_i32), ("act", c_i32)]
+                ("split_k", c_i32), ("act", c_i32), ("tile_sums", c_vp), ("rows_per_image", c_i32)]
 
 
 class AttentionParams(C.Structure):
@@ -37,7 +37,13 @@ class EmbedParams(C.Structure):
 class GroupNormParams(C.Structure):
     _fields_ = [("x1", c_vp), ("c1", c_i32), ("x2", c_vp), ("c2", c_i32), ("in_dtype", c_i32), ("n_img", c_i32),
                 ("hw", c_i32), ("groups", c_i32), ("eps", c_f32), ("gamma", c_vp), ("beta", c_vp), ("silu", c_i32),
-                ("y", c_vp), ("raw", c_vp), ("out_dtype", c_i32), ("workspace", c_vp), ("workspace_bytes", c_i64)]
+                ("y", c_vp), ("raw", c_vp), ("out_dtype", c_i32), ("workspace", c_vp), ("workspace_bytes", c_i64),
+                ("sums", c_vp), ("stat_hw", c_i64), ("sums_out", c_vp)]
+
+
+class GnTileSumsParams(C.Structure):
+    _fields_ = [("tile_sums1", c_vp), ("parts1", c_i32), ("c1", c_i32), ("tile_sums2", c_vp), ("parts2", c_i32),
+                ("c2", c_i32), ("n_img", c_i32), ("groups", c_i32), ("sums", c_vp)]
 
 
 class LayerNormParams(C.Structure):
@@ -88,6 +94,8 @@ SYMBOLS = {
     "b200sd_gemm": (c_i32, [C.POINTER(GemmParams), c_vp]),
     "b200sd_gemm_pick_block_n": (c_i32, [c_i32, c_i32]),
     "b200sd_gemm_workspace_bytes": (c_i64, [C.POINTER(GemmParams)]),
+    "b200sd_gemm_tile_sum_parts": (c_i32, [C.POINTER(GemmParams)]),
+    "b200sd_gn_tile_sums": (c_i32, [C.POINTER(GnTileSumsParams), c_vp]),
     "b200sd_attention": (c_i32, [C.POINTER(AttentionParams), c_vp]),
     "b200sd_groupnorm_workspace_bytes": (c_i64, [C.POINTER(GroupNormParams)]),
     "b200sd_groupnorm": (c_i32, [C.POINTER(GroupNormParams), c_vp]),

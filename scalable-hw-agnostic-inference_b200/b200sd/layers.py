@@ -23,8 +23,12 @@ def default_op_dtype() -> torch.dtype:
 
 
 def default_trunk_dtype() -> torch.dtype:
-    """dtype of the residual stream (the tensors every block adds into): fp32 unless B200SD_TRUNK_DTYPE says fp16/bf16"""
-    name = os.environ.get("B200SD_TRUNK_DTYPE", "fp32").lower()
+    """dtype of the residual stream (the tensors every block adds into).  fp16 by default: the reference keeps it in
+    bf16 (its only dtype, app/run-sd.py:39); fp16 has three more significand bits, every sum is still formed in fp32
+    inside the epilogue and rounded once, and stores saturate instead of overflowing.  Measured against the fp32 oracle at
+    768^2: single-step rel-L2 1.7e-3 with the fp16 trunk, 1.3e-3 with an fp32 trunk (B200SD_TRUNK_DTYPE=fp32), both far
+    inside the 1e-2 bound, for 3.5 % more images/s (the trunk is read and written by every memory-bound kernel)."""
+    name = os.environ.get("B200SD_TRUNK_DTYPE", "fp16").lower()
     return torch.float32 if name in ("fp32", "float32") else _OP_DTYPES[name]
 
 
@@ -58,6 +62,20 @@ def pack_geglu(w: torch.Tensor, b: torch.Tensor, block_n: int,
 
 
 # ------------------------------------------------------------------------------------------------ call helpers
+def tile_sums_of(x: torch.Tensor) -> Optional[torch.Tensor]:
+    """the column-sum table the kernel that wrote `x` attached to it (Kernels.conv3x3 / linear with gn_next), if any.
+    It rides on the tensor OBJECT, so a tensor that merely reuses the address later never inherits it; code that takes a
+    view of such a tensor and passes the view on copies it with `keep_tile_sums`."""
+    return getattr(x, "_b200_tile_sums", None)
+
+
+def keep_tile_sums(view: torch.Tensor, src: torch.Tensor) -> torch.Tensor:
+    t = tile_sums_of(src)
+    if t is not None:
+        view._b200_tile_sums = t
+    return view
+
+
 class Kernels:
     """Helper bound to one device: owns the GroupNorm scratch and the dtype policy."""
 
@@ -68,6 +86,8 @@ class Kernels:
         self.op_dtype = op_dtype or default_op_dtype()
         assert self.op_dtype in (torch.float16, torch.bfloat16)
         self._gn_ws: Optional[torch.Tensor] = None
+        # GroupNorm statistics from the producing kernel's epilogue instead of a pass over the tensor (B200SD_GN_FUSE=0: off)
+        self.fuse_gn_stats = os.environ.get("B200SD_GN_FUSE", "1") != "0"
         # split-K scratch for GEMMs with fewer output tiles than SMs; zero-filled once, the kernel keeps its counters clean
         self.gemm_ws = torch.zeros(int(os.environ.get("B200SD_GEMM_WS_MB", "96")) << 18, device=device,
                                    dtype=torch.float32) if device.type == "cuda" else None
@@ -80,12 +100,30 @@ class Kernels:
 
     def groupnorm(self, x1: torch.Tensor, x2: Optional[torch.Tensor], gamma, beta, eps: float, silu: bool,
                   want_raw: bool = False, groups: int = 32):
+        """GroupNorm(+SiLU) of x1 (or of the channel concat [x1, x2]).  When the kernels that produced x1 (and x2) left
+        their column sums behind (`tile_sums_of`), the statistics pass over the tensors is skipped: a small kernel reduces
+        those tables to per-(image, group) sums and only the normalising pass reads the activations."""
         n, h, w, c1 = x1.shape
         c = c1 + (x2.shape[-1] if x2 is not None else 0)
         y = torch.empty(n, h, w, c, device=self.device, dtype=self.op_dtype)
         raw = torch.empty_like(y) if want_raw else None
-        ops.groupnorm(x1, x2, n, h * w, groups, eps, gamma, beta, silu, y, raw, self.gn_workspace(n, h * w, groups))
+        t1 = tile_sums_of(x1)
+        t2 = tile_sums_of(x2) if x2 is not None else None
+        if self.fuse_gn_stats and t1 is not None and (x2 is None or t2 is not None):
+            sums = torch.empty(n, groups, 2, device=self.device, dtype=torch.float32)
+            ops.gn_tile_sums(t1, t2, n, groups, sums)
+            ops.groupnorm(x1, x2, n, h * w, groups, eps, gamma, beta, silu, y, raw, None, sums, 0, None)
+        else:
+            ops.groupnorm(x1, x2, n, h * w, groups, eps, gamma, beta, silu, y, raw, self.gn_workspace(n, h * w, groups))
         return (y, raw) if want_raw else y
+
+    def _tile_sums_buffer(self, gemm_args, n_img: int, cout: int, rows_per_image: int = 0) -> Optional[torch.Tensor]:
+        if not self.fuse_gn_stats:
+            return None
+        parts = ops.gemm_tile_sum_parts(*gemm_args, rows_per_image=rows_per_image)
+        if parts <= 0:
+            return None
+        return torch.empty(n_img, parts, cout, 2, device=self.device, dtype=torch.float32)
 
     def layernorm(self, x: torch.Tensor, gamma, beta, eps: float = 1e-5) -> torch.Tensor:
         y = torch.empty(x.shape, device=self.device, dtype=self.op_dtype)
@@ -93,8 +131,9 @@ class Kernels:
         return y
 
     def conv3x3(self, a: torch.Tensor, w: torch.Tensor, bias, *, row_bias=None, residual=None,
-                out_dtype=None) -> torch.Tensor:
-        """a 16-bit NHWC, w packed [Cout, 9*Cin]; stride 1, pad 1."""
+                out_dtype=None, gn_next: bool = False) -> torch.Tensor:
+        """a 16-bit NHWC, w packed [Cout, 9*Cin]; stride 1, pad 1.  gn_next: the output feeds a GroupNorm -- have the
+        epilogue emit its column sums (when this problem's tiling allows it) and attach them to the result."""
         n, h, wd, cin = a.shape
         cout = w.shape[0]
         out = torch.empty(n, h, wd, cout, device=self.device, dtype=out_dtype or self.trunk_dtype)
@@ -102,22 +141,36 @@ class Kernels:
         if row_bias is not None and row_bias.shape[0] > 1:
             rb_stride = row_bias.stride(0)
         res2 = residual.view(-1, cout) if residual is not None else None
-        ops.gemm(a, n, h, wd, cin, 9, w, bias, False, row_bias, rb_stride, res2, out.view(-1, cout), False, 0,
-                 self.gemm_ws, 0)
+        args = (a, n, h, wd, cin, 9, w, bias, False, row_bias, rb_stride, res2, out.view(-1, cout), False, 0)
+        ts = self._tile_sums_buffer(args, n, cout) if gn_next else None
+        if ts is not None:
+            ops.gemm(*args, None, 1, 0, ts, 0)
+            out._b200_tile_sums = ts
+        else:
+            ops.gemm(*args, self.gemm_ws, 0)
         return out
 
     def linear(self, a: torch.Tensor, w: torch.Tensor, bias, *, residual=None, out_dtype=None, geglu=False,
                out: Optional[torch.Tensor] = None, bias_along_m: bool = False, block_n: int = 0,
-               split_k: int = 0, gelu: bool = False) -> torch.Tensor:
-        """a 16-bit [M, K] (any leading dims), w 16-bit [N, K].  gelu: erf-GELU on (a w^T + bias), before the residual."""
+               split_k: int = 0, gelu: bool = False, gn_rows_per_image: int = 0) -> torch.Tensor:
+        """a 16-bit [M, K] (any leading dims), w 16-bit [N, K].  gelu: erf-GELU on (a w^T + bias), before the residual.
+        gn_rows_per_image > 0: the output is an NHWC activation of that many pixels per image and feeds a GroupNorm --
+        emit the column sums (see conv3x3)."""
         k = a.shape[-1]
         m = a.numel() // k
         n_cols = w.shape[0] // 2 if geglu else w.shape[0]
         if out is None:
             out = torch.empty(*a.shape[:-1], n_cols, device=self.device, dtype=out_dtype or self.trunk_dtype)
         res2 = residual.view(m, n_cols) if residual is not None else None
-        ops.gemm(a, 1, 1, m, k, 1, w, bias, bias_along_m, None, 0, res2, out.view(m, n_cols), geglu, block_n,
-                 self.gemm_ws, split_k, 1 if gelu else 0)
+        args = (a, 1, 1, m, k, 1, w, bias, bias_along_m, None, 0, res2, out.view(m, n_cols), geglu, block_n)
+        ts = None
+        if gn_rows_per_image > 0 and split_k <= 1 and m % gn_rows_per_image == 0:
+            ts = self._tile_sums_buffer(args, m // gn_rows_per_image, n_cols, gn_rows_per_image)
+        if ts is not None:
+            ops.gemm(*args, None, 1, 1 if gelu else 0, ts, gn_rows_per_image)
+            out._b200_tile_sums = ts
+        else:
+            ops.gemm(*args, self.gemm_ws, split_k, 1 if gelu else 0)
         return out
 
     def im2col(self, x: torch.Tensor, n_img: int, stride: int, k_pad: int) -> torch.Tensor:
@@ -170,12 +223,13 @@ def run_resnet(K: Kernels, P: ResnetParams, x: torch.Tensor, skip: Optional[torc
         a, raw = K.groupnorm(x, None, P.n1_g, P.n1_b, eps, True), None
     if temb_table is not None:
         lo, hi = P.temb_slice
-        h1 = K.conv3x3(a, P.w1, None, row_bias=temb_table[:, lo:hi], out_dtype=K.op_dtype)
+        h1 = K.conv3x3(a, P.w1, None, row_bias=temb_table[:, lo:hi], out_dtype=K.op_dtype, gn_next=True)
     else:
-        h1 = K.conv3x3(a, P.w1, P.b1, out_dtype=K.op_dtype)
+        h1 = K.conv3x3(a, P.w1, P.b1, out_dtype=K.op_dtype, gn_next=True)
     b = K.groupnorm(h1, None, P.n2_g, P.n2_b, eps, True)
     if P.has_shortcut:
         res = K.linear(raw, P.ws, P.bs)  # 1x1 conv == linear over pixels
     else:
         res = x
-    return K.conv3x3(b, P.w2, P.b2, residual=res)
+    # every resnet output is normalised next (a transformer's GroupNorm, the next resnet's norm1, conv_norm_out)
+    return K.conv3x3(b, P.w2, P.b2, residual=res, gn_next=True)

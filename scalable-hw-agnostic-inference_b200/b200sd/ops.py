@@ -103,8 +103,8 @@ def _nbytes(*ts) -> float:
 
 
 # ------------------------------------------------------------------------------------------------ impls
-def _gemm(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, row_bias_stride, residual, out,
-          geglu, block_n, workspace=None, split_k=0, act=0):
+def _gemm_params(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, row_bias_stride, residual, out,
+                 geglu, block_n, workspace=None, split_k=0, act=0, tile_sums=None, rows_per_image=0):
     p = L.GemmParams()
     p.a, p.a_dtype, p.n_img, p.img_h, p.img_w, p.cin, p.taps = _ptr(a), _dt(a), n_img, img_h, img_w, cin, taps
     p.w, p.w_dtype, p.n_out = _ptr(w), _dt(w), w.shape[0]
@@ -117,6 +117,24 @@ def _gemm(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, ro
     p.geglu, p.block_n, p.split_k, p.act = int(geglu), block_n, split_k, act
     if workspace is not None:
         p.workspace, p.workspace_bytes = _ptr(workspace), workspace.numel() * workspace.element_size()
+    if tile_sums is not None:
+        assert tile_sums.dtype == torch.float32 and tile_sums.is_contiguous()
+        p.tile_sums, p.rows_per_image = _ptr(tile_sums), rows_per_image
+    return p
+
+
+def gemm_tile_sum_parts(*args, rows_per_image=0) -> int:
+    """slices per image of the column-sum table this problem's epilogue can emit for the next GroupNorm (0 = it cannot);
+    same arguments as `gemm`"""
+    p = _gemm_params(*args)
+    p.rows_per_image = rows_per_image
+    return int(L.load().b200sd_gemm_tile_sum_parts(C.byref(p)))
+
+
+def _gemm(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, row_bias_stride, residual, out,
+          geglu, block_n, workspace=None, split_k=0, act=0, tile_sums=None, rows_per_image=0):
+    p = _gemm_params(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, row_bias_stride, residual, out,
+                     geglu, block_n, workspace, split_k, act, tile_sums, rows_per_image)
     m = n_img * img_h * img_w
     _run("gemm", 2.0 * m * w.shape[0] * taps * cin, L.load().b200sd_gemm, p,
          f"M{m} N{w.shape[0]} K{taps * cin} taps{taps} img{n_img}x{img_h}x{img_w}{' geglu' if geglu else ''}")
@@ -147,7 +165,18 @@ def _embed_tokens(ids, token_table, position_table, out):
     _run("embed_tokens", _nbytes(out) * 2, L.load().b200sd_embed_tokens, p, f"rows{p.rows} dim{p.dim}")
 
 
-def _groupnorm(x1, x2, n_img, hw, groups, eps, gamma, beta, silu, y, raw, workspace):
+def _gn_tile_sums(t1, t2, n_img, groups, sums):
+    """[n_img, parts, C, 2] column-sum tables of one or two producers -> per-(image, group) sums [n_img, groups, 2]"""
+    p = L.GnTileSumsParams()
+    p.tile_sums1, p.parts1, p.c1 = _ptr(t1), t1.shape[1], t1.shape[2]
+    if t2 is not None:
+        p.tile_sums2, p.parts2, p.c2 = _ptr(t2), t2.shape[1], t2.shape[2]
+    p.n_img, p.groups, p.sums = n_img, groups, _ptr(sums)
+    assert t1.shape[0] == n_img and (t2 is None or t2.shape[0] == n_img) and sums.numel() == n_img * groups * 2
+    _run("gn_tile_sums", _nbytes(t1, t2), L.load().b200sd_gn_tile_sums, p, f"n{n_img} parts{p.parts1}+{p.parts2} C{p.c1}+{p.c2}")
+
+
+def _groupnorm(x1, x2, n_img, hw, groups, eps, gamma, beta, silu, y, raw, workspace, sums=None, stat_hw=0, sums_out=None):
     if x2 is not None:
         assert x2.dtype == x1.dtype
     if raw is not None:
@@ -157,11 +186,21 @@ def _groupnorm(x1, x2, n_img, hw, groups, eps, gamma, beta, silu, y, raw, worksp
     p.x2, p.c2 = (_ptr(x2), x2.shape[-1]) if x2 is not None else (None, 0)
     p.in_dtype, p.n_img, p.hw, p.groups, p.eps = _dt(x1), n_img, hw, groups, eps
     p.gamma, p.beta, p.silu = _ptr(gamma), _ptr(beta), int(silu)
-    p.y, p.raw, p.out_dtype = _ptr(y), _ptr(raw), _dt(y)
-    p.workspace, p.workspace_bytes = _ptr(workspace), workspace.numel() * workspace.element_size()
-    # algorithmic bytes: inputs read once for statistics and once to normalise, outputs written once
-    _run("groupnorm", 2 * _nbytes(x1, x2) + _nbytes(y, raw), L.load().b200sd_groupnorm, p,
-         f"n{n_img} hw{hw} C{p.c1 + p.c2} {x1.dtype}")
+    p.y, p.raw, p.out_dtype = _ptr(y), _ptr(raw), (_dt(y) if y is not None else L.F16)
+    if workspace is not None:
+        p.workspace, p.workspace_bytes = _ptr(workspace), workspace.numel() * workspace.element_size()
+    if sums is not None:
+        assert sums.dtype == torch.float32 and sums.numel() == n_img * groups * 2
+        p.sums, p.stat_hw = _ptr(sums), stat_hw
+    if sums_out is not None:
+        assert sums_out.dtype == torch.float32 and sums_out.numel() == n_img * groups * 2
+        p.sums_out = _ptr(sums_out)
+    # algorithmic bytes: inputs read once for statistics and once to normalise, outputs written once (with the
+    # statistics supplied, or only the statistics wanted, one read of the inputs)
+    reads = 1 if (sums is not None or sums_out is not None) else 2
+    work = reads * _nbytes(x1, x2) + (0.0 if sums_out is not None else _nbytes(y, raw))
+    kind = "groupnorm" if sums is None and sums_out is None else ("groupnorm_apply" if sums is not None else "groupnorm_stats")
+    _run(kind, work, L.load().b200sd_groupnorm, p, f"n{n_img} hw{hw} C{p.c1 + p.c2} {x1.dtype}")
 
 
 def _layernorm(x, eps, gamma, beta, y):
@@ -238,12 +277,15 @@ def umma_selftest(a: torch.Tensor, b: torch.Tensor, b_mn_major: bool) -> torch.T
 _SCHEMAS = {
     "gemm": ("(Tensor a, int n_img, int img_h, int img_w, int cin, int taps, Tensor w, Tensor? bias, bool bias_along_m, "
              "Tensor? row_bias, int row_bias_stride, Tensor? residual, Tensor(a!) out, bool geglu, int block_n, "
-             "Tensor(b!)? workspace=None, int split_k=0, int act=0) -> ()", _gemm),
+             "Tensor(b!)? workspace=None, int split_k=0, int act=0, Tensor(c!)? tile_sums=None, int rows_per_image=0) -> ()",
+             _gemm),
     "attention": ("(Tensor q, Tensor k, Tensor v, Tensor(a!) out, int batch, int heads, int sq, int skv, float scale, "
                   "bool causal=False) -> ()", _attention),
     "embed_tokens": ("(Tensor ids, Tensor token_table, Tensor position_table, Tensor(a!) out) -> ()", _embed_tokens),
-    "groupnorm": ("(Tensor x1, Tensor? x2, int n_img, int hw, int groups, float eps, Tensor gamma, Tensor beta, bool silu, "
-                  "Tensor(a!) y, Tensor(b!)? raw, Tensor(c!) workspace) -> ()", _groupnorm),
+    "groupnorm": ("(Tensor x1, Tensor? x2, int n_img, int hw, int groups, float eps, Tensor? gamma, Tensor? beta, bool silu, "
+                  "Tensor(a!)? y, Tensor(b!)? raw, Tensor(c!)? workspace, Tensor? sums=None, int stat_hw=0, "
+                  "Tensor(d!)? sums_out=None) -> ()", _groupnorm),
+    "gn_tile_sums": ("(Tensor t1, Tensor? t2, int n_img, int groups, Tensor(a!) sums) -> ()", _gn_tile_sums),
     "layernorm": ("(Tensor x, float eps, Tensor gamma, Tensor beta, Tensor(a!) y) -> ()", _layernorm),
     "im2col3x3": ("(Tensor x, int n_img, int n_src, int in_h, int in_w, int cin, int stride, Tensor(a!) out) -> ()",
                   _im2col3x3),
@@ -277,6 +319,7 @@ _register()
 gemm = torch.ops.b200sd.gemm
 attention = torch.ops.b200sd.attention
 groupnorm = torch.ops.b200sd.groupnorm
+gn_tile_sums = torch.ops.b200sd.gn_tile_sums
 layernorm = torch.ops.b200sd.layernorm
 im2col3x3 = torch.ops.b200sd.im2col3x3
 upsample2x = torch.ops.b200sd.upsample2x

@@ -12,7 +12,7 @@ import torch
 
 from . import ops
 from .config import UNetConfig
-from .layers import Kernels, ResnetParams, pack_conv3x3, pack_conv3x3_im2col, pack_geglu, run_resnet
+from .layers import Kernels, ResnetParams, keep_tile_sums, pack_conv3x3, pack_conv3x3_im2col, pack_geglu, run_resnet
 
 
 class _TransformerParams:
@@ -173,8 +173,11 @@ class B200UNet(torch.nn.Module):
         t2 = K.linear(g, T.ff2_w, T.ff2_b, residual=t, out_dtype=BF)
         # in place on the block's input (nothing else reads it): an fp32 residual that is also the output is added by a TMA
         # reduce in L2 instead of being read by the epilogue
+        # (the block's output is normalised next -- by the following resnet's norm1, possibly after a detour through the
+        # skip stack -- so the epilogue leaves its column sums where the tiling allows; that epilogue reads the residual)
         xr = x.view(m, c)
-        return K.linear(t2, T.pout_w, T.pout_b, residual=xr, out=xr).view(n, h, w, c)
+        o = K.linear(t2, T.pout_w, T.pout_b, residual=xr, out=xr, gn_rows_per_image=s)
+        return keep_tile_sums(o.view(n, h, w, c), o)
 
     # ---- the whole forward on NHWC tensors ---------------------------------------------------------------
     def forward_nhwc(self, latent: torch.Tensor, n_img: int, t: torch.Tensor, ctx_kv: List[torch.Tensor],
@@ -185,7 +188,8 @@ class B200UNet(torch.nn.Module):
         eps = cfg.norm_eps
         table = self.time_table(t)
         cols = self.K.im2col(latent, n_img, 1, 64)
-        h = K.linear(cols, self.conv_in_w, self.conv_in_b)
+        hw = latent.shape[1] * latent.shape[2]
+        h = K.linear(cols, self.conv_in_w, self.conv_in_b, gn_rows_per_image=hw)
         skips = [h]
         kv_i = 0
         for blk in self.down:
@@ -198,7 +202,8 @@ class B200UNet(torch.nn.Module):
             if blk["down"] is not None:
                 w, b = blk["down"]
                 c = h.shape[-1]
-                h = K.linear(K.im2col(h, h.shape[0], 2, 9 * c), w, b)
+                cols = K.im2col(h, h.shape[0], 2, 9 * c)
+                h = K.linear(cols, w, b, gn_rows_per_image=cols.shape[1] * cols.shape[2])
                 skips.append(h)
         h = run_resnet(K, self.mid_res[0], h, None, eps, table)
         h = self._transformer(self.mid_attn, h, ctx_kv[kv_i], ctx_len)
@@ -212,7 +217,7 @@ class B200UNet(torch.nn.Module):
                     kv_i += 1
             if blk["up"] is not None:
                 w, b = blk["up"]
-                h = K.conv3x3(K.upsample2x(h), w, b)
+                h = K.conv3x3(K.upsample2x(h), w, b, gn_next=True)
         a = K.groupnorm(h, None, self.out_g, self.out_b, eps, True)
         return K.conv3x3(a, self.conv_out_w, self.conv_out_b, out_dtype=torch.float32)
 

@@ -14,7 +14,7 @@ import torch
 
 from . import ops
 from .config import VAEConfig
-from .layers import Kernels, ResnetParams, pack_conv3x3, run_resnet
+from .layers import Kernels, ResnetParams, keep_tile_sums, pack_conv3x3, run_resnet
 
 
 class B200PostQuantConv(torch.nn.Module):
@@ -99,14 +99,15 @@ class B200VAEDecoder(torch.nn.Module):
             ops.softmax_rows(scores, probs, s, s, float(c) ** -0.5)
             K.linear(probs, vt, None, out=o[i])
         hr = h.view(n * s, c)  # in place on the block's input (dead after this)
-        return K.linear(o.view(n * s, c), self.wo, self.bo, residual=hr, out=hr).view(n, hh, ww, c)
+        r = K.linear(o.view(n * s, c), self.wo, self.bo, residual=hr, out=hr, gn_rows_per_image=s)
+        return keep_tile_sums(r.view(n, hh, ww, c), r)
 
     def decode_nhwc(self, z: torch.Tensor) -> torch.Tensor:
         """z fp32 NHWC [B, h, w, 4] (already divided by scaling_factor) -> fp32 NHWC [B, 8h, 8w, 3]."""
         K = self.K
         n = z.shape[0]
         z5 = torch.cat([z, torch.ones_like(z[..., :1])], dim=-1).contiguous()
-        h = K.linear(K.im2col(z5, n, 1, 64), self.conv_in_w, self.conv_in_b)
+        h = K.linear(K.im2col(z5, n, 1, 64), self.conv_in_w, self.conv_in_b, gn_rows_per_image=z.shape[1] * z.shape[2])
         h = run_resnet(K, self.mid_res[0], h, None, 1e-6, None)
         h = self._mid_attention(h)
         h = run_resnet(K, self.mid_res[1], h, None, 1e-6, None)
@@ -115,7 +116,7 @@ class B200VAEDecoder(torch.nn.Module):
                 h = run_resnet(K, R, h, None, 1e-6, None)
             if blk["up"] is not None:
                 w, b = blk["up"]
-                h = K.conv3x3(K.upsample2x(h), w, b)
+                h = K.conv3x3(K.upsample2x(h), w, b, gn_next=True)
         a = K.groupnorm(h, None, self.out_g, self.out_b, 1e-6, True)
         return K.conv3x3(a, self.conv_out_w, self.conv_out_b, out_dtype=torch.float32)
 

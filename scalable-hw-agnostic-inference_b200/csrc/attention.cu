@@ -163,6 +163,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_sync();  // set-up above overlaps the previous kernel's tail; Q/K/V are read and O written from here on
 
     // Warps 0 and 1 keep all 32 lanes in warp-uniform control flow and predicate only the asynchronous instructions
     // on one elected lane; barrier probes are made uniform with a vote.  Issued from inside an `if (lane == 0)`
@@ -459,7 +460,8 @@ static int32_t launch_attention(const CUtensorMap& tmQ, const CUtensorMap& tmK, 
         if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "attention smem attribute: %s", cudaGetErrorString(e));
         attr_set[dev] = true;
     }
-    attention_kernel<F16, EMU_MASK, PERSIST><<<grid, ATT_THREADS, ATT_SMEM, stream>>>(tmQ, tmK, tmV, kp);
+    B200SD_LAUNCH("attention_kernel", (attention_kernel<F16, EMU_MASK, PERSIST>), grid, dim3(ATT_THREADS), ATT_SMEM, stream, tmQ,
+                  tmK, tmV, kp);
     count_launch();
     B200SD_CHECK_LAUNCH("attention_kernel");
     return B200SD_OK;

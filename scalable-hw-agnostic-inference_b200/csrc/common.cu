@@ -1,5 +1,6 @@
 // Library plumbing: status / error string, device check, launch counter, TMA descriptor encoder.
 #include <atomic>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -31,6 +32,14 @@ int num_sms() {
         cached[dev] = n > 0 ? n : 148;
     }
     return cached[dev];
+}
+
+bool pdl_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("B200SD_PDL");
+        return !(e && e[0] == '0');
+    }();
+    return on;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,

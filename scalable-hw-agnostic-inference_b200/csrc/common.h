@@ -34,4 +34,37 @@ int32_t encode_tmap_2d(CUtensorMap* map, const void* base, int elem_bytes, uint6
 
 static inline cudaStream_t as_stream(b200sd_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
+// B200SD_PDL=0 launches every kernel fully serialised (no programmatic dependent launch)
+bool pdl_enabled();
+
+// One launch path for every kernel of the library: optional thread-block cluster, and the programmatic-dependent-launch
+// attribute (ptx.cuh, pdl_sync) so that consecutive kernels of a stream -- and of a captured CUDA graph -- overlap
+// one kernel's set-up with the previous kernel's tail.
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                        int cluster_x, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid, cfg.blockDim = block, cfg.dynamicSmemBytes = smem, cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    unsigned n = 0;
+    if (cluster_x > 1) {
+        attr[n].id = cudaLaunchAttributeClusterDimension;
+        attr[n].val.clusterDim.x = (unsigned)cluster_x, attr[n].val.clusterDim.y = 1, attr[n].val.clusterDim.z = 1;
+        ++n;
+    }
+    if (pdl_enabled()) {
+        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
+    cfg.attrs = attr, cfg.numAttrs = n;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+#define B200SD_LAUNCH(name, kernel, grid, block, smem, stream, ...)                                              \
+    do {                                                                                                         \
+        cudaError_t le__ = launch_kernel(kernel, grid, block, smem, stream, 1, __VA_ARGS__);                       \
+        if (le__ != cudaSuccess) return set_error(B200SD_ERR_CUDA, "%s launch: %s", name, cudaGetErrorString(le__)); \
+    } while (0)
+
 }  // namespace b200sd

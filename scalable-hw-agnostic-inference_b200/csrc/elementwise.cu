@@ -69,6 +69,7 @@ __device__ __forceinline__ void storev_h(void* base, size_t idx, const float (&v
 template <int VEC>
 __global__ void gn_stats_kernel(const void* __restrict__ x1, int c1, const void* __restrict__ x2, int c2, int dt,
                                 int hw, int groups, int splits, float* __restrict__ partial) {
+    pdl_sync();
     extern __shared__ float sm[];  // [lanes][C] sums, then [lanes][C] sums of squares
     const int C = c1 + c2;
     const int vpp = C / VEC;
@@ -124,7 +125,8 @@ template <int VEC>
 __global__ void gn_apply_kernel(const void* __restrict__ x1, int c1, const void* __restrict__ x2, int c2, int dt,
                                 int hw, int groups, int splits, const float* __restrict__ partial, float eps,
                                 const float* __restrict__ gamma, const float* __restrict__ beta, int silu,
-                                void* __restrict__ y, void* __restrict__ raw, int out_f16, int chunks) {
+                                void* __restrict__ y, void* __restrict__ raw, int out_f16, int chunks, float stat_hw) {
+    pdl_sync();
     __shared__ float s_mean[64], s_rstd[64];
     const int C = c1 + c2;
     const int vpp = C / VEC;
@@ -150,7 +152,7 @@ __global__ void gn_apply_kernel(const void* __restrict__ x1, int c1, const void*
         float a = 0.f, b = 0.f;
 #pragma unroll
         for (int k = 0; k < 8; ++k) a += s_pa[g][k], b += s_pb[g][k];
-        const float inv = 1.0f / ((float)cpg * (float)hw);
+        const float inv = 1.0f / ((float)cpg * stat_hw);  // stat_hw = pixels the sums cover (hw, or the whole image's)
         const float mean = a * inv;
         const float var = fmaxf(b * inv - mean * mean, 0.f);
         s_mean[g] = mean, s_rstd[g] = rsqrtf(var + eps);
@@ -209,12 +211,70 @@ static int gn_splits(int n_img, int hw) {
     return s;
 }
 
+// Per-(image, group) sums from the split statistics: out[n][g] = sum over splits, in split order.
+__global__ void gn_reduce_splits_kernel(const float* __restrict__ partial, int splits, int groups, float* __restrict__ out) {
+    pdl_sync();
+    const int n = blockIdx.x;
+    for (int g = threadIdx.x; g < groups; g += blockDim.x) {
+        float a = 0.f, b = 0.f;
+        for (int s = 0; s < splits; ++s) {
+            const float2 in = *reinterpret_cast<const float2*>(partial + (((size_t)n * splits + s) * groups + g) * 2);
+            a += in.x, b += in.y;
+        }
+        out[((size_t)n * groups + g) * 2] = a, out[((size_t)n * groups + g) * 2 + 1] = b;
+    }
+}
+
+// Per-(image, group) sums from the column sums a producing GEMM's epilogue left behind (gemm.cu, staged_store):
+// t[n][part][c] = (sum, sum of squares) of column c over one 32-row slice of a tile.  One CTA per (group, image);
+// thread i adds the elements i, i + 128, ... of its group's [parts x channels-per-group] block in order, then the 128
+// per-thread sums are added by a fixed tree: the result does not depend on scheduling.
+__global__ void __launch_bounds__(128)
+    gn_tile_sums_kernel(const float2* __restrict__ t1, int parts1, int c1, const float2* __restrict__ t2, int parts2,
+                        int c2, int groups, float* __restrict__ out) {
+    pdl_sync();
+    __shared__ float sa[128], sb[128];
+    const int g = blockIdx.x, n = blockIdx.y;
+    const int cpg = (c1 + c2) / groups;
+    const int ch0 = g * cpg, ch1 = ch0 + cpg;
+    float a = 0.f, b = 0.f;
+    // channels [ch0, ch1) of the concatenation: [ch0, min(ch1, c1)) from the first producer, the rest from the second
+    const int e1 = min(ch1, c1);
+    if (ch0 < e1) {
+        const int w = e1 - ch0;
+        const float2* base = t1 + (size_t)n * parts1 * c1 + ch0;
+        for (int i = threadIdx.x; i < parts1 * w; i += 128) {
+            const int part = i / w, c = i - part * w;
+            const float2 v = base[(size_t)part * c1 + c];
+            a += v.x, b += v.y;
+        }
+    }
+    const int b2 = max(ch0, c1);
+    if (b2 < ch1) {
+        const int w = ch1 - b2;
+        const float2* base = t2 + (size_t)n * parts2 * c2 + (b2 - c1);
+        for (int i = threadIdx.x; i < parts2 * w; i += 128) {
+            const int part = i / w, c = i - part * w;
+            const float2 v = base[(size_t)part * c2 + c];
+            a += v.x, b += v.y;
+        }
+    }
+    sa[threadIdx.x] = a, sb[threadIdx.x] = b;
+    __syncthreads();
+    for (int o = 64; o > 0; o >>= 1) {
+        if (threadIdx.x < o) sa[threadIdx.x] += sa[threadIdx.x + o], sb[threadIdx.x] += sb[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[((size_t)n * groups + g) * 2] = sa[0], out[((size_t)n * groups + g) * 2 + 1] = sb[0];
+}
+
 // =============================================================================================== LayerNorm
 // one warp per row, whole row held in registers (cols <= 1536): exact two-pass mean / variance.
 template <int MAXV>
 __global__ void layernorm_kernel(const void* __restrict__ x, int dt, long long rows, int cols, float eps,
                                  const float* __restrict__ gamma, const float* __restrict__ beta,
                                  void* __restrict__ y, int out_f16) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= rows) return;
@@ -263,6 +323,7 @@ __global__ void layernorm_kernel(const void* __restrict__ x, int dt, long long r
 __global__ void embed_tokens_kernel(const int* __restrict__ ids, const float* __restrict__ tok,
                                     const float* __restrict__ pos, float* __restrict__ out, long long rows, int seq_len,
                                     int dim) {
+    pdl_sync();
     const int vpr = dim >> 2;
     const long long total = rows * vpr;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -280,6 +341,7 @@ __global__ void embed_tokens_kernel(const int* __restrict__ ids, const float* __
 __global__ void im2col3x3_kernel(const void* __restrict__ x, int dt, int n_img, int n_src, int in_h, int in_w,
                                  int cin, int stride, int out_h, int out_w, int k_pad, void* __restrict__ out,
                                  int out_f16) {
+    pdl_sync();
     const int kchunks = k_pad >> 3;
     const long long total = (long long)n_img * out_h * out_w * kchunks;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -322,6 +384,7 @@ __global__ void im2col3x3_kernel(const void* __restrict__ x, int dt, int n_img, 
 // =============================================================================================== upsample 2x
 __global__ void upsample2x_kernel(const void* __restrict__ x, int dt, int n_img, int h, int w, int c,
                                   void* __restrict__ out, int out_f16) {
+    pdl_sync();
     const int cv = c >> 3;
     const long long total = (long long)n_img * (2 * h) * (2 * w) * cv;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -342,6 +405,7 @@ __global__ void upsample2x_kernel(const void* __restrict__ x, int dt, int n_img,
 __global__ void cfg_sched_kernel(const void* __restrict__ eps2, int dt, float* __restrict__ x,
                                  float* __restrict__ x0_prev, const float* __restrict__ coef,
                                  const int* __restrict__ step_index, long long n) {
+    pdl_sync();
     const int step = step_index ? *step_index : 0;
     const float g = coef[step * 6 + 0], cx = coef[step * 6 + 1], cm = coef[step * 6 + 2], cp = coef[step * 6 + 3],
                 ax = coef[step * 6 + 4], am = coef[step * 6 + 5];
@@ -370,6 +434,7 @@ __global__ void cfg_sched_kernel(const void* __restrict__ eps2, int dt, float* _
 __global__ void small_linear_kernel(const float* __restrict__ x, int rows, int k, int n, int sinusoid_dim,
                                     int silu_in, int silu_out, const uint16_t* __restrict__ w, int w_f16,
                                     const float* __restrict__ b, float* __restrict__ y) {
+    pdl_sync();
     extern __shared__ float xs[];  // [8][k]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int col = blockIdx.x * (blockDim.x >> 5) + warp;
@@ -421,6 +486,7 @@ __global__ void small_linear_kernel(const float* __restrict__ x, int rows, int k
 // =============================================================================================== row softmax
 __global__ void softmax_rows_kernel(const void* __restrict__ x, int dt, long long ld_in, void* __restrict__ y,
                                     int out_f16, long long ld_out, int cols, float scale) {
+    pdl_sync();
     extern __shared__ float row[];
     __shared__ float red[32];
     const size_t in0 = (size_t)blockIdx.x * ld_in, out0 = (size_t)blockIdx.x * ld_out;
@@ -460,6 +526,7 @@ __global__ void softmax_rows_kernel(const void* __restrict__ x, int dt, long lon
 
 // =============================================================================================== K7 / cast
 __global__ void denorm_u8_kernel(const void* __restrict__ x, int dt, uint8_t* __restrict__ out, long long n) {
+    pdl_sync();
     const long long nv = n >> 2;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
          i += (long long)gridDim.x * blockDim.x) {
@@ -477,6 +544,7 @@ __global__ void denorm_u8_kernel(const void* __restrict__ x, int dt, uint8_t* __
 }
 
 __global__ void cast_kernel(const void* __restrict__ x, int dt_in, void* __restrict__ y, int dt_out, long long n) {
+    pdl_sync();
     const long long nv = n >> 2;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
          i += (long long)gridDim.x * blockDim.x) {
@@ -513,7 +581,7 @@ namespace b200sd {
 
 // argument checks shared by the two GroupNorm entry points
 static int32_t gn_check(const b200sd_groupnorm_params* p, const char* who) {
-    B200SD_CHECK_ARG(p && p->x1 && p->y && p->gamma && p->beta, "%s: null pointer", who);
+    B200SD_CHECK_ARG(p && p->x1 && (p->sums_out || (p->y && p->gamma && p->beta)), "%s: null pointer", who);
     const int c2 = p->x2 ? p->c2 : 0;
     const int C = p->c1 + c2;
     B200SD_CHECK_ARG(p->n_img > 0 && p->hw > 0, "%s: bad shape", who);
@@ -525,9 +593,11 @@ static int32_t gn_check(const b200sd_groupnorm_params* p, const char* who) {
     return B200SD_OK;
 }
 
-// the two launches of GroupNorm: split statistics into `scratch` (n_img * splits * groups * 2 floats), then
-// reduce + normalise.  Both kernels accept any split count >= 1.
-static int32_t gn_launch(const b200sd_groupnorm_params* p, int splits, float* scratch, cudaStream_t s, const char* who) {
+// The launches of GroupNorm: split statistics into `scratch` (n_img * splits * groups * 2 floats), then reduce +
+// normalise.  Both kernels accept any split count >= 1.  `stats` / `apply` select the halves: statistics only
+// (p->sums_out receives the per-(image, group) sums), apply only (p->sums given: they ARE the one split), or both.
+static int32_t gn_launch(const b200sd_groupnorm_params* p, int splits, float* scratch, cudaStream_t s, const char* who,
+                         bool stats = true, bool apply = true) {
     const int c2 = p->x2 ? p->c2 : 0;
     const int C = p->c1 + c2;
     const bool vec8 = p->c1 % 8 == 0 && c2 % 8 == 0;  // 8 channels per thread: 16-byte accesses on the 16-bit side
@@ -536,20 +606,39 @@ static int32_t gn_launch(const b200sd_groupnorm_params* p, int splits, float* sc
     if (lanes < 1) lanes = 1;
     const int threads = vpp * lanes;
     const size_t smem = (size_t)2 * lanes * C * sizeof(float);
-    const int chunks = splits * 2;
+    const int chunks = gn_splits(p->n_img, p->hw) * 2;
     dim3 g1(splits, p->n_img), g2(chunks, p->n_img);
-    if (vec8) {
-        gn_stats_kernel<8><<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch);
-        gn_apply_kernel<8><<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch,
-                                                  p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
-                                                  p->out_dtype == B200SD_F16, chunks);
-    } else {
-        gn_stats_kernel<4><<<g1, threads, smem, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch);
-        gn_apply_kernel<4><<<g2, threads, 0, s>>>(p->x1, p->c1, p->x2, c2, p->in_dtype, p->hw, p->groups, splits, scratch,
-                                                  p->eps, p->gamma, p->beta, p->silu, p->y, p->raw,
-                                                  p->out_dtype == B200SD_F16, chunks);
+    int launches = 0;
+    const int dt = p->in_dtype, f16 = p->out_dtype == B200SD_F16;
+    if (stats) {
+        if (vec8) {
+            B200SD_LAUNCH("gn_stats_kernel", (gn_stats_kernel<8>), g1, dim3(threads), smem, s, p->x1, p->c1, p->x2, c2, dt, p->hw,
+                          p->groups, splits, scratch);
+        } else {
+            B200SD_LAUNCH("gn_stats_kernel", (gn_stats_kernel<4>), g1, dim3(threads), smem, s, p->x1, p->c1, p->x2, c2, dt, p->hw,
+                          p->groups, splits, scratch);
+        }
+        ++launches;
     }
-    count_launch(2);
+    if (stats && !apply) {
+        B200SD_LAUNCH("gn_reduce_splits_kernel", gn_reduce_splits_kernel, dim3(p->n_img), dim3(64), 0, s, scratch, splits,
+                      p->groups, p->sums_out);
+        ++launches;
+    }
+    if (apply) {
+        const float* part = stats ? scratch : p->sums;
+        const int nsplit = stats ? splits : 1;
+        const float stat_hw = (float)((!stats && p->stat_hw > 0) ? p->stat_hw : (int64_t)p->hw);
+        if (vec8) {
+            B200SD_LAUNCH("gn_apply_kernel", (gn_apply_kernel<8>), g2, dim3(threads), 0, s, p->x1, p->c1, p->x2, c2, dt, p->hw,
+                          p->groups, nsplit, part, p->eps, p->gamma, p->beta, p->silu, p->y, p->raw, f16, chunks, stat_hw);
+        } else {
+            B200SD_LAUNCH("gn_apply_kernel", (gn_apply_kernel<4>), g2, dim3(threads), 0, s, p->x1, p->c1, p->x2, c2, dt, p->hw,
+                          p->groups, nsplit, part, p->eps, p->gamma, p->beta, p->silu, p->y, p->raw, f16, chunks, stat_hw);
+        }
+        ++launches;
+    }
+    count_launch(launches);
     B200SD_CHECK_LAUNCH(who);
     return B200SD_OK;
 }
@@ -559,13 +648,36 @@ static int32_t gn_launch(const b200sd_groupnorm_params* p, int splits, float* sc
 extern "C" int32_t b200sd_groupnorm(const b200sd_groupnorm_params* p, b200sd_stream_t stream) {
     const int32_t rc = gn_check(p, "groupnorm");
     if (rc != B200SD_OK) return rc;
+    B200SD_CHECK_ARG(!(p->sums && p->sums_out), "groupnorm: sums and sums_out are exclusive");
+    if (p->sums) {  // statistics supplied by the caller (a producer's epilogue, or an all-reduce over GPUs): apply only
+        B200SD_CHECK_ARG(p->stat_hw == 0 || p->stat_hw >= p->hw, "groupnorm: stat_hw %lld < hw %d", (long long)p->stat_hw, p->hw);
+        return gn_launch(p, 1, nullptr, as_stream(stream), "groupnorm (apply)", false, true);
+    }
     B200SD_CHECK_ARG(p->workspace, "groupnorm: null workspace");
     const int splits = gn_splits(p->n_img, p->hw);
     const int64_t need = (int64_t)p->n_img * splits * p->groups * 2 * sizeof(float);
     if (p->workspace_bytes < need)
         return set_error(B200SD_ERR_WORKSPACE, "groupnorm: workspace %lld < %lld bytes", (long long)p->workspace_bytes,
                          (long long)need);
+    if (p->sums_out) return gn_launch(p, splits, p->workspace, as_stream(stream), "groupnorm (statistics)", true, false);
     return gn_launch(p, splits, p->workspace, as_stream(stream), "groupnorm");
+}
+
+extern "C" int32_t b200sd_gn_tile_sums(const b200sd_gn_tile_sums_params* p, b200sd_stream_t stream) {
+    B200SD_CHECK_ARG(p && p->tile_sums1 && p->sums, "gn_tile_sums: null pointer");
+    const int c2 = p->tile_sums2 ? p->c2 : 0;
+    B200SD_CHECK_ARG(p->n_img > 0 && p->parts1 > 0 && p->c1 > 0 && (!p->tile_sums2 || (p->parts2 > 0 && p->c2 > 0)),
+                     "gn_tile_sums: bad shape");
+    B200SD_CHECK_ARG(p->groups > 0 && p->groups <= 64 && (p->c1 + c2) % p->groups == 0, "gn_tile_sums: C=%d groups=%d",
+                     p->c1 + c2, p->groups);
+    B200SD_CHECK_ARG((reinterpret_cast<uintptr_t>(p->tile_sums1) & 7) == 0 &&
+                         (reinterpret_cast<uintptr_t>(p->tile_sums2) & 7) == 0, "gn_tile_sums: tables must be 8-byte aligned");
+    B200SD_LAUNCH("gn_tile_sums_kernel", gn_tile_sums_kernel, dim3(p->groups, p->n_img), dim3(128), 0, as_stream(stream), 
+        reinterpret_cast<const float2*>(p->tile_sums1), p->parts1, p->c1, reinterpret_cast<const float2*>(p->tile_sums2),
+        p->parts2, c2, p->groups, p->sums);
+    count_launch();
+    B200SD_CHECK_LAUNCH("gn_tile_sums");
+    return B200SD_OK;
 }
 
 extern "C" int32_t b200sd_embed_tokens(const b200sd_embed_params* p, b200sd_stream_t stream) {
@@ -575,7 +687,7 @@ extern "C" int32_t b200sd_embed_tokens(const b200sd_embed_params* p, b200sd_stre
     B200SD_CHECK_ARG(ALIGNED16(p->token_table) && ALIGNED16(p->position_table) && ALIGNED16(p->out),
                      "embed_tokens: tables and output must be 16-byte aligned");
     if (p->rows == 0) return B200SD_OK;
-    embed_tokens_kernel<<<ew_grid(p->rows * (p->dim / 4), 256), 256, 0, as_stream(stream)>>>(
+    B200SD_LAUNCH("embed_tokens_kernel", embed_tokens_kernel, dim3(ew_grid(p->rows * (p->dim / 4), 256)), dim3(256), 0, as_stream(stream), 
         p->ids, p->token_table, p->position_table, p->out, p->rows, p->seq_len, p->dim);
     count_launch();
     B200SD_CHECK_LAUNCH("embed_tokens");
@@ -595,7 +707,7 @@ extern "C" int32_t b200sd_layernorm(const b200sd_layernorm_params* p, b200sd_str
     // registers per thread follow the row length (4 * MAXV floats), so short rows run at full occupancy
     const int nv = (p->cols / 4 + 31) / 32;
 #define B200SD_LN_LAUNCH(MV)                                                                                       \
-    layernorm_kernel<MV><<<grid, wpb * 32, 0, as_stream(stream)>>>(p->x, p->in_dtype, p->rows, p->cols, p->eps,   \
+    B200SD_LAUNCH("layernorm_kernel", (layernorm_kernel<MV>), dim3(grid), dim3(wpb * 32), 0, as_stream(stream), p->x, p->in_dtype, p->rows, p->cols, p->eps,   \
                                                                   p->gamma, p->beta, p->y, p->out_dtype == B200SD_F16)
     if (nv <= 3) B200SD_LN_LAUNCH(3);
     else if (nv <= 5) B200SD_LN_LAUNCH(5);
@@ -616,7 +728,7 @@ extern "C" int32_t b200sd_im2col3x3(const b200sd_im2col_params* p, b200sd_stream
     B200SD_CHECK_ARG(ALIGNED16(p->x) && ALIGNED16(p->out), "im2col: pointers must be 16-byte aligned");
     const int out_h = (p->in_h + 2 - 3) / p->stride + 1, out_w = (p->in_w + 2 - 3) / p->stride + 1;
     const long long total = (long long)p->n_img * out_h * out_w * (p->k_pad / 8);
-    im2col3x3_kernel<<<ew_grid(total, 256), 256, 0, as_stream(stream)>>>(
+    B200SD_LAUNCH("im2col3x3_kernel", im2col3x3_kernel, dim3(ew_grid(total, 256)), dim3(256), 0, as_stream(stream), 
         p->x, p->in_dtype, p->n_img, p->n_src, p->in_h, p->in_w, p->cin, p->stride, out_h, out_w, p->k_pad, p->out,
         p->out_dtype == B200SD_F16);
     count_launch();
@@ -630,7 +742,7 @@ extern "C" int32_t b200sd_upsample2x(const b200sd_upsample_params* p, b200sd_str
     B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype) && H_DTYPE(p->out_dtype), "upsample2x: bad in_dtype / out_dtype");
     B200SD_CHECK_ARG(ALIGNED16(p->x) && ALIGNED16(p->out), "upsample2x: pointers must be 16-byte aligned");
     const long long total = (long long)p->n_img * 4 * p->h * p->w * (p->c / 8);
-    upsample2x_kernel<<<ew_grid(total, 256), 256, 0, as_stream(stream)>>>(p->x, p->in_dtype, p->n_img, p->h, p->w,
+    B200SD_LAUNCH("upsample2x_kernel", upsample2x_kernel, dim3(ew_grid(total, 256)), dim3(256), 0, as_stream(stream), p->x, p->in_dtype, p->n_img, p->h, p->w,
                                                                          p->c, p->out, p->out_dtype == B200SD_F16);
     count_launch();
     B200SD_CHECK_LAUNCH("upsample2x");
@@ -644,7 +756,7 @@ extern "C" int32_t b200sd_cfg_sched_step(const b200sd_cfg_sched_params* p, b200s
     B200SD_CHECK_ARG(ALIGNED16(p->eps2) && ALIGNED16(p->x) && (!p->x0_prev || ALIGNED16(p->x0_prev)) &&
                          (p->eps_dtype == B200SD_F32 || (p->n % 8 == 0)),
                      "cfg_sched_step: pointers must be 16-byte aligned (16-bit eps: n %% 8 == 0)");
-    cfg_sched_kernel<<<ew_grid(p->n / 4, 256), 256, 0, as_stream(stream)>>>(p->eps2, p->eps_dtype, p->x, p->x0_prev,
+    B200SD_LAUNCH("cfg_sched_kernel", cfg_sched_kernel, dim3(ew_grid(p->n / 4, 256)), dim3(256), 0, as_stream(stream), p->eps2, p->eps_dtype, p->x, p->x0_prev,
                                                                            p->coef, p->step_index, p->n);
     count_launch();
     B200SD_CHECK_LAUNCH("cfg_sched_step");
@@ -667,7 +779,7 @@ extern "C" int32_t b200sd_small_linear(const b200sd_small_linear_params* p, b200
         cudaFuncSetAttribute(small_linear_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4096 * 4);
         attr_set[dev] = true;
     }
-    small_linear_kernel<<<grid, wpb * 32, smem, as_stream(stream)>>>(
+    B200SD_LAUNCH("small_linear_kernel", small_linear_kernel, dim3(grid), dim3(wpb * 32), smem, as_stream(stream), 
         p->x, p->rows, p->k, p->n, p->sinusoid_dim, p->silu_in, p->silu_out, (const uint16_t*)p->w,
         p->w_dtype == B200SD_F16, p->b, p->y);
     count_launch();
@@ -691,7 +803,7 @@ extern "C" int32_t b200sd_softmax_rows(const b200sd_softmax_params* p, b200sd_st
         cudaFuncSetAttribute(softmax_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 49152 * 4);
         attr_set[dev] = true;
     }
-    softmax_rows_kernel<<<(unsigned)p->rows, 256, smem, as_stream(stream)>>>(
+    B200SD_LAUNCH("softmax_rows_kernel", softmax_rows_kernel, dim3((unsigned)p->rows), dim3(256), smem, as_stream(stream), 
         p->x, p->in_dtype, p->ld_in, p->y, p->out_dtype == B200SD_F16, p->ld_out, p->cols, p->scale);
     count_launch();
     B200SD_CHECK_LAUNCH("softmax_rows");
@@ -703,7 +815,7 @@ extern "C" int32_t b200sd_denorm_u8(const b200sd_denorm_u8_params* p, b200sd_str
     B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype), "denorm_u8: bad in_dtype");
     B200SD_CHECK_ARG(p->n > 0 && p->n % 4 == 0 && ALIGNED16(p->x) && (reinterpret_cast<uintptr_t>(p->out) & 3) == 0,
                      "denorm_u8: n %% 4 == 0 and aligned pointers required");
-    denorm_u8_kernel<<<ew_grid(p->n / 4, 256), 256, 0, as_stream(stream)>>>(p->x, p->in_dtype, p->out, p->n);
+    B200SD_LAUNCH("denorm_u8_kernel", denorm_u8_kernel, dim3(ew_grid(p->n / 4, 256)), dim3(256), 0, as_stream(stream), p->x, p->in_dtype, p->out, p->n);
     count_launch();
     B200SD_CHECK_LAUNCH("denorm_u8");
     return B200SD_OK;
@@ -713,7 +825,7 @@ extern "C" int32_t b200sd_cast(const b200sd_cast_params* p, b200sd_stream_t stre
     B200SD_CHECK_ARG(p && p->x && p->y, "cast: null pointer");
     B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype) && ANY_DTYPE(p->out_dtype), "cast: bad dtype");
     B200SD_CHECK_ARG(p->n > 0 && p->n % 4 == 0 && ALIGNED16(p->x) && ALIGNED16(p->y), "cast: n %% 4 == 0, aligned");
-    cast_kernel<<<ew_grid(p->n / 4, 256), 256, 0, as_stream(stream)>>>(p->x, p->in_dtype, p->y, p->out_dtype, p->n);
+    B200SD_LAUNCH("cast_kernel", cast_kernel, dim3(ew_grid(p->n / 4, 256)), dim3(256), 0, as_stream(stream), p->x, p->in_dtype, p->y, p->out_dtype, p->n);
     count_launch();
     B200SD_CHECK_LAUNCH("cast");
     return B200SD_OK;
@@ -770,6 +882,8 @@ static int32_t gn_static_scratch_address(float** out) {
 extern "C" int32_t b200sd_groupnorm_static_scratch(const b200sd_groupnorm_params* p, b200sd_stream_t stream) {
     int32_t rc = gn_check(p, "groupnorm_static_scratch");
     if (rc != B200SD_OK) return rc;
+    B200SD_CHECK_ARG(!p->sums && !p->sums_out && p->y, "groupnorm_static_scratch: the split-phase fields (sums, sums_out) "
+                     "belong to b200sd_groupnorm; this entry point always runs the whole GroupNorm");
     int splits = gn_splits(p->n_img, p->hw);
     const long long per_split = (long long)p->n_img * p->groups * 2;
     if (per_split > GN_STATIC_SCRATCH_FLOATS)

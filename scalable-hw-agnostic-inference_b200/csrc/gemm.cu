@@ -60,6 +60,8 @@ struct GemmKernelParams {
     int tma_reduce;  // 1: (with tma_epi) out IS the fp32 residual: the chunk is added to it by a TMA reduce, no residual read
     int tma_epi;   // 1: (linear layout, no residual) the staging tile is written in the output dtype, row per thread, and
                    //    leaves with one TMA store per 32x32 chunk: no shared-memory read-back on the epilogue's chain
+    float2* tile_sums;  // (staged epilogue only) [m_tile * 4 + lane quadrant][n_out] (sum, sum of squares) of the stored
+                        // values over the quadrant's valid rows: the next GroupNorm's statistics, or nullptr
 };
 
 // PAIR: two CTAs (one cluster) share a 256-row tile through tcgen05.mma.cta_group::2; each CTA stages its own 128 rows
@@ -252,13 +254,17 @@ __device__ __forceinline__ void res_request(const GemmKernelParams& p, const int
 }
 // Reads the staged chunk back transposed, adds the column bias (`bs` = this chunk's 32 bias values in shared memory,
 // or nullptr) and the requested residual (`use_res`), converts and stores full row segments.
+// `sums` (or nullptr) = where this warp's column sums of the chunk go: after the stores, the per-lane partial sums over
+// the rows a lane handled are combined across the lanes that share its columns (xor butterfly: every lane adds the
+// same values in the same order, so the result does not depend on timing) and one lane per column group writes them.
 __device__ __forceinline__ void staged_store(const GemmKernelParams& p, const float* stg, const int (&mt)[8],
                                              uint32_t vmask, int lane, int col0, const float* bs, bool use_res,
-                                             const uint4 (&buf)[8]) {
+                                             const uint4 (&buf)[8], float2* sums) {
     if (p.out_dtype == B200SD_F32) {
         const int cg = lane & 7;
         float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
         if (bs) b = *reinterpret_cast<const float4*>(bs + 4 * cg);
+        float4 cs = make_float4(0.f, 0.f, 0.f, 0.f), cq = cs;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const int row = 4 * i + (lane >> 3);
@@ -269,8 +275,28 @@ __device__ __forceinline__ void staged_store(const GemmKernelParams& p, const fl
                 a.x += __uint_as_float(buf[i].x), a.y += __uint_as_float(buf[i].y);
                 a.z += __uint_as_float(buf[i].z), a.w += __uint_as_float(buf[i].w);
             }
-            if ((vmask >> row) & 1)
+            if ((vmask >> row) & 1) {
                 *reinterpret_cast<float4*>(static_cast<float*>(p.out) + (long long)mt[i] * p.ld_out + col0 + 4 * cg) = a;
+                if (sums) {
+                    cs.x += a.x, cs.y += a.y, cs.z += a.z, cs.w += a.w;
+                    cq.x = fmaf(a.x, a.x, cq.x), cq.y = fmaf(a.y, a.y, cq.y);
+                    cq.z = fmaf(a.z, a.z, cq.z), cq.w = fmaf(a.w, a.w, cq.w);
+                }
+            }
+        }
+        if (sums) {
+#pragma unroll
+            for (int o = 8; o <= 16; o <<= 1) {
+                cs.x += __shfl_xor_sync(0xffffffffu, cs.x, o), cs.y += __shfl_xor_sync(0xffffffffu, cs.y, o);
+                cs.z += __shfl_xor_sync(0xffffffffu, cs.z, o), cs.w += __shfl_xor_sync(0xffffffffu, cs.w, o);
+                cq.x += __shfl_xor_sync(0xffffffffu, cq.x, o), cq.y += __shfl_xor_sync(0xffffffffu, cq.y, o);
+                cq.z += __shfl_xor_sync(0xffffffffu, cq.z, o), cq.w += __shfl_xor_sync(0xffffffffu, cq.w, o);
+            }
+            if (lane < 8) {
+                float4* d = reinterpret_cast<float4*>(sums + col0 + 4 * cg);
+                d[0] = make_float4(cs.x, cq.x, cs.y, cq.y);
+                d[1] = make_float4(cs.z, cq.z, cs.w, cq.w);
+            }
         }
     } else {
         const bool f16 = p.out_dtype == B200SD_F16;
@@ -280,6 +306,9 @@ __device__ __forceinline__ void staged_store(const GemmKernelParams& p, const fl
             b0 = *reinterpret_cast<const float4*>(bs + 8 * cg);
             b1 = *reinterpret_cast<const float4*>(bs + 8 * cg + 4);
         }
+        float cs[8], cq[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) cs[j] = 0.f, cq[j] = 0.f;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int row = 8 * i + (lane >> 2);
@@ -301,10 +330,30 @@ __device__ __forceinline__ void staged_store(const GemmKernelParams& p, const fl
                 a1.x += h_lo(buf[i].z, f16), a1.y += h_hi(buf[i].z, f16);
                 a1.z += h_lo(buf[i].w, f16), a1.w += h_hi(buf[i].w, f16);
             }
-            if ((vmask >> row) & 1)
+            if ((vmask >> row) & 1) {
                 *reinterpret_cast<uint4*>(static_cast<uint16_t*>(p.out) + (long long)mt[i] * p.ld_out + col0 + 8 * cg) =
                     make_uint4(pack_h2(a0.x, a0.y, f16), pack_h2(a0.z, a0.w, f16), pack_h2(a1.x, a1.y, f16),
                                pack_h2(a1.z, a1.w, f16));
+                if (sums) {
+                    const float v[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) cs[j] += v[j], cq[j] = fmaf(v[j], v[j], cq[j]);
+                }
+            }
+        }
+        if (sums) {
+#pragma unroll
+            for (int o = 4; o <= 16; o <<= 1)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], o);
+                    cq[j] += __shfl_xor_sync(0xffffffffu, cq[j], o);
+                }
+            if (lane < 4) {
+                float4* d = reinterpret_cast<float4*>(sums + col0 + 8 * cg);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) d[j] = make_float4(cs[2 * j], cq[2 * j], cs[2 * j + 1], cq[2 * j + 1]);
+            }
         }
     }
 }
@@ -388,6 +437,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_base_slot;
+    pdl_sync();  // everything above overlapped the previous kernel's tail; global memory is touched from here on
 
     const int splits = p.splits;
     const int num_kb = p.taps * p.kb_per_tap;
@@ -589,6 +639,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
             const int colbase = n_tile * BLOCK_N;
             const int row0 = m_tile * BLOCK_M + quad * 32;  // first output row of this warp (linear layout only)
             const bool use_res = fast && !tma && p.residual != nullptr;  // (a TMA reduce needs no residual read)
+            // this warp's row of the column-sum table: slice (m_tile, lane quadrant); a pair's odd CTA may hold a tile
+            // past the end of the problem
+            float2* sums_row = (p.tile_sums != nullptr && m_tile < p.m_tiles)
+                                   ? p.tile_sums + (size_t)(m_tile * 4 + quad) * p.n_out : nullptr;
             uint4 rbuf[8];
             if (use_res && splits == 1 && colbase + eg * 32 + 32 <= p.n_cols)
                 res_request(p, mt, vmask, lane, colbase + eg * 32, rbuf);
@@ -735,7 +789,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                         }
                         __syncwarp();
                         if (full) {
-                            staged_store(p, stg, mt, vmask, lane, col0, bs + c * 32, use_res, rbuf);
+                            staged_store(p, stg, mt, vmask, lane, col0, bs + c * 32, use_res, rbuf, sums_row);
                             if (more && use_res && col0 + 96 <= p.n_cols)
                                 res_request(p, mt, vmask, lane, col0 + 64, rbuf);
                             __syncwarp();
@@ -789,7 +843,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                         } else if (fast) {
                             stage_rows(stg, lane, v);
                             __syncwarp();
-                            staged_store(p, stg, mt, vmask, lane, col0, nullptr, false, rbuf);
+                            staged_store(p, stg, mt, vmask, lane, col0, nullptr, false, rbuf, nullptr);
                             __syncwarp();
                         } else if (valid) {
                             epilogue_store32(p, v, m, img, col0);
@@ -916,7 +970,8 @@ static int32_t launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const
     }
     long long total = (long long)kp.m_tiles * kp.n_tiles * kp.splits;
     int grid = (int)(total < num_sms() ? total : num_sms());
-    gemm_kernel<BLOCK_N, false><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmOut, kp);
+    B200SD_LAUNCH("gemm_kernel", (gemm_kernel<BLOCK_N, false>), dim3(grid), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, tmA, tmB,
+                  tmOut, kp);
     count_launch();
     B200SD_CHECK_LAUNCH("gemm_kernel");
     return B200SD_OK;
@@ -939,16 +994,8 @@ static int32_t launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, 
     const long long pairs = (long long)((kp.m_tiles + 1) / 2) * kp.n_tiles;
     const int max_clusters = num_sms() / 2;
     const int clusters = (int)(pairs < max_clusters ? pairs : max_clusters);
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(2 * clusters, 1, 1);
-    cfg.blockDim = dim3(GEMM_THREADS, 1, 1);
-    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2, attr[0].val.clusterDim.y = 1, attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr, cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_kernel<BLOCK_N, true>, tmA, tmB, tmOut, kp);
+    cudaError_t e = launch_kernel(gemm_kernel<BLOCK_N, true>, dim3(2 * clusters), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, 2,
+                                  tmA, tmB, tmOut, kp);
     if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "gemm (pair) launch: %s", cudaGetErrorString(e));
     count_launch();
     B200SD_CHECK_LAUNCH("gemm_kernel<pair>");
@@ -961,6 +1008,26 @@ struct GemmPlan {
     int block_n;
     int64_t ws_bytes;
 };
+
+static int32_t make_plan(const b200sd_gemm_params* p, bool have_ws, GemmPlan* plan);
+
+// Slices per image of the column-sum table (4 per 128-row tile), or 0 when this problem's epilogue cannot produce it.
+// Needs the staged epilogue on every chunk (plain column bias, n_out % 32 == 0, no GEGLU, no split K) and tiles that
+// stay inside one image (NHWC: pixel boxes of one image; [M, K]: rows_per_image % 128 == 0).
+static int tile_sum_parts(const b200sd_gemm_params* p, const GemmPlan& plan) {
+    const GemmKernelParams& kp = plan.kp;
+    if (p->geglu || kp.splits != 1 || p->bias_along_m || p->n_out % 32 != 0 || p->n_out < 32) return 0;
+    if (p->row_bias && kp.bn != 1) return 0;
+    const bool res_ok = !p->residual || p->residual_dtype == p->out_dtype ||
+                        (p->residual_dtype == B200SD_F32 && p->out_dtype != B200SD_F32);
+    if (!res_ok) return 0;
+    if (p->img_h == 1 && p->n_img == 1) {
+        if (p->rows_per_image <= 0 || p->rows_per_image % BLOCK_M != 0 || p->img_w % p->rows_per_image != 0) return 0;
+        return (p->rows_per_image / BLOCK_M) * 4;
+    }
+    if (kp.bn != 1 || p->rows_per_image != 0) return 0;
+    return kp.tiles_x * kp.tiles_y * 4;
+}
 
 static int32_t make_plan(const b200sd_gemm_params* p, bool have_ws, GemmPlan* plan) {
     B200SD_CHECK_ARG(p->taps == 1 || p->taps == 9, "gemm: taps must be 1 or 9 (got %d)", p->taps);
@@ -1025,6 +1092,16 @@ extern "C" int32_t b200sd_gemm_pick_block_n(int32_t n_out, int32_t geglu) {
     return pick_block_n_auto(n_out, geglu, 1 << 20);
 }
 
+extern "C" int32_t b200sd_gemm_tile_sum_parts(const b200sd_gemm_params* p) {
+    if (!p) return 0;
+    GemmPlan plan;
+    // planned as b200sd_gemm will plan it when it is handed tile_sums: never split along K
+    b200sd_gemm_params q = *p;
+    q.split_k = 1;
+    if (make_plan(&q, false, &plan) != B200SD_OK) return 0;
+    return tile_sum_parts(&q, plan);
+}
+
 extern "C" int64_t b200sd_gemm_workspace_bytes(const b200sd_gemm_params* p) {
     if (!p) return 0;
     GemmPlan plan;
@@ -1067,8 +1144,15 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
     B200SD_CHECK_ARG(!have_ws || (reinterpret_cast<uintptr_t>(p->workspace) & 255) == 0,
                      "gemm: workspace must be 256-byte aligned");
     GemmPlan plan;
-    int32_t rc = make_plan(p, have_ws, &plan);
+    int32_t rc = make_plan(p, have_ws && !p->tile_sums, &plan);  // column sums come from whole-K accumulators
     if (rc) return rc;
+    if (p->tile_sums) {
+        B200SD_CHECK_ARG(p->split_k <= 1, "gemm: tile_sums cannot be combined with split_k");
+        B200SD_CHECK_ARG((reinterpret_cast<uintptr_t>(p->tile_sums) & 15) == 0, "gemm: tile_sums must be 16-byte aligned");
+        if (tile_sum_parts(p, plan) == 0)
+            return set_error(B200SD_ERR_UNSUPPORTED, "gemm: this problem cannot emit tile_sums (ask "
+                             "b200sd_gemm_tile_sum_parts first): tiles span images, or the epilogue is not the staged one");
+    }
     if (plan.kp.splits > 1 && plan.ws_bytes > p->workspace_bytes) {
         if (p->split_k > 1)
             return set_error(B200SD_ERR_WORKSPACE, "gemm: split_k=%d needs %lld workspace bytes, have %lld", p->split_k,
@@ -1098,8 +1182,10 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
         static const bool red_off = getenv("B200SD_GEMM_NO_TMA_REDUCE") != nullptr;
         const bool inplace32 = p->residual == p->out && p->ld_res == p->ld_out && p->out_dtype == B200SD_F32 &&
                                p->residual_dtype == B200SD_F32 && !p->act && !red_off;
+        // (column sums are taken in the staged epilogue's transposed read-back, so they rule the TMA store out)
         kp.tma_epi = (kp.fast_epi && !tma_off && (!p->residual || inplace32) && kp.splits == 1 && p->taps == 1 &&
-                      p->img_h == 1 && p->n_img == 1 && (p->ld_out * osz) % 16 == 0) ? 1 : 0;
+                      p->img_h == 1 && p->n_img == 1 && (p->ld_out * osz) % 16 == 0 && !p->tile_sums) ? 1 : 0;
+        kp.tile_sums = reinterpret_cast<float2*>(p->tile_sums);
         kp.tma_reduce = (kp.tma_epi && p->residual) ? 1 : 0;
     }
     if (kp.splits > 1) {

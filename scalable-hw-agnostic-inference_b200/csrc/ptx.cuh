@@ -309,6 +309,21 @@ __device__ __forceinline__ void tmem_st_x16(uint32_t taddr, const uint32_t (&r)[
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// A kernel launched with the programmatic-stream-serialization attribute may start while its predecessor in the stream
+// still runs: its prologue (barrier init, TMEM allocation, descriptor prefetch) then overlaps the predecessor's tail.
+// pdl_wait() returns once every predecessor grid has COMPLETED and its writes are visible -- every thread calls it before
+// its first global-memory access (reads of what predecessors wrote, and writes to what they may still read).
+// pdl_launch_dependents() lets the successor's CTAs be scheduled once all CTAs of this grid have issued it; it is issued
+// right after the wait, so at most one successor is ever parked behind a running kernel.  Both are no-ops in a
+// kernel launched without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() {
+    pdl_wait();
+    pdl_launch_dependents();
+}
+
 // ---------------------------------------------------------------- small helpers
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);

@@ -486,3 +486,120 @@ def test_attention_writes_only_its_output(K, cuda, batch, heads, sq, skv):
     ref = (torch.softmax(qf @ kf.transpose(-1, -2) * 0.125, -1) @ vf).transpose(1, 2).reshape(batch * sq, c)
     assert _guards_intact(buf, batch * sq, c)
     assert rel(out, ref) < 2 * out_tol(dt)
+
+
+# ------------------------------------------------------------------------------------------------ GroupNorm statistics from the producer
+def _sums_from_table(ts, groups):
+    """[n, parts, C, 2] column sums -> per-(image, group) (sum, sum of squares), in float64"""
+    n, parts, c, _ = ts.shape
+    return ts.double().sum(1).view(n, groups, c // groups, 2).sum(2)
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,mode", [(3, 24, 24, 64, 128, "rowbias16"), (2, 48, 48, 64, 320, "residual32"),
+                                                 (2, 20, 36, 72, 96, "plain32"), (4, 96, 96, 64, 64, "rowbias16"),
+                                                 (32, 48, 48, 128, 640, "residual32")])
+def test_conv_epilogue_column_sums(K, cuda, n, h, w, cin, cout, mode):
+    """the conv epilogue's by-product for the next GroupNorm: per 32-row slice of every tile, per output column, the sum and
+    the sum of squares of what it stores -- checked against sums over the stored tensor, and the output itself must be
+    the same bits as without the by-product"""
+    from b200sd.layers import pack_conv3x3, tile_sums_of
+    dt = K.op_dtype
+    x = rnd(n, h, w, cin, dev=cuda, seed=1, dtype=dt)
+    wp = pack_conv3x3(rnd(cout, cin, 3, 3, dev=cuda, seed=2, scale=(9 * cin) ** -0.5), dt)
+    kw = {}
+    if mode == "rowbias16":
+        kw = dict(row_bias=rnd(n, cout, dev=cuda, seed=3), out_dtype=dt)
+        bias = None
+    elif mode == "residual32":
+        kw = dict(residual=rnd(n, h, w, cout, dev=cuda, seed=4))
+        bias = rnd(cout, dev=cuda, seed=3)
+    else:
+        kw = dict(out_dtype=torch.float32)
+        bias = rnd(cout, dev=cuda, seed=3)
+    out = K.conv3x3(x, wp, bias, gn_next=True, **kw)
+    ts = tile_sums_of(out)
+    assert ts is not None and ts.shape[0] == n and ts.shape[2:] == (cout, 2)
+    plain = K.conv3x3(x, wp, bias, **kw)
+    assert torch.equal(out, plain)
+    got = _sums_from_table(ts, 32)
+    o = out.double().view(n, h * w, 32, cout // 32)
+    ref = torch.stack([o.sum((1, 3)), (o * o).sum((1, 3))], -1)
+    # the table sums the fp32 values before their rounding to the output dtype
+    assert rel(got, ref) < (1e-5 if out.dtype == torch.float32 else out_tol(dt))
+
+
+@pytest.mark.parametrize("hw,c,inplace", [(2304, 320, True), (9216, 64, False), (256, 128, True)])
+def test_linear_epilogue_column_sums(K, cuda, hw, c, inplace):
+    """[M, K] problems (proj_out onto the trunk, the im2col'd convs): rows_per_image tells the epilogue where images end"""
+    from b200sd.layers import tile_sums_of
+    dt = K.op_dtype
+    n = 3
+    a = rnd(n * hw, c, dev=cuda, seed=1, dtype=dt)
+    w, bias = rnd(c, c, dev=cuda, seed=2, scale=c ** -0.5, dtype=dt), rnd(c, dev=cuda, seed=3)
+    res = rnd(n * hw, c, dev=cuda, seed=4)
+    if inplace:
+        t = res.clone()
+        out = K.linear(a, w, bias, residual=t, out=t, gn_rows_per_image=hw)
+        t2 = res.clone()
+        K.linear(a, w, bias, residual=t2, out=t2)  # the TMA-reduce path
+        assert torch.equal(out, t2)
+    else:
+        out = K.linear(a, w, bias, gn_rows_per_image=hw)
+    ts = tile_sums_of(out)
+    assert ts is not None and ts.shape == (n, hw // 128 * 4, c, 2)
+    o = out.double().view(n, hw, 32, c // 32)
+    ref = torch.stack([o.sum((1, 3)), (o * o).sum((1, 3))], -1)
+    assert rel(_sums_from_table(ts, 32), ref) < 1e-5
+    assert tile_sums_of(K.linear(a, w, bias, gn_rows_per_image=hw - 64)) is None  # tiles would span images: not offered
+
+
+@pytest.mark.parametrize("c1,c2,h", [(320, 0, 48), (640, 320, 24), (128, 64, 96)])
+def test_groupnorm_from_producer_column_sums(K, cuda, c1, c2, h):
+    """GroupNorm whose statistics come from the producers' epilogues (two producers for the up blocks' channel concat, the
+    groups straddling the seam) against torch's GroupNorm on the same tensors, and against the two-pass kernel"""
+    from b200sd.layers import pack_conv3x3, tile_sums_of
+    dt = K.op_dtype
+    n = 2
+    mk = lambda c, seed: K.conv3x3(rnd(n, h, h, 64, dev=cuda, seed=seed, dtype=dt),
+                                   pack_conv3x3(rnd(c, 64, 3, 3, dev=cuda, seed=seed + 1, scale=1 / 24), dt),
+                                   rnd(c, dev=cuda, seed=seed + 2) * 0.5, gn_next=True)
+    x1 = mk(c1, 10)
+    x2 = mk(c2, 20) if c2 else None
+    assert tile_sums_of(x1) is not None and (x2 is None or tile_sums_of(x2) is not None)
+    c = c1 + c2
+    gamma, beta = rnd(c, dev=cuda, seed=3) * 0.1 + 1, rnd(c, dev=cuda, seed=4) * 0.1
+    y, raw = K.groupnorm(x1, x2, gamma, beta, 1e-5, True, want_raw=True)
+    cat = torch.cat([x1, x2], -1) if c2 else x1
+    ref = F.silu(F.group_norm(cat.float().permute(0, 3, 1, 2), 32, gamma, beta, 1e-5)).permute(0, 2, 3, 1)
+    assert rel(y, ref) < out_tol(dt) and torch.equal(raw, cat.to(dt))
+    K.fuse_gn_stats = False
+    try:
+        y2 = K.groupnorm(x1, x2, gamma, beta, 1e-5, True)
+    finally:
+        K.fuse_gn_stats = True
+    assert rel(y, y2) < out_tol(dt)
+
+
+def test_groupnorm_split_phases(K, cuda):
+    """statistics-only and apply-only calls (the two halves a multi-GPU row split all-reduces between): together they equal
+    the one-call GroupNorm; with the image cut in two row bands and the sums added, they equal GroupNorm of the whole"""
+    from b200sd import ops
+    dt = K.op_dtype
+    n, h, w, c = 2, 32, 48, 320
+    x = rnd(n, h, w, c, dev=cuda, seed=1) * 1.5 + 0.3
+    gamma, beta = rnd(c, dev=cuda, seed=3) * 0.1 + 1, rnd(c, dev=cuda, seed=4) * 0.1
+    ref = K.groupnorm(x, None, gamma, beta, 1e-5, True)
+    sums = torch.empty(n, 32, 2, device=cuda)
+    ops.groupnorm(x, None, n, h * w, 32, 1e-5, None, None, False, None, None, K.gn_workspace(n, h * w, 32), None, 0, sums)
+    y = torch.empty_like(ref)
+    ops.groupnorm(x, None, n, h * w, 32, 1e-5, gamma, beta, True, y, None, None, sums, 0, None)
+    assert rel(y, ref) < 0.25 * out_tol(dt)  # same sums up to their summation order (a few flipped 16-bit roundings)
+    top, bot = x[:, :20].contiguous(), x[:, 20:].contiguous()
+    s1, s2 = torch.empty_like(sums), torch.empty_like(sums)
+    ops.groupnorm(top, None, n, 20 * w, 32, 1e-5, None, None, False, None, None, K.gn_workspace(n, 20 * w, 32), None, 0, s1)
+    ops.groupnorm(bot, None, n, 12 * w, 32, 1e-5, None, None, False, None, None, K.gn_workspace(n, 12 * w, 32), None, 0, s2)
+    tot = s1 + s2
+    yt, yb = torch.empty(n, 20, w, c, device=cuda, dtype=dt), torch.empty(n, 12, w, c, device=cuda, dtype=dt)
+    ops.groupnorm(top, None, n, 20 * w, 32, 1e-5, gamma, beta, True, yt, None, None, tot, h * w, None)
+    ops.groupnorm(bot, None, n, 12 * w, 32, 1e-5, gamma, beta, True, yb, None, None, tot, h * w, None)
+    assert rel(torch.cat([yt, yb], 1), ref) < out_tol(dt)

@@ -24,14 +24,15 @@ def test_library_exports_every_declared_symbol(lib_built):
     lib = ctypes.CDLL(str(lib_built))
     for name in declared:
         assert hasattr(lib, name), name
-    assert _lib.load().b200sd_abi_version() == _lib.ABI_VERSION == 4
+    assert _lib.load().b200sd_abi_version() == _lib.ABI_VERSION == 5
 
 
 def test_ctypes_struct_layout_matches_c(lib_built, tmp_path):
     """sizeof / offsetof from gcc on include/b200sd.h == the ctypes mirror in b200sd/_lib.py"""
     from b200sd import _lib
     pairs = {"b200sd_gemm_params": _lib.GemmParams, "b200sd_attention_params": _lib.AttentionParams,
-             "b200sd_groupnorm_params": _lib.GroupNormParams, "b200sd_layernorm_params": _lib.LayerNormParams,
+             "b200sd_groupnorm_params": _lib.GroupNormParams, "b200sd_gn_tile_sums_params": _lib.GnTileSumsParams,
+             "b200sd_layernorm_params": _lib.LayerNormParams,
              "b200sd_im2col_params": _lib.Im2colParams, "b200sd_upsample_params": _lib.UpsampleParams,
              "b200sd_cfg_sched_params": _lib.CfgSchedParams, "b200sd_small_linear_params": _lib.SmallLinearParams,
              "b200sd_softmax_params": _lib.SoftmaxParams, "b200sd_denorm_u8_params": _lib.DenormU8Params,
