@@ -52,6 +52,9 @@ def parse():
                     help="skip the same-box stock-torch bf16 comparator (tests/torch_gpu_baseline.py) and the bf16-operand sub-line")
     ap.add_argument("--comparator-compile", default="auto", choices=["auto", "on", "off"],
                     help="torch.compile arm of the comparator (the reference's DEVICE=triton); auto = on, under a wall-clock limit")
+    ap.add_argument("--patch-parallel", action="store_true",
+                    help="BASELINE configs[4]: ONE request split over the ranks by latent rows (NCCL K/V all-gather, halo "
+                         "rows, GroupNorm all-reduce); use with --size 1024 --batch 1 under torchrun.  Not the default metric.")
     ap.add_argument("--profile-only", action="store_true", help="one eager profiled pass, no timing (for ncu runs)")
     ap.add_argument("--shape-profile", action="store_true", help="per-(kernel, shape) CUDA-event times of one eager pass")
     return ap.parse_args()
@@ -504,6 +507,110 @@ def classes_share_vae(prof, pipe) -> float:
     return t_vae / (t_vae + t_den)
 
 
+# ---------------------------------------------------------------------------------------------------- patch-parallel arm
+def run_patch_parallel(args):
+    """BASELINE configs[4]: one request (batch `--batch`, default use 1) denoised by all ranks together, each on its band of
+    latent rows (b200sd/patch.py).  A step of this arm = one whole image: `denoise_steps` UNet band steps + CFG/scheduler
+    on the band, the all-gather of the final latent bands, and the VAE decode (on every rank, not split).  Strong scaling:
+    the total work is fixed as N grows.  Rank 0 also runs the same request on its GPU alone and reports the PSNR between the
+    two uint8 images."""
+    import math
+
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world == 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29531")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    import b200sd
+    from b200sd import ops
+    from b200sd._randinit import random_state_dicts
+    from b200sd.patch import BandComm, PatchParallelPipeline
+
+    hw, B = args.size // 8, args.batch
+    ucfg = b200sd.UNetConfig(sample_size=hw, prediction_type="v_prediction")
+    vcfg = b200sd.VAEConfig()
+    usd, vsd = random_state_dicts(ucfg, vcfg, 0)
+    unet, vae = b200sd.B200UNet(usd, ucfg, dev), b200sd.B200VAEDecoder(vsd, vcfg, dev)
+    del usd, vsd
+    comm = BandComm()
+    pipe = PatchParallelPipeline(unet, vae, b200sd.B200Scheduler(args.scheduler, ucfg.prediction_type, dev), comm)
+    g = torch.Generator("cpu").manual_seed(1234)          # the same request on every rank
+    lat = torch.randn(B, 4, hw, hw, generator=g)
+    cond = torch.randn(B, 77, 1024, generator=g)
+    unc = torch.randn(1, 77, 1024, generator=torch.Generator("cpu").manual_seed(7)).expand(B, -1, -1).contiguous()
+
+    def one(time_steps=False):
+        return pipe(prompt_embeds=cond, negative_prompt_embeds=unc, latents=lat, num_inference_steps=args.denoise_steps,
+                    time_steps=time_steps).images
+
+    for _ in range(max(args.warmup, 1)):
+        one()
+    torch.cuda.synchronize()
+    n0, comm.bytes_gathered, comm.bytes_halo, comm.n_allreduce = ops.launch_count(), 0, 0, 0
+    one()
+    torch.cuda.synchronize()
+    launches = ops.launch_count() - n0
+    gathered, halo, n_ar = comm.bytes_gathered, comm.bytes_halo, comm.n_allreduce
+    clocks = ClockSampler(local)
+    dist.barrier()
+    torch.cuda.synchronize()
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        img = one()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop()
+    dist.barrier()
+    one(time_steps=True)                                   # per-step times (a synchronize per step: outside the timed region)
+    step_ms = sorted(pipe.step_ms)[len(pipe.step_ms) // 2]
+    t = torch.tensor([ms, step_ms], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, step_ms = float(t[0]), float(t[1])
+    if rank == 0:
+        single = b200sd.B200Pipeline(unet, vae, b200sd.B200Scheduler(args.scheduler, ucfg.prediction_type, dev))
+        ref = single(prompt_embeds=cond, negative_prompt_embeds=unc, latents=lat, num_inference_steps=args.denoise_steps,
+                     height=args.size, width=args.size, output_type="uint8").images
+        e0.record()
+        single.denoise(lat.to(dev).permute(0, 2, 3, 1).contiguous(), torch.cat([unc, cond]).to(dev).to(unet.K.op_dtype),
+                       args.denoise_steps)
+        e1.record()
+        torch.cuda.synchronize()
+        one_gpu_step_ms = e0.elapsed_time(e1) / args.denoise_steps
+        mse = float(((img.float() - ref.float()) ** 2).mean())
+        psnr = 99.0 if mse == 0 else 10.0 * math.log10(255.0 ** 2 / mse)
+        value = B * args.steps / (ms * 1e-3)
+        pk = peaks()
+        tflop_img = args.denoise_steps * UNET_TFLOP.get(hw, 0) + VAE_TFLOP.get(hw, 0)
+        line = {"metric": "sd21_images_per_sec", "value": round(value, 4), "unit": "images/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None,
+                "dtype": {torch.float16: "fp16", torch.bfloat16: "bf16"}[unet.K.op_dtype], "data": "synthetic",
+                "config": {"workload": f"SD2.1 {args.size}x{args.size}, {args.denoise_steps} {args.scheduler} steps, CFG 7.5, "
+                                       f"{B} image(s) patch-parallel over {world} GPU(s) by latent rows (BASELINE configs[4])",
+                           "size": args.size, "denoise_steps": args.denoise_steps, "batch": B,
+                           "parallelism": f"pp{world} (row bands; NCCL all-gather of self-attention K|V into local memory, "
+                                          f"send/recv halo rows, all-reduce of GroupNorm sums; VAE decode not split)"},
+                "unet_step_ms": round(step_ms, 3), "unet_step_ms_one_gpu_graph": round(one_gpu_step_ms, 3),
+                "per_step": {"allgather_bytes_received_per_gpu": gathered // args.denoise_steps,
+                             "halo_bytes_received_per_gpu": halo // args.denoise_steps,
+                             "groupnorm_allreduces": n_ar // args.denoise_steps},
+                "psnr_vs_single_gpu_db": round(psnr, 2),
+                "whole_image_tensor_roofline_frac": round(value * tflop_img / (world * pk["tflops"]), 4) if tflop_img else None,
+                "gpu_launches": int(launches * args.steps), "clocks": clk}
+        _emit(line)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
 _REAL_STDOUT = None
 
 
@@ -526,6 +633,8 @@ def main():
         os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
+    elif args.patch_parallel:
+        run_patch_parallel(args)
     else:
         run_b200(args)
 

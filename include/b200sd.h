@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200SD_ABI_VERSION 5
+#define B200SD_ABI_VERSION 6
 
 typedef struct CUstream_st* b200sd_stream_t; /* == cudaStream_t / CUstream */
 
@@ -201,7 +201,10 @@ typedef struct {
 int32_t b200sd_layernorm(const b200sd_layernorm_params* p, b200sd_stream_t stream);
 
 /* ---- im2col for the convs TMA cannot tile: stride-2 Downsample2D and the 4-channel conv_in ---------
- * out[m, (r*3+s)*cin + c] = x[(n % n_src), oy*stride + r - 1, ox*stride + s - 1, c]   (0 outside, 0 for k >= 9*cin)
+ * out[m, (r*3+s)*cin + c] = x[(n % n_src), oy*stride + r - pad_lo, ox*stride + s - pad_lo, c]
+ * (0 outside, 0 for k >= 9*cin); out_h = (in_h + pad_lo + 1 - 3) / stride + 1, likewise out_w.
+ * pad_lo = 1: Conv2d(padding=1).  pad_lo = 0: the VAE encoder's Downsample2D(padding=0), which pads (0,1,0,1) --
+ * nothing before, one row / column after -- and then convolves with stride 2 (AutoencoderKL.encode).
  * n % n_src lets the CFG pair (uncond, cond) share one latent: n_img = 2B, n_src = B.
  */
 typedef struct {
@@ -211,6 +214,7 @@ typedef struct {
     void* out;              /* out_dtype [n_img*out_h*out_w, k_pad], k_pad >= 9*cin, k_pad % 8 == 0 */
     int32_t out_dtype;      /* B200SD_BF16 or B200SD_F16 */
     int32_t k_pad;
+    int32_t pad_lo;         /* 1 or 0 (see above) */
 } b200sd_im2col_params;
 int32_t b200sd_im2col3x3(const b200sd_im2col_params* p, b200sd_stream_t stream);
 

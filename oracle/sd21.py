@@ -18,6 +18,8 @@ Appendix A) on plain torch fp32 primitives.  What pins the restatement:
 What each piece stands for in the reference's call stack:
   UNet2DCondition    -> ``pipe.unet``          (swapped at app/run-sd.py:110-116)
   VAEDecoder         -> ``pipe.vae.decoder`` + ``pipe.vae.post_quant_conv`` (app/run-sd.py:124-134)
+  VAEEncoder         -> ``pipe.vae.encoder`` + ``pipe.vae.quant_conv`` (img2img; SURVEY.md 8f rank 4 -- the reference loads the
+                        whole AutoencoderKL at app/run-sd.py:107 but its text2img path never calls encode)
   DDIM               -> ``DDIMScheduler.from_config`` forced at app/run-sd.py:108
   DPMSolverPP2M/Euler-> the schedulers BASELINE.json words ("DPMSolver++/Euler")
   denoise_loop       -> ``StableDiffusionPipeline.__call__`` steps 2-6, call site app/run-sd.py:140
@@ -408,6 +410,85 @@ class VAEDecoder(nn.Module):
         return self.decoder(self.post_quant_conv(z))
 
     forward = decode
+
+
+# ----------------------------------------------------------------------------------------------
+# AutoencoderKL.encode restatement (the VAE encoder of img2img).  diffusers' Encoder:
+# conv_in -> 4 DownEncoderBlock2D (2 resnets each, the first three followed by a Downsample2D built with padding=0,
+# which pads (0,1,0,1) and then convolves 3x3 stride 2 without padding) -> the same mid block as the decoder ->
+# GroupNorm(eps 1e-6) + SiLU -> conv_out to 2*latent channels; AutoencoderKL then applies the 1x1 quant_conv and reads
+# the result as (mean, logvar) of a diagonal Gaussian.  Published size: 34,163,592 encoder + 72 quant_conv parameters
+# (AutoencoderKL 83,653,863 = encoder + quant_conv + post_quant_conv 20 + decoder 49,490,179).
+# ----------------------------------------------------------------------------------------------
+class EncoderDownsample2D(nn.Module):
+    def __init__(self, c: int):
+        super().__init__()
+        self.conv = nn.Conv2d(c, c, 3, stride=2, padding=0)
+
+    def forward(self, x):
+        return self.conv(F.pad(x, (0, 1, 0, 1), mode="constant", value=0.0))
+
+
+class VAEDownBlock(nn.Module):
+    def __init__(self, cin, cout, layers, groups, add_down):
+        super().__init__()
+        self.resnets = nn.ModuleList([ResnetBlock2D(cin if j == 0 else cout, cout, None, groups, 1e-6) for j in range(layers)])
+        self.downsamplers = nn.ModuleList([EncoderDownsample2D(cout)]) if add_down else None
+
+    def forward(self, h):
+        for r in self.resnets:
+            h = r(h)
+        if self.downsamplers is not None:
+            h = self.downsamplers[0](h)
+        return h
+
+
+class Encoder(nn.Module):
+    def __init__(self, cfg: VAEConfig):
+        super().__init__()
+        boc = cfg.block_out_channels
+        g = cfg.norm_num_groups
+        self.conv_in = nn.Conv2d(cfg.out_channels, boc[0], 3, padding=1)
+        self.down_blocks = nn.ModuleList()
+        cin = boc[0]
+        for i, co in enumerate(boc):
+            self.down_blocks.append(VAEDownBlock(cin, co, cfg.layers_per_block, g, i < len(boc) - 1))
+            cin = co
+        self.mid_block = VAEMidBlock(boc[-1], g)
+        self.conv_norm_out = nn.GroupNorm(g, boc[-1], eps=1e-6)
+        self.conv_out = nn.Conv2d(boc[-1], 2 * cfg.latent_channels, 3, padding=1)
+
+    def forward(self, x):
+        h = self.conv_in(x)
+        for blk in self.down_blocks:
+            h = blk(h)
+        h = self.mid_block(h)
+        return self.conv_out(F.silu(self.conv_norm_out(h)))
+
+
+class VAEEncoder(nn.Module):
+    """``encoder`` + ``quant_conv`` under the key names of AutoencoderKL; ``encode`` returns the moments
+    [B, 2*latent, h/8, w/8] = cat(mean, logvar) that diffusers wraps in DiagonalGaussianDistribution."""
+
+    def __init__(self, cfg: VAEConfig = VAEConfig()):
+        super().__init__()
+        self.cfg = cfg
+        self.encoder = Encoder(cfg)
+        self.quant_conv = nn.Conv2d(2 * cfg.latent_channels, 2 * cfg.latent_channels, 1)
+
+    def encode(self, x):
+        return self.quant_conv(self.encoder(x))
+
+    forward = encode
+
+
+def gaussian_sample(moments: torch.Tensor, noise: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """DiagonalGaussianDistribution: mean, logvar = chunk(moments, 2, dim=1); logvar clamped to [-30, 20];
+    sample = mean + exp(0.5 * logvar) * noise; mode (noise None) = mean."""
+    mean, logvar = torch.chunk(moments, 2, dim=1)
+    if noise is None:
+        return mean
+    return mean + torch.exp(0.5 * torch.clamp(logvar, -30.0, 20.0)) * noise
 
 
 # ----------------------------------------------------------------------------------------------

@@ -12,7 +12,7 @@ from .config import UNetConfig, VAEConfig  # noqa: E402
 from .pipeline import B200Pipeline, StandInTextEncoder, install_into  # noqa: E402
 from .scheduler import B200Scheduler  # noqa: E402
 from .unet import B200UNet  # noqa: E402
-from .vae import B200PostQuantConv, B200VAEDecoder  # noqa: E402
+from .vae import B200PostQuantConv, B200QuantConv, B200VAEDecoder, B200VAEEncoder  # noqa: E402
 
 __all__ = ["ops", "B200CLIPTextEncoder", "CLIPTextConfig", "HashTokenizer", "PromptEncoder", "UNetConfig", "VAEConfig", "B200Pipeline", "StandInTextEncoder", "install_into", "B200Scheduler",
-           "B200UNet", "B200VAEDecoder", "B200PostQuantConv"]
+           "B200UNet", "B200VAEDecoder", "B200PostQuantConv", "B200VAEEncoder", "B200QuantConv"]

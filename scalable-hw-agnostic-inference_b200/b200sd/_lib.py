@@ -7,7 +7,7 @@ from pathlib import Path
 
 _HERE = Path(__file__).resolve().parent
 LIB_PATH = _HERE / "libb200sd.so"
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 BF16, F32, F16 = 1, 2, 3
 
@@ -54,7 +54,7 @@ class LayerNormParams(C.Structure):
 class Im2colParams(C.Structure):
     _fields_ = [("x", c_vp), ("in_dtype", c_i32), ("n_img", c_i32), ("n_src", c_i32), ("in_h", c_i32),
                 ("in_w", c_i32), ("cin", c_i32), ("stride", c_i32), ("out", c_vp), ("out_dtype", c_i32),
-                ("k_pad", c_i32)]
+                ("k_pad", c_i32), ("pad_lo", c_i32)]
 
 
 class UpsampleParams(C.Structure):

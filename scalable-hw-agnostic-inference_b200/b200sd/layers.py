@@ -173,11 +173,12 @@ class Kernels:
             ops.gemm(*args, self.gemm_ws, split_k, 1 if gelu else 0)
         return out
 
-    def im2col(self, x: torch.Tensor, n_img: int, stride: int, k_pad: int) -> torch.Tensor:
+    def im2col(self, x: torch.Tensor, n_img: int, stride: int, k_pad: int, pad_lo: int = 1) -> torch.Tensor:
+        """pad_lo = 1: Conv2d(padding=1); pad_lo = 0: pad (0,1,0,1) then padding 0 (the VAE encoder's Downsample2D)"""
         n_src, h, w, cin = x.shape
-        oh, ow = (h - 1) // stride + 1, (w - 1) // stride + 1
+        oh, ow = (h + pad_lo - 2) // stride + 1, (w + pad_lo - 2) // stride + 1
         out = torch.empty(n_img, oh, ow, k_pad, device=self.device, dtype=self.op_dtype)
-        ops.im2col3x3(x, n_img, n_src, h, w, cin, stride, out)
+        ops.im2col3x3(x, n_img, n_src, h, w, cin, stride, out, pad_lo)
         return out
 
     def upsample2x(self, x: torch.Tensor) -> torch.Tensor:

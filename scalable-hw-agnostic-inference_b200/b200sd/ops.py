@@ -210,11 +210,11 @@ def _layernorm(x, eps, gamma, beta, y):
     _run("layernorm", _nbytes(x, y), L.load().b200sd_layernorm, p, f"rows{p.rows} cols{p.cols}")
 
 
-def _im2col3x3(x, n_img, n_src, in_h, in_w, cin, stride, out):
+def _im2col3x3(x, n_img, n_src, in_h, in_w, cin, stride, out, pad_lo=1):
     p = L.Im2colParams()
     p.x, p.in_dtype, p.n_img, p.n_src, p.in_h, p.in_w, p.cin, p.stride = (_ptr(x), _dt(x), n_img, n_src, in_h, in_w,
                                                                          cin, stride)
-    p.out, p.out_dtype, p.k_pad = _ptr(out), _dt(out), out.shape[-1]
+    p.out, p.out_dtype, p.k_pad, p.pad_lo = _ptr(out), _dt(out), out.shape[-1], pad_lo
     _run("im2col3x3", _nbytes(x, out), L.load().b200sd_im2col3x3, p)
 
 
@@ -287,7 +287,7 @@ _SCHEMAS = {
                   "Tensor(d!)? sums_out=None) -> ()", _groupnorm),
     "gn_tile_sums": ("(Tensor t1, Tensor? t2, int n_img, int groups, Tensor(a!) sums) -> ()", _gn_tile_sums),
     "layernorm": ("(Tensor x, float eps, Tensor gamma, Tensor beta, Tensor(a!) y) -> ()", _layernorm),
-    "im2col3x3": ("(Tensor x, int n_img, int n_src, int in_h, int in_w, int cin, int stride, Tensor(a!) out) -> ()",
+    "im2col3x3": ("(Tensor x, int n_img, int n_src, int in_h, int in_w, int cin, int stride, Tensor(a!) out, int pad_lo=1) -> ()",
                   _im2col3x3),
     "upsample2x": ("(Tensor x, int n_img, int h, int w, int c, Tensor(a!) out) -> ()", _upsample2x),
     "cfg_sched_step": ("(Tensor eps2, Tensor(a!) x, Tensor(b!)? x0_prev, Tensor coef, Tensor? step_index) -> ()",

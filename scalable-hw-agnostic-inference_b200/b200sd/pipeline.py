@@ -125,7 +125,9 @@ class B200Pipeline:
                 self._step_body(st)
             torch.cuda.current_stream().wait_stream(s)
             graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
+            # capture on a stream of THIS pipeline's device: torch.cuda.graph's default capture stream is created once per
+            # process, on whichever device was current then, and entering it would switch a second replica to that device
+            with torch.cuda.graph(graph, stream=s):
                 self._step_body(st)
             self._graph = graph
             st["x"].copy_(keep)

@@ -150,8 +150,13 @@ class BatchingEngine(Engine):
     ONE pipeline call with `output_type="uint8"` (K7 on the device, 4x less D2H than fp32) and hands each uint8 image
     to a thread pool that builds the PIL image / PNG, so encoding overlaps the next batch on the GPU."""
 
-    def __init__(self, pipe, default_steps: int, max_batch: int = 16, max_wait_ms: float = 5.0, png_workers: int = 4):
+    def __init__(self, pipe, default_steps: int, max_batch: int = 16, max_wait_ms: float = 5.0, png_workers: int = 4,
+                 seed_from_prompt: Optional[bool] = None):
         super().__init__(pipe, default_steps)
+        # reproducible serving: the initial noise of a request is drawn from a generator seeded by its prompt, so the same
+        # prompt gives the same image whichever replica, batch or batch slot serves it (B200SD_SEED_FROM_PROMPT=1)
+        self.seed_from_prompt = (os.environ.get("B200SD_SEED_FROM_PROMPT", "0") == "1") if seed_from_prompt is None \
+            else seed_from_prompt
         from concurrent.futures import ThreadPoolExecutor
         import queue
         self.max_batch, self.max_wait_s = max_batch, max_wait_ms / 1e3
@@ -199,9 +204,10 @@ class BatchingEngine(Engine):
                 continue
             self.batches.append(len(batch))
             try:
+                extra = {"latents": self._prompt_latents([r.prompt for r in batch])} if self.seed_from_prompt else {}
                 with self._lock, self._on_device():
                     out = self.pipe(prompt=[r.prompt for r in batch], num_inference_steps=batch[0].steps,
-                                    output_type="uint8").images
+                                    output_type="uint8", **extra).images
                     arr = self._to_host(out)
                 for r, a in zip(batch, arr):
                     self._pool.submit(self._finish, r, a)
@@ -209,6 +215,17 @@ class BatchingEngine(Engine):
                 for r in batch:
                     r.error = e
                     r.event.set()
+
+    def _prompt_latents(self, prompts: List[str]):
+        import hashlib
+
+        import torch
+        hw = self.pipe.unet.config.sample_size
+        out = []
+        for p in prompts:
+            seed = int.from_bytes(hashlib.sha256(p.encode("utf-8")).digest()[:8], "little") % (2 ** 63)
+            out.append(torch.randn(4, hw, hw, generator=torch.Generator("cpu").manual_seed(seed)))
+        return torch.stack(out)
 
     def _to_host(self, out):
         """device uint8 images -> numpy through a pinned staging buffer (async copy + one stream sync, no pageable

@@ -24,6 +24,41 @@ class B200PostQuantConv(torch.nn.Module):
         return z
 
 
+class _MidAttention:
+    """the single-head, 512-wide attention of the VAE mid block (decoder and encoder share the module)"""
+
+    def __init__(self, sd, prefix: str, dev, BF):
+        f = lambda k: sd[prefix + k].to(dev).float().contiguous()
+        b = lambda k: sd[prefix + k].to(dev).to(BF).contiguous()
+        self.at_g, self.at_b = f("group_norm.weight"), f("group_norm.bias")
+        self.wq, self.bq = b("to_q.weight"), f("to_q.bias")
+        self.wk, self.bk = b("to_k.weight"), f("to_k.bias")
+        self.wv, self.bv = b("to_v.weight"), f("to_v.bias")
+        self.wo, self.bo = b("to_out.0.weight"), f("to_out.0.bias")
+
+    def __call__(self, K: Kernels, h: torch.Tensor) -> torch.Tensor:
+        BF = K.op_dtype
+        dev = K.device
+        n, hh, ww, c = h.shape
+        s = hh * ww
+        a = K.groupnorm(h, None, self.at_g, self.at_b, 1e-6, False).view(n, s, c)
+        q = K.linear(a, self.wq, self.bq, out_dtype=BF)
+        k = K.linear(a, self.wk, self.bk, out_dtype=BF)
+        o = torch.empty(n, s, c, device=dev, dtype=BF)
+        scores = torch.empty(s, s, device=dev, dtype=torch.float32)
+        probs = torch.empty(s, s, device=dev, dtype=BF)
+        vt = torch.empty(c, s, device=dev, dtype=BF)
+        for i in range(n):
+            # V^T [c, s] = Wv [c, c] . a_i^T  (+ bv along rows): the PV GEMM then takes it as a K-major B operand
+            K.linear(self.wv, a[i], self.bv, out=vt, bias_along_m=True)
+            K.linear(q[i], k[i], None, out=scores)
+            ops.softmax_rows(scores, probs, s, s, float(c) ** -0.5)
+            K.linear(probs, vt, None, out=o[i])
+        hr = h.view(n * s, c)  # in place on the block's input (dead after this)
+        r = K.linear(o.view(n * s, c), self.wo, self.bo, residual=hr, out=hr, gn_rows_per_image=s)
+        return keep_tile_sums(r.view(n, hh, ww, c), r)
+
+
 class B200VAEDecoder(torch.nn.Module):
     def __init__(self, state_dict: Dict[str, torch.Tensor], config=None, device="cuda",
                  trunk_dtype=None, op_dtype=None, max_images_per_pass: int = 4):
@@ -54,12 +89,7 @@ class B200VAEDecoder(torch.nn.Module):
         self.conv_in_b = f("decoder.conv_in.bias")
 
         self.mid_res = [ResnetParams(sd, f"decoder.mid_block.resnets.{j}.", dev, BF) for j in range(2)]
-        a = "decoder.mid_block.attentions.0."
-        self.at_g, self.at_b = f(a + "group_norm.weight"), f(a + "group_norm.bias")
-        self.wq, self.bq = b(a + "to_q.weight"), f(a + "to_q.bias")
-        self.wk, self.bk = b(a + "to_k.weight"), f(a + "to_k.bias")
-        self.wv, self.bv = b(a + "to_v.weight"), f(a + "to_v.bias")
-        self.wo, self.bo = b(a + "to_out.0.weight"), f(a + "to_out.0.bias")
+        self.mid_attn = _MidAttention(sd, "decoder.mid_block.attentions.0.", dev, BF)
         self.up = []
         for i, co in enumerate(rev):
             blk = {"res": [ResnetParams(sd, f"decoder.up_blocks.{i}.resnets.{j}.", dev, BF)
@@ -80,28 +110,6 @@ class B200VAEDecoder(torch.nn.Module):
     def device(self):
         return self._device
 
-    def _mid_attention(self, h: torch.Tensor) -> torch.Tensor:
-        K = self.K
-        BF = K.op_dtype
-        n, hh, ww, c = h.shape
-        s = hh * ww
-        a = K.groupnorm(h, None, self.at_g, self.at_b, 1e-6, False).view(n, s, c)
-        q = K.linear(a, self.wq, self.bq, out_dtype=BF)
-        k = K.linear(a, self.wk, self.bk, out_dtype=BF)
-        o = torch.empty(n, s, c, device=self._device, dtype=BF)
-        scores = torch.empty(s, s, device=self._device, dtype=torch.float32)
-        probs = torch.empty(s, s, device=self._device, dtype=BF)
-        vt = torch.empty(c, s, device=self._device, dtype=BF)
-        for i in range(n):
-            # V^T [c, s] = Wv [c, c] . a_i^T  (+ bv along rows): the PV GEMM then takes it as a K-major B operand
-            K.linear(self.wv, a[i], self.bv, out=vt, bias_along_m=True)
-            K.linear(q[i], k[i], None, out=scores)
-            ops.softmax_rows(scores, probs, s, s, float(c) ** -0.5)
-            K.linear(probs, vt, None, out=o[i])
-        hr = h.view(n * s, c)  # in place on the block's input (dead after this)
-        r = K.linear(o.view(n * s, c), self.wo, self.bo, residual=hr, out=hr, gn_rows_per_image=s)
-        return keep_tile_sums(r.view(n, hh, ww, c), r)
-
     def decode_nhwc(self, z: torch.Tensor) -> torch.Tensor:
         """z fp32 NHWC [B, h, w, 4] (already divided by scaling_factor) -> fp32 NHWC [B, 8h, 8w, 3]."""
         K = self.K
@@ -109,7 +117,7 @@ class B200VAEDecoder(torch.nn.Module):
         z5 = torch.cat([z, torch.ones_like(z[..., :1])], dim=-1).contiguous()
         h = K.linear(K.im2col(z5, n, 1, 64), self.conv_in_w, self.conv_in_b, gn_rows_per_image=z.shape[1] * z.shape[2])
         h = run_resnet(K, self.mid_res[0], h, None, 1e-6, None)
-        h = self._mid_attention(h)
+        h = self.mid_attn(K, h)
         h = run_resnet(K, self.mid_res[1], h, None, 1e-6, None)
         for blk in self.up:
             for R in blk["res"]:
@@ -130,3 +138,100 @@ class B200VAEDecoder(torch.nn.Module):
         zn = z.to(device=self._device, dtype=torch.float32).permute(0, 2, 3, 1).contiguous()
         img = self.decode_batched_nhwc(zn)
         return img.permute(0, 3, 1, 2).to(z.dtype)
+
+
+class B200QuantConv(torch.nn.Module):
+    """quant_conv lives inside B200VAEEncoder.conv_out; this keeps `vae.quant_conv(h)` callable."""
+
+    def forward(self, h):
+        return h
+
+
+class B200VAEEncoder(torch.nn.Module):
+    """Drop-in for `pipe.vae.encoder` (+ `pipe.vae.quant_conv`): AutoencoderKL.encode of the img2img pipelines
+    (the reference loads the whole AutoencoderKL at app/run-sd.py:107).  Same kernels as the decoder:
+    GroupNorm+SiLU, implicit-GEMM conv3x3, the mid-block attention; the three Downsample2D(padding=0) convolutions --
+    pad (0,1,0,1), then 3x3 stride 2 -- go through im2col with `pad_lo = 0`.  The 1x1 quant_conv is folded exactly into
+    conv_out (it follows it with nothing in between).  Returns the moments cat(mean, logvar)."""
+
+    def __init__(self, state_dict: Dict[str, torch.Tensor], config=None, device="cuda", trunk_dtype=None, op_dtype=None,
+                 max_images_per_pass: int = 2):
+        super().__init__()
+        self.config = VAEConfig.from_any(config if config is not None else VAEConfig())
+        cfg = self.config
+        self._device = torch.device(device)
+        if self._device.type != "cuda":
+            raise RuntimeError("B200VAEEncoder needs a CUDA device (there is no CPU path)")
+        ops.check_device(self._device.index or 0)
+        self.K = Kernels(self._device, trunk_dtype, op_dtype)
+        BF = self.K.op_dtype
+        self.max_images_per_pass = max_images_per_pass
+        dev, sd = self._device, state_dict
+        f = lambda k: sd[k].to(dev).float().contiguous()
+        boc = list(cfg.block_out_channels)
+        lc2 = 2 * cfg.latent_channels
+        # conv_in: 3 image channels -> im2col'd GEMM with K = 27 padded to 64
+        from .layers import pack_conv3x3_im2col
+        self.conv_in_w = pack_conv3x3_im2col(sd["encoder.conv_in.weight"].to(dev), 64, BF)
+        self.conv_in_b = f("encoder.conv_in.bias")
+        self.down = []
+        for i, _co in enumerate(boc):
+            blk = {"res": [ResnetParams(sd, f"encoder.down_blocks.{i}.resnets.{j}.", dev, BF)
+                           for j in range(cfg.layers_per_block)], "down": None}
+            if i < len(boc) - 1:
+                p = f"encoder.down_blocks.{i}.downsamplers.0.conv."
+                blk["down"] = (pack_conv3x3(sd[p + "weight"].to(dev), BF), f(p + "bias"))
+            self.down.append(blk)
+        self.mid_res = [ResnetParams(sd, f"encoder.mid_block.resnets.{j}.", dev, BF) for j in range(2)]
+        self.mid_attn = _MidAttention(sd, "encoder.mid_block.attentions.0.", dev, BF)
+        self.out_g, self.out_b = f("encoder.conv_norm_out.weight"), f("encoder.conv_norm_out.bias")
+        # quant_conv o conv_out: W'[o, c, ky, kx] = sum_m Wq[o, m] W[m, c, ky, kx];  b' = Wq b + bq
+        w_out = sd["encoder.conv_out.weight"].to(dev).double()                  # [2lc, C, 3, 3]
+        w_q = sd["quant_conv.weight"].to(dev).double().reshape(lc2, lc2)
+        folded = torch.einsum("om,mcyx->ocyx", w_q, w_out)
+        self.conv_out_w = pack_conv3x3(folded.float(), BF)
+        self.conv_out_b = (w_q @ sd["encoder.conv_out.bias"].to(dev).double()
+                           + sd["quant_conv.bias"].to(dev).double()).float().contiguous()
+
+    @property
+    def dtype(self):
+        return self.K.op_dtype
+
+    @property
+    def device(self):
+        return self._device
+
+    def encode_nhwc(self, x: torch.Tensor) -> torch.Tensor:
+        """x fp32 NHWC [B, H, W, 3] in [-1, 1] -> moments fp32 NHWC [B, H/8, W/8, 2*latent]"""
+        K = self.K
+        n, hh, ww, _ = x.shape
+        h = K.linear(K.im2col(x.contiguous(), n, 1, 64), self.conv_in_w, self.conv_in_b, gn_rows_per_image=hh * ww)
+        for blk in self.down:
+            for R in blk["res"]:
+                h = run_resnet(K, R, h, None, 1e-6, None)
+            if blk["down"] is not None:
+                w, b = blk["down"]
+                c = h.shape[-1]
+                cols = K.im2col(h, h.shape[0], 2, 9 * c, pad_lo=0)
+                h = K.linear(cols, w, b, gn_rows_per_image=cols.shape[1] * cols.shape[2])
+        h = run_resnet(K, self.mid_res[0], h, None, 1e-6, None)
+        h = self.mid_attn(K, h)
+        h = run_resnet(K, self.mid_res[1], h, None, 1e-6, None)
+        a = K.groupnorm(h, None, self.out_g, self.out_b, 1e-6, True)
+        return K.conv3x3(a, self.conv_out_w, self.conv_out_b, out_dtype=torch.float32)
+
+    def forward(self, x: torch.Tensor, *_a, **_k) -> torch.Tensor:
+        """`vae.encoder(x)` signature: NCHW image in [-1, 1] -> NCHW moments (quant_conv folded in), caller's dtype"""
+        xn = x.to(device=self._device, dtype=torch.float32).permute(0, 2, 3, 1).contiguous()
+        outs = [self.encode_nhwc(xn[i:i + self.max_images_per_pass])
+                for i in range(0, xn.shape[0], self.max_images_per_pass)]
+        m = outs[0] if len(outs) == 1 else torch.cat(outs)
+        return m.permute(0, 3, 1, 2).to(x.dtype)
+
+    def encode_latents(self, x: torch.Tensor, noise: torch.Tensor = None) -> torch.Tensor:
+        """what img2img feeds the denoising loop: scaling_factor * (mean + exp(0.5 * clamp(logvar, -30, 20)) * noise),
+        or scaling_factor * mean (the distribution's mode) without noise"""
+        m = self.forward(x).float()
+        mean, logvar = torch.chunk(m, 2, dim=1)
+        z = mean if noise is None else mean + torch.exp(0.5 * logvar.clamp(-30.0, 20.0)) * noise.to(m.device)
+        return self.config.scaling_factor * z

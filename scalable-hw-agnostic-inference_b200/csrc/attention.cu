@@ -2,12 +2,14 @@
 //
 // One CTA owns 256 query rows = two 128-row tiles (A, B) that share every K/V tile:
 //   warp 0        TMA producer : both Q tiles once, then K/V tiles (128 kv rows x 64) through a 4-stage ring
-//   warp 1        UMMA issuer  : S_t = Q_t K^T (128x128x64, both operands from shared memory) into TMEM;
-//                                O_t += P_t V (128x64x128) with P_t read FROM TMEM (tcgen05.mma A-in-TMEM form) and V as
-//                                an MN-major shared-memory operand -- no transpose of V and no shared-memory round trip
-//                                for P.  Issue is event-driven: whichever of {P_A V, P_B V, Q_A K^T, Q_B K^T} is ready goes.
-//   warps 2..9    softmax A    } two threads per query row, 64 score columns each (tcgen05.ld 32x32b: a thread owns whole
-//   warps 10..17  softmax B    } columns of its row, so the only cross-thread step is one row-max exchange per tile);
+//   warp 1, 18    UMMA issuers : one warp per Q tile.  S_t = Q_t K^T (128x128x64, both operands from shared memory) into
+//                                TMEM; O_t += P_t V (128x64x128) with P_t read FROM TMEM (tcgen05.mma A-in-TMEM form) and V
+//                                as an MN-major shared-memory operand -- no transpose of V and no shared-memory round trip
+//                                for P.  A tile's events come in a fixed order, so its warp issues in order behind
+//                                blocking barrier waits (Q K^T of step j+1, then P V of step j).
+//   warps 2..9    softmax A    } either two threads per query row, 64 score columns each (tcgen05.ld 32x32b; one row-max
+//   warps 10..17  softmax B    } exchange per tile), or -- default -- a row spread over the four threads of a quad
+//                                (tcgen05.ld 16x256b; row max = two shuffles, nothing crosses warps);
 //                                the scores are held in registers so S_t is released to the next QK^T at once; exp2 with
 //                                the scale folded in; lazy rescale of O (only when the running max grows by more than
 //                                2^8); P packed to 16 bits and written back to TMEM with one tcgen05.st per thread.
@@ -29,7 +31,8 @@ constexpr int ATT_BN = 128;          // kv rows per tile
 constexpr int ATT_D = 64;
 constexpr int ATT_STAGES = 4;
 constexpr int ATT_TILE = 128 * 128;  // bytes of a [128 x 64] 16-bit tile
-constexpr int ATT_THREADS = 32 * (2 + 8 * ATT_QT);  // TMA, UMMA, then 8 softmax warps per Q tile
+constexpr int ATT_THREADS = 32 * (3 + 8 * ATT_QT);  // TMA, UMMA (tile A), 8 softmax warps per Q tile, UMMA (tile B)
+constexpr int ATT_MMA_B_WARP = 2 + 8 * ATT_QT;
 constexpr int ATT_XCH = 3 * ATT_QT * 256 * 4;       // row-max exchange [parity][tile][half][128] fp32 + row-sum exchange [tile][half][128]
 constexpr int ATT_SMEM = ATT_QT * ATT_TILE /*Q*/ + ATT_STAGES * 2 * ATT_TILE /*K,V*/ + ATT_XCH + 1024 + 256;
 // TMEM columns: S_A 0..127, S_B 128..255, O_A 256..319, O_B 320..383, P_A 384..447, P_B 448..511 (16-bit pairs)
@@ -43,6 +46,7 @@ struct AttnKernelParams {
     long long ld_out;
     int causal;   // 1: key j is visible to query i only if j <= i
     int stagger;  // 1: Q tile B starts half a softmax period behind tile A (see the UMMA warp)
+    int pair_bar; // (half-row layout) 1: the two warps that share a row synchronise alone (64-thread barrier) instead of per tile
 };
 
 __device__ __forceinline__ float ex2_ftz(float x) {
@@ -107,7 +111,9 @@ __device__ __forceinline__ void tmem_st_x32(uint32_t taddr, const uint32_t (&r)[
 }
 
 // EMU_MASK: bit i set = pair i of every eight pairs of exponentials is evaluated by exp2_poly2 instead of the MUFU.
-template <bool F16, int EMU_MASK, bool PERSIST>
+// QUADROWS: the softmax warps read S with the 16-lane TMEM shapes (a row lives in the four threads of a quad, a warp owns
+// 16 whole rows) instead of one half-row per thread: no row-max exchange between warps, no named barrier per kv step.
+template <bool F16, int EMU_MASK, bool PERSIST, bool QUADROWS>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
     attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                      const __grid_constant__ CUtensorMap tmV, const AttnKernelParams p) {
@@ -147,7 +153,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
     }
     if (warp == 1 && lane == 0) {
         mbar_init(q_full, 1);
-        for (int s = 0; s < ATT_STAGES; ++s) mbar_init(&kv_full[s], 1), mbar_init(&kv_empty[s], 1);
+        for (int s = 0; s < ATT_STAGES; ++s) mbar_init(&kv_full[s], 1), mbar_init(&kv_empty[s], ATT_QT);  // one report per issuing warp
         for (int t = 0; t < ATT_QT; ++t) {
             mbar_init(&s_full[t], 1);
             mbar_init(&s_free[t], 8);
@@ -155,7 +161,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
             mbar_init(&pv_done[t], 1);
         }
         mbar_init(b_go, 8);
-        mbar_init(q_empty, 1);
+        mbar_init(q_empty, ATT_QT);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_slot, 512);
@@ -197,103 +203,260 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                 if (++stage == ATT_STAGES) stage = 0, phase ^= 1;
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == 1 || warp == ATT_MMA_B_WARP) {
+        // ---------------------------------------------------------------- UMMA issue: one warp per Q tile
+        // Each Q tile has its own issuing warp.  For ONE tile the events come in a fixed order -- S(j) read by the
+        // softmax group (s_free) always precedes P(j) written (p_full) -- so the warp waits for them in that order with
+        // blocking waits and needs no polling.  Measured with one warp polling for both tiles (ncu source view, S = 9216):
+        // that warp's loop was ~600 dependent scalar instructions per kv step, ~3000 cycles, and it found all four of
+        // {P_A V, Q_A K^T, P_B V, Q_B K^T} ready on every pass: the issuing warp, not the exponentials or the tensor pipe
+        // (34 % active), set the kernel's speed, and the softmax warps spent 46 % of their time waiting for it.
         constexpr uint32_t bf = F16 ? 0u : 1u;
         constexpr uint32_t idesc_qk = umma_idesc(128, ATT_BN, bf, bf, 0, 0);
         constexpr uint32_t idesc_pv = umma_idesc(128, ATT_D, bf, bf, 0, 1);  // A = P (TMEM, K-major), B = V MN-major
+        const int t = warp == 1 ? 0 : 1;
         const uint32_t tmem_u = __shfl_sync(FULL, tmem_base, 0);
         const uint32_t q_u = __shfl_sync(FULL, smem_u32(sQ), 0);
         const uint32_t kv_u = __shfl_sync(FULL, smem_u32(sKV), 0);
-        auto issue_qk = [&](int t, int stage) {
-            const uint32_t q_addr = q_u + t * ATT_TILE;
-            const uint32_t k_addr = kv_u + stage * 2 * ATT_TILE;
-            const uint32_t d = tmem_u + ATT_TMEM_S + t * 128;
+        // descriptors of stage 0; stage s adds s * (2 * TILE >> 4) to the start-address field (no carry: the field holds
+        // addr >> 4 of a 227 KB window in 14 bits)
+        const uint64_t qdesc = umma_desc_sw128(q_u + t * ATT_TILE);
+        const uint64_t kdesc0 = umma_desc_sw128(kv_u);
+        const uint64_t vdesc0 = umma_desc_sw128(kv_u + ATT_TILE, /*lbo*/ 128 * 128, /*sbo*/ 1024);
+        constexpr uint32_t STAGE_STEP = (2 * ATT_TILE) >> 4;
+        const uint32_t s_tmem = tmem_u + ATT_TMEM_S + t * 128;
+        const uint32_t p_tmem = tmem_u + ATT_TMEM_P + t * 64;
+        const uint32_t o_tmem = tmem_u + ATT_TMEM_O + t * ATT_D;
+        auto issue_qk = [&](int stage) {
+            const uint64_t kdesc = kdesc0 + (uint64_t)(stage * STAGE_STEP);
             if (elect_one()) {
 #pragma unroll
-                for (int ks = 0; ks < ATT_D / 16; ++ks)
-                    umma_bf16(d, umma_desc_sw128(q_addr + ks * 32), umma_desc_sw128(k_addr + ks * 32), idesc_qk,
-                              ks != 0);
+                for (int ks = 0; ks < ATT_D / 16; ++ks)  // +32 bytes along K = +2 in the (addr >> 4) field
+                    umma_bf16(s_tmem, qdesc + 2 * ks, kdesc + 2 * ks, idesc_qk, ks != 0);
                 umma_commit(&s_full[t]);
             }
             __syncwarp();
         };
-        auto issue_pv = [&](int t, int j, int stage) {
-            const uint32_t v_addr = kv_u + stage * 2 * ATT_TILE + ATT_TILE;
-            const uint32_t p_tmem = tmem_u + ATT_TMEM_P + t * 64;
-            const uint32_t o_tmem = tmem_u + ATT_TMEM_O + t * ATT_D;
+        auto issue_pv = [&](int j, int stage) {
+            const uint64_t vdesc = vdesc0 + (uint64_t)(stage * STAGE_STEP);
             if (elect_one()) {
 #pragma unroll
-                for (int ks = 0; ks < ATT_BN / 16; ++ks) {
+                for (int ks = 0; ks < ATT_BN / 16; ++ks)
                     // 16 K-elements of P = 8 TMEM columns (two 16-bit values per column); 16 kv rows of V = 2048 bytes
-                    const uint64_t bdesc = umma_desc_sw128(v_addr + ks * 2048, /*lbo*/ 128 * 128, /*sbo*/ 1024);
-                    umma_ts(o_tmem, p_tmem + ks * 8, bdesc, idesc_pv, (j | ks) != 0);
-                }
+                    umma_ts(o_tmem, p_tmem + ks * 8, vdesc + (uint64_t)(ks * (2048 >> 4)), idesc_pv, (j | ks) != 0);
                 umma_commit(&pv_done[t]);
+                umma_commit(&kv_empty[stage]);  // this tile is done with the stage (the other tile's warp reports too)
             }
             __syncwarp();
         };
-        // Event-driven issue: the two Q tiles advance independently.  Whatever is ready goes next, P V first (the
-        // softmax group of that tile needs its completion before it may overwrite P), then the next Q K^T.
-        // Barrier parities run over the whole life of the CTA: gk0 = kv tiles of all earlier items (the K/V ring),
-        // gt0[t] = kv steps Q tile t has done before this item (tile B sits out items whose second tile is empty).
-        int gk0 = 0, gt0[ATT_QT] = {0, 0}, n_it = 0;
+        // Barrier parities run over the whole life of the CTA: gk = kv tiles of all earlier items (the K/V ring),
+        // gt = kv steps this Q tile has done before this item (tile B sits out items whose second tile is empty).
+        int gk = 0, gt = 0, n_it = 0;
         for (int it = blockIdx.x; it < p.items; it += (PERSIST ? (int)gridDim.x : p.items), ++n_it) {
-        const int nq = item_q0(it) + ATT_BM < p.sq ? 2 : 1;
-        const int NI = PERSIST ? n_it : 0, GK = PERSIST ? gk0 : 0;
-        const int GT[ATT_QT] = {PERSIST ? gt0[0] : 0, PERSIST ? gt0[1] : 0};
-        mbar_wait(q_full, NI & 1);
-        tc_fence_after();
-        int next_qk[ATT_QT] = {0, 0}, next_pv[ATT_QT] = {0, 0};
-        int kv_ready = 0;  // kv tiles [0, kv_ready) of this item have landed in shared memory
-        int released = 0;  // kv tiles [0, released) of this item have been handed back to the producer
-        int pending = nq * n_tiles;
-        while (pending > 0) {
-            while (kv_ready < n_tiles && __all_sync(FULL, mbar_test_wait(&kv_full[(GK + kv_ready) % ATT_STAGES],
-                                                                          ((GK + kv_ready) / ATT_STAGES) & 1)))
-                ++kv_ready;
-#pragma unroll
-            for (int t = 0; t < ATT_QT; ++t) {
-                if (t >= nq) continue;
-                int j = next_pv[t];
-                if (j < next_qk[t] && __all_sync(FULL, mbar_test_wait(&p_full[t], (GT[t] + j) & 1))) {
+            const bool active = t == 0 || item_q0(it) + ATT_BM < p.sq;
+            const int NI = PERSIST ? n_it : 0, GK = PERSIST ? gk : 0, GT = PERSIST ? gt : 0;
+            auto kv_stage = [&](int j) { return (GK + j) % ATT_STAGES; };
+            auto kv_parity = [&](int j) { return (uint32_t)(((GK + j) / ATT_STAGES) & 1); };
+            if (!active) {
+                // this tile holds no live row: the ring and the Q buffer still expect one report per issuing warp.  It also
+                // waits on the once-per-item barriers like an active tile would, so that it can never run a whole phase
+                // ahead of them (a parity wait cannot tell phase n from phase n - 2)
+                mbar_wait(q_full, NI & 1);
+                if (p.stagger) mbar_wait(b_go, NI & 1);
+                for (int j = 0; j < n_tiles; ++j) {
+                    mbar_wait(&kv_full[kv_stage(j)], kv_parity(j));
+                    if (elect_one()) mbar_arrive(&kv_empty[kv_stage(j)]);
+                    __syncwarp();
+                }
+                if (PERSIST) {
+                    if (elect_one()) mbar_arrive(q_empty);
+                    __syncwarp();
+                }
+            } else {
+                mbar_wait(q_full, NI & 1);
+                // The softmax groups of the two tiles alternate between a MUFU-bound phase (exponentials) and a phase that
+                // does not touch the MUFU (TMEM loads, row max, P store).  Started together they stay in step and fight
+                // over the MUFU, then leave it idle together; tile B's first Q K^T therefore waits until tile A has
+                // entered its first exponential phase, and the offset persists (the loops are self-paced).
+                if (t == 1 && p.stagger) mbar_wait(b_go, NI & 1);
+                mbar_wait(&kv_full[kv_stage(0)], kv_parity(0));
+                // the S tile must have been read by the softmax group (the last step of this tile's previous item)
+                if (GT > 0) mbar_wait(&s_free[t], (GT - 1) & 1);
+                tc_fence_after();
+                issue_qk(kv_stage(0));
+                if (PERSIST && n_tiles == 1) {
+                    if (elect_one()) umma_commit(q_empty);
+                    __syncwarp();
+                }
+                for (int j = 0; j < n_tiles; ++j) {
+                    if (j + 1 < n_tiles) {
+                        mbar_wait(&kv_full[kv_stage(j + 1)], kv_parity(j + 1));
+                        mbar_wait(&s_free[t], (GT + j) & 1);
+                        tc_fence_after();
+                        issue_qk(kv_stage(j + 1));
+                        // every Q K^T of this item is issued: once they complete, the next item's Q tiles may land
+                        if (PERSIST && j + 2 == n_tiles) {
+                            if (elect_one()) umma_commit(q_empty);
+                            __syncwarp();
+                        }
+                    }
+                    mbar_wait(&p_full[t], (GT + j) & 1);
                     tc_fence_after();
-                    issue_pv(t, j, (GK + j) % ATT_STAGES);
-                    next_pv[t] = j + 1;
-                    --pending;
-                    int mn = next_pv[0];
-                    if (nq > 1 && next_pv[1] < mn) mn = next_pv[1];
-                    for (; released < mn; ++released) {
-                        if (elect_one()) umma_commit(&kv_empty[(GK + released) % ATT_STAGES]);
-                        __syncwarp();
+                    issue_pv(j, kv_stage(j));
+                }
+                gt += n_tiles;
+            }
+            gk += n_tiles;
+        }
+    } else if (QUADROWS) {
+        // ---------------------------------------------------------------- softmax + output, quad-row layout
+        // 8 warps per Q tile; warp (quad, half) owns rows quad*32 + half*16 .. +15 of the tile and ALL 128 score columns
+        // of them: thread t holds rows t/4 and t/4 + 8, columns 8i + 2(t%4), +1 for i = 0..15 (tcgen05.ld 16x256b).
+        // The row max is two shuffles inside the quad; nothing is exchanged between warps, so the warps of a tile drift
+        // apart freely and spread their MUFU phases instead of hitting the pipe in lock-step after a barrier.
+        const int t = (warp - 2) >> 3;
+        int gt = 0, n_it = 0;
+        for (int it = blockIdx.x; it < p.items; it += (PERSIST ? (int)gridDim.x : p.items), ++n_it) {
+        const int q0 = item_q0(it), head = item_head(it), b = item_b(it);
+        const bool has_b = q0 + ATT_BM < p.sq;
+        const int GTS = PERSIST ? gt : 0;
+        if (t == 0 || has_b) {
+            const int half = ((warp - 2) >> 2) & 1;
+            const int quad = warp & 3;
+            const int wrow0 = quad * 32 + half * 16;   // first tile row of this warp
+            const int r_in = lane >> 2, cq = lane & 3;  // thread: rows wrow0 + r_in, + 8; column pair index cq
+            const uint32_t lane_off = (uint32_t)wrow0 << 16;
+            const uint32_t s_addr = tmem_base + ATT_TMEM_S + t * 128 + lane_off;
+            const uint32_t o_addr = tmem_base + ATT_TMEM_O + t * ATT_D + lane_off;
+            const uint32_t p_addr = tmem_base + ATT_TMEM_P + t * 64 + lane_off;
+            const float sc = p.scale_log2;
+            float m_used[2] = {0.f, 0.f}, l[2] = {0.f, 0.f};
+            for (int j = 0; j < n_tiles; ++j) {
+                mbar_wait(&s_full[t], (GTS + j) & 1);
+                tc_fence_after();
+                uint32_t s[64];
+                tmem_ld_16x256b_x16(s_addr, s);
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s_free[t]);
+
+                // masking stays behind a warp-uniform branch (see the half-row layout below)
+                const int valid = p.skv - j * ATT_BN;  // live kv columns of this tile
+                const int kbase = j * ATT_BN;
+                const bool diag = p.causal && (kbase + ATT_BN - 1 > q0 + t * ATT_BM + wrow0);
+                if (valid < ATT_BN || diag) {
+                    __syncwarp();
+                    const int qa = p.causal ? q0 + t * ATT_BM + wrow0 + r_in : 0x7fffffff;
+                    const int qb = p.causal ? qa + 8 : 0x7fffffff;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const int col = 8 * i + 2 * cq + (e & 1);
+                            if (col >= valid || kbase + col > ((e & 2) ? qb : qa)) s[4 * i + e] = __float_as_uint(-INFINITY);
+                        }
+                }
+                float mxa = -INFINITY, mxb = -INFINITY;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    mxa = fmax3(mxa, __uint_as_float(s[4 * i]), __uint_as_float(s[4 * i + 1]));
+                    mxb = fmax3(mxb, __uint_as_float(s[4 * i + 2]), __uint_as_float(s[4 * i + 3]));
+                }
+                mxa = fmaxf(mxa, __shfl_xor_sync(0xffffffffu, mxa, 1));
+                mxb = fmaxf(mxb, __shfl_xor_sync(0xffffffffu, mxb, 1));
+                mxa = fmaxf(mxa, __shfl_xor_sync(0xffffffffu, mxa, 2));
+                mxb = fmaxf(mxb, __shfl_xor_sync(0xffffffffu, mxb, 2));
+                if (t == 0 && j == 0 && lane == 0) mbar_arrive(b_go);
+                const float m_new[2] = {mxa * sc, mxb * sc};
+                float alpha[2] = {1.f, 1.f};
+                bool need = false;
+#pragma unroll
+                for (int r = 0; r < 2; ++r) {
+                    if (j == 0) {
+                        m_used[r] = m_new[r];
+                    } else if (m_new[r] > m_used[r] + TAU) {
+                        alpha[r] = ex2_ftz(m_used[r] - m_new[r]);
+                        m_used[r] = m_new[r];
+                        need = true;
                     }
                 }
-                j = next_qk[t];
-                // The softmax groups of the two tiles alternate between a MUFU-bound phase (exponentials) and a phase
-                // that does not touch the MUFU (TMEM loads, row max, exchange, P store).  Started together they stay in
-                // step and fight over the MUFU, then leave it idle together; tile B's first Q K^T therefore waits until
-                // tile A has entered its first exponential phase, and the offset persists (the loops are self-paced).
-                // (Measured with clock stamps afterwards: per kv step a group spends ~1850 of ~2780 cycles in its
-                // exponentials whether or not the other group is in them too -- run strictly in turns, each phase still
-                // took ~1450 cycles, twice the MUFU time of its 2 warps per scheduler: the phase is bound by per-warp
-                // latency, and four warps in it at once fill the MUFU better than two.  So no hand-over barrier.)
-                bool go = j < kv_ready;
-                // the S tile must have been read by the softmax group (also the last one of this tile's previous item)
-                if (go && GT[t] + j > 0) go = __all_sync(FULL, mbar_test_wait(&s_free[t], (GT[t] + j - 1) & 1));
-                if (go && j == 0 && t == 1 && p.stagger) go = __all_sync(FULL, mbar_test_wait(b_go, NI & 1));
-                if (go) {
+                uint32_t pk[32];
+                const uint64_t sc2 = pack2(sc, sc);
+                const uint64_t negm2[2] = {pack2(-m_used[0], -m_used[0]), pack2(-m_used[1], -m_used[1])};
+                uint64_t ls2[2] = {pack2(0.f, 0.f), pack2(0.f, 0.f)};
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+#pragma unroll
+                    for (int r = 0; r < 2; ++r) {
+                        const uint64_t x2 = fma2(pack2(__uint_as_float(s[4 * i + 2 * r]), __uint_as_float(s[4 * i + 2 * r + 1])),
+                                                 sc2, negm2[r]);
+                        float e0, e1;
+                        if ((EMU_MASK >> ((2 * i + r) & 7)) & 1) {
+                            exp2_poly2(x2, e0, e1);
+                        } else {
+                            float x0, x1;
+                            unpack2(x2, x0, x1);
+                            e0 = ex2_ftz(x0), e1 = ex2_ftz(x1);
+                        }
+                        ls2[r] = add2(ls2[r], pack2(e0, e1));
+                        pk[2 * i + r] = pack_h2(e0, e1, F16);
+                    }
+                }
+                if (j > 0) {
+                    mbar_wait(&pv_done[t], (GTS + j - 1) & 1);
                     tc_fence_after();
-                    issue_qk(t, (GK + j) % ATT_STAGES);
-                    next_qk[t] = j + 1;
+                }
+                if (__any_sync(0xffffffffu, need)) {
+                    uint32_t o[32];  // rows r_in / r_in + 8, columns 8i + 2cq, +1 of the 64 head-dim columns
+                    tmem_ld_16x256b_x8(o_addr, o);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        o[4 * i] = __float_as_uint(__uint_as_float(o[4 * i]) * alpha[0]);
+                        o[4 * i + 1] = __float_as_uint(__uint_as_float(o[4 * i + 1]) * alpha[0]);
+                        o[4 * i + 2] = __float_as_uint(__uint_as_float(o[4 * i + 2]) * alpha[1]);
+                        o[4 * i + 3] = __float_as_uint(__uint_as_float(o[4 * i + 3]) * alpha[1]);
+                    }
+                    tmem_st_16x256b_x8(o_addr, o);
+                }
+#pragma unroll
+                for (int r = 0; r < 2; ++r) {
+                    float a0, a1;
+                    unpack2(ls2[r], a0, a1);
+                    l[r] = l[r] * alpha[r] + (a0 + a1);
+                }
+                tmem_st_16x128b_x16(p_addr, pk);  // 128 probabilities per row = 64 TMEM columns, 16 of them from this thread
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&p_full[t]);
+            }
+            // ---- epilogue: O / l -> 16-bit
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+                l[r] += __shfl_xor_sync(0xffffffffu, l[r], 1);
+                l[r] += __shfl_xor_sync(0xffffffffu, l[r], 2);
+            }
+            const float inv[2] = {1.0f / l[0], 1.0f / l[1]};
+            mbar_wait(&pv_done[t], (GTS + n_tiles - 1) & 1);
+            tc_fence_after();
+            uint32_t o[32];
+            tmem_ld_16x256b_x8(o_addr, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+                const int qrow = q0 + t * ATT_BM + wrow0 + r_in + 8 * r;
+                if (qrow < p.sq) {
+                    uint32_t* orow = reinterpret_cast<uint32_t*>(p.out + ((long long)b * p.sq + qrow) * p.ld_out + head * ATT_D);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        orow[4 * i + cq] = pack_h2(__uint_as_float(o[4 * i + 2 * r]) * inv[r],
+                                                   __uint_as_float(o[4 * i + 2 * r + 1]) * inv[r], F16);
                 }
             }
+            gt += n_tiles;
         }
-        // every Q K^T of this item is issued: once they complete, the Q tiles may be overwritten by the next item's
-        if (PERSIST) {
-            if (elect_one()) umma_commit(q_empty);
-            __syncwarp();
-        }
-        gk0 += n_tiles;
-        for (int t = 0; t < nq; ++t) gt0[t] += n_tiles;
         }
     } else {
         // ---------------------------------------------------------------- softmax + output
@@ -354,7 +517,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
                 // double-buffered by tile parity so one named barrier per tile suffices
                 float* xch = xchg + (((GTS + j) & 1) * ATT_QT + t) * 256;
                 xch[half * 128 + row] = fmaxf(mx0, mx1);
-                named_bar_sync(2 + t, 256);
+                if (p.pair_bar) named_bar_sync(4 + t * 4 + quad, 64); else named_bar_sync(2 + t, 256);
                 if (t == 0 && j == 0 && lane == 0) mbar_arrive(b_go);
                 const float m_new = fmaxf(xch[row], xch[128 + row]) * sc;
                 float alpha = 1.f;
@@ -419,7 +582,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
             float* xch = xchg + (2 * ATT_QT + t) * 256;  // its own buffer: the next item's first row max may already be
                                                          // on its way into the parity buffers
             xch[half * 128 + row] = l;
-            named_bar_sync(2 + t, 256);
+            if (p.pair_bar) named_bar_sync(4 + t * 4 + quad, 64); else named_bar_sync(2 + t, 256);
             const float inv = 1.0f / (xch[row] + xch[128 + row]);
             mbar_wait(&pv_done[t], (GTS + n_tiles - 1) & 1);
             tc_fence_after();
@@ -448,19 +611,19 @@ __global__ void __launch_bounds__(ATT_THREADS, 1)
     if (warp == 2) tmem_dealloc(tmem_base, 512);
 }
 
-template <bool F16, int EMU_MASK, bool PERSIST>
+template <bool F16, int EMU_MASK, bool PERSIST, bool QUADROWS>
 static int32_t launch_attention(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                                 const AttnKernelParams& kp, dim3 grid, cudaStream_t stream) {
     static bool attr_set[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(attention_kernel<F16, EMU_MASK, PERSIST>,
+        cudaError_t e = cudaFuncSetAttribute(attention_kernel<F16, EMU_MASK, PERSIST, QUADROWS>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM);
         if (e != cudaSuccess) return set_error(B200SD_ERR_CUDA, "attention smem attribute: %s", cudaGetErrorString(e));
         attr_set[dev] = true;
     }
-    B200SD_LAUNCH("attention_kernel", (attention_kernel<F16, EMU_MASK, PERSIST>), grid, dim3(ATT_THREADS), ATT_SMEM, stream, tmQ,
+    B200SD_LAUNCH("attention_kernel", (attention_kernel<F16, EMU_MASK, PERSIST, QUADROWS>), grid, dim3(ATT_THREADS), ATT_SMEM, stream, tmQ,
                   tmK, tmV, kp);
     count_launch();
     B200SD_CHECK_LAUNCH("attention_kernel");
@@ -471,6 +634,27 @@ static int stagger_from_env() {
     static int cached = -1;
     if (cached < 0) {
         const char* e = getenv("B200SD_ATTN_STAGGER");
+        cached = (e && e[0] == '0') ? 0 : 1;
+    }
+    return cached;
+}
+
+// softmax register layout: 0 = half rows per thread (default), 1 = quad rows (16-lane TMEM shapes, no exchange between
+// warps).  Measured inside the batch-16 pipeline (power-capped clocks): half rows with the pair barrier 740 ms of attention
+// per pass, quad rows 760 ms; standalone at S = 9216 both run at ~905 TFLOP/s (profiles/r02_attn_sweep.txt)
+static int layout_from_env() {
+    static int cached = -1;
+    if (cached < 0) {
+        const char* e = getenv("B200SD_ATTN_LAYOUT");
+        cached = (e && e[0] == '1') ? 1 : 0;
+    }
+    return cached;
+}
+
+static int pair_bar_from_env() {
+    static int cached = -1;
+    if (cached < 0) {
+        const char* e = getenv("B200SD_ATTN_PAIR_BAR");
         cached = (e && e[0] == '0') ? 0 : 1;
     }
     return cached;
@@ -525,6 +709,7 @@ extern "C" int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_str
     kp.out = static_cast<uint16_t*>(p->out);
     kp.ld_out = p->ld_out;
     kp.stagger = stagger_from_env();
+    kp.pair_bar = pair_bar_from_env();
     kp.causal = p->causal ? 1 : 0;
     B200SD_CHECK_ARG(!p->causal || p->sq == p->skv, "attention: causal needs sq == skv");
     const int rows_per_cta = ATT_BM * ATT_QT;
@@ -540,20 +725,23 @@ extern "C" int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_str
     cudaStream_t s = as_stream(stream);
     // share of the exponentials evaluated on the FMA pipe instead of the MUFU: 0 none, 1 = 50 %, 2 = 25 %, 3 = 37.5 %
     const int emu = emu_mask_from_env();
+    const bool quad = layout_from_env() != 0;
+#define B200SD_ATTN_LAUNCH(F, M)                                                                               \
+    return quad ? (persistent ? launch_attention<F, M, true, true>(tmQ, tmK, tmV, kp, grid, s)                  \
+                              : launch_attention<F, M, false, true>(tmQ, tmK, tmV, kp, grid, s))                \
+                : (persistent ? launch_attention<F, M, true, false>(tmQ, tmK, tmV, kp, grid, s)                 \
+                              : launch_attention<F, M, false, false>(tmQ, tmK, tmV, kp, grid, s));
 #define B200SD_ATTN_DISPATCH(F)                                                                              \
     switch (emu) {                                                                                            \
-        case 1: return persistent ? launch_attention<F, 0b10101010, true>(tmQ, tmK, tmV, kp, grid, s)          \
-                                  : launch_attention<F, 0b10101010, false>(tmQ, tmK, tmV, kp, grid, s);        \
-        case 2: return persistent ? launch_attention<F, 0b10001000, true>(tmQ, tmK, tmV, kp, grid, s)          \
-                                  : launch_attention<F, 0b10001000, false>(tmQ, tmK, tmV, kp, grid, s);        \
-        case 3: return persistent ? launch_attention<F, 0b10010010, true>(tmQ, tmK, tmV, kp, grid, s)          \
-                                  : launch_attention<F, 0b10010010, false>(tmQ, tmK, tmV, kp, grid, s);        \
-        default: return persistent ? launch_attention<F, 0, true>(tmQ, tmK, tmV, kp, grid, s)                  \
-                                   : launch_attention<F, 0, false>(tmQ, tmK, tmV, kp, grid, s);                \
+        case 1: B200SD_ATTN_LAUNCH(F, 0b10101010)                                                             \
+        case 2: B200SD_ATTN_LAUNCH(F, 0b10001000)                                                             \
+        case 3: B200SD_ATTN_LAUNCH(F, 0b10010010)                                                             \
+        default: B200SD_ATTN_LAUNCH(F, 0)                                                                     \
     }
     if (p->dtype == B200SD_F16) {
         B200SD_ATTN_DISPATCH(true)
     }
     B200SD_ATTN_DISPATCH(false)
+#undef B200SD_ATTN_LAUNCH
 #undef B200SD_ATTN_DISPATCH
 }

@@ -340,7 +340,7 @@ __global__ void embed_tokens_kernel(const int* __restrict__ ids, const float* __
 // one thread per 8 consecutive k of one output pixel
 __global__ void im2col3x3_kernel(const void* __restrict__ x, int dt, int n_img, int n_src, int in_h, int in_w,
                                  int cin, int stride, int out_h, int out_w, int k_pad, void* __restrict__ out,
-                                 int out_f16) {
+                                 int out_f16, int pad_lo) {
     pdl_sync();
     const int kchunks = k_pad >> 3;
     const long long total = (long long)n_img * out_h * out_w * kchunks;
@@ -356,7 +356,7 @@ __global__ void im2col3x3_kernel(const void* __restrict__ x, int dt, int n_img, 
         const int k0 = kc << 3;
         if ((cin & 7) == 0) {
             const int tap = k0 / cin, c = k0 - tap * cin;
-            const int iy = oy * stride + tap / 3 - 1, ix = ox * stride + tap % 3 - 1;
+            const int iy = oy * stride + tap / 3 - pad_lo, ix = ox * stride + tap % 3 - pad_lo;
             if (tap < 9 && iy >= 0 && iy < in_h && ix >= 0 && ix < in_w) {
                 const size_t p = src + ((size_t)iy * in_w + ix) * cin + c;
                 const float4 a = load4(x, p, dt), b = load4(x, p + 4, dt);
@@ -370,7 +370,7 @@ __global__ void im2col3x3_kernel(const void* __restrict__ x, int dt, int n_img, 
             for (int j = 0; j < 8; ++j) {
                 const int k = k0 + j;
                 const int tap = k / cin, c = k - tap * cin;
-                const int iy = oy * stride + tap / 3 - 1, ix = ox * stride + tap % 3 - 1;
+                const int iy = oy * stride + tap / 3 - pad_lo, ix = ox * stride + tap % 3 - pad_lo;
                 float t = 0.f;
                 if (tap < 9 && iy >= 0 && iy < in_h && ix >= 0 && ix < in_w)
                     t = load1(x, src + ((size_t)iy * in_w + ix) * cin + c, dt);
@@ -726,11 +726,13 @@ extern "C" int32_t b200sd_im2col3x3(const b200sd_im2col_params* p, b200sd_stream
     B200SD_CHECK_ARG(p->n_src > 0 && p->n_img > 0, "im2col: bad batch");
     B200SD_CHECK_ARG(ANY_DTYPE(p->in_dtype) && H_DTYPE(p->out_dtype), "im2col: bad in_dtype / out_dtype");
     B200SD_CHECK_ARG(ALIGNED16(p->x) && ALIGNED16(p->out), "im2col: pointers must be 16-byte aligned");
-    const int out_h = (p->in_h + 2 - 3) / p->stride + 1, out_w = (p->in_w + 2 - 3) / p->stride + 1;
+    B200SD_CHECK_ARG(p->pad_lo == 0 || p->pad_lo == 1, "im2col: pad_lo must be 0 or 1");
+    B200SD_CHECK_ARG(p->in_h + p->pad_lo >= 2 && p->in_w + p->pad_lo >= 2, "im2col: image smaller than the filter");
+    const int out_h = (p->in_h + p->pad_lo + 1 - 3) / p->stride + 1, out_w = (p->in_w + p->pad_lo + 1 - 3) / p->stride + 1;
     const long long total = (long long)p->n_img * out_h * out_w * (p->k_pad / 8);
     B200SD_LAUNCH("im2col3x3_kernel", im2col3x3_kernel, dim3(ew_grid(total, 256)), dim3(256), 0, as_stream(stream), 
         p->x, p->in_dtype, p->n_img, p->n_src, p->in_h, p->in_w, p->cin, p->stride, out_h, out_w, p->k_pad, p->out,
-        p->out_dtype == B200SD_F16);
+        p->out_dtype == B200SD_F16, p->pad_lo);
     count_launch();
     B200SD_CHECK_LAUNCH("im2col3x3");
     return B200SD_OK;

@@ -173,6 +173,49 @@ def test_full_size_vae_decode_512(cuda, lib_built):
     assert err <= 1e-2 and p >= PSNR_MIN
 
 
+# ------------------------------------------------------------------------------------------------ VAE encoder (8f rank 4)
+@pytest.mark.parametrize("size,real", [(64, False), (96, False), (256, True)])
+def test_vae_encoder_moments_vs_oracle(cuda, lib_built, size, real):
+    """AutoencoderKL.encode: moments (mean | logvar) of B200VAEEncoder vs the oracle restatement -- toy widths at 64^2 and
+    96^2, SD2.1 widths at 256^2 (image sides are multiples of 64 in every SD2.1 use: the mid block's token count must be
+    a multiple of 8 for the GEMM-form attention); quant_conv
+    is folded into conv_out on the GPU side and separate in the oracle."""
+    import b200sd
+    cfg = O.VAEConfig() if real else O.tiny_vae_config()
+    oe = O.seeded_init_(O.VAEEncoder(cfg), 5).eval()
+    g = torch.Generator("cpu").manual_seed(77)
+    img = torch.rand(2, 3, size, size, generator=g) * 2 - 1
+    with torch.no_grad():
+        ref = oe.encode(img)
+    ge = b200sd.B200VAEEncoder(oe.state_dict(), cfg, cuda)
+    with torch.no_grad():
+        out = ge(img.to(cuda)).float().cpu()
+    err = O.rel_l2(out, ref)
+    print(f"VAE encoder {size}^2 ({'SD2.1' if real else 'toy'} widths) moments rel L2 {err:.3e}")
+    assert out.shape == ref.shape == (2, 2 * cfg.latent_channels, size // 8, size // 8)
+    assert err <= 1e-2
+    noise = torch.randn(ref.shape[0], cfg.latent_channels, size // 8, size // 8, generator=g)
+    z = ge.encode_latents(img.to(cuda), noise).cpu()
+    assert O.rel_l2(z, cfg.scaling_factor * O.gaussian_sample(ref, noise)) <= 1e-2
+    assert torch.equal(ge.encode_latents(img.to(cuda)).cpu(), cfg.scaling_factor * out[:, :cfg.latent_channels])
+
+
+def test_vae_encode_then_decode_round_trip_matches_the_oracle(cuda, lib_built):
+    """img2img's two ends through the GPU path: decode(mode(encode(x))) against the same composition in the oracle"""
+    import b200sd
+    cfg = O.tiny_vae_config()
+    oe = O.seeded_init_(O.VAEEncoder(cfg), 5).eval()
+    od = O.seeded_init_(O.VAEDecoder(cfg), 1).eval()
+    img = torch.rand(1, 3, 64, 64, generator=torch.Generator("cpu").manual_seed(3)) * 2 - 1
+    with torch.no_grad():
+        ref = od.decode(O.gaussian_sample(oe.encode(img)))
+    ge, gd = b200sd.B200VAEEncoder(oe.state_dict(), cfg, cuda), b200sd.B200VAEDecoder(od.state_dict(), cfg, cuda)
+    with torch.no_grad():
+        z = ge.encode_latents(img.to(cuda)) / cfg.scaling_factor
+        out = gd(z).float().cpu()
+    assert O.rel_l2(out, ref) <= 1e-2
+
+
 # ------------------------------------------------------------------------------------------------ text encoder (8f rank 1)
 def _clip_rel(a, b):
     return ((a.float().cpu() - b.float().cpu()).norm() / b.float().cpu().norm()).item()

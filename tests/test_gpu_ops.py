@@ -2,10 +2,14 @@
 fp32 references of the same op on the same 16-bit-rounded inputs.  Every test that takes `K` runs twice: with fp16
 and with bf16 tensor-core operands.  Tolerances are stated per test."""
 import math
+import os
+from pathlib import Path
 
 import pytest
 import torch
 import torch.nn.functional as F
+
+ROOT = Path(__file__).resolve().parent.parent
 
 pytestmark = pytest.mark.gpu
 BF, FH = torch.bfloat16, torch.float16
@@ -212,6 +216,15 @@ def test_im2col_conv_in_and_stride2(K, cuda):
     unf = F.unfold(x.permute(0, 3, 1, 2), 3, padding=1, stride=2)
     ref = unf.view(2, 64, 9, 144).permute(0, 3, 2, 1).reshape(2, 12, 12, 576)
     assert torch.equal(c2, ref.to(dt))
+    # the VAE encoder's Downsample2D(padding=0): pad (0,1,0,1), then 3x3 stride 2 without padding
+    c3 = K.im2col(x, 2, 2, 9 * 64, pad_lo=0)
+    unf = F.unfold(F.pad(x.permute(0, 3, 1, 2), (0, 1, 0, 1)), 3, padding=0, stride=2)
+    ref = unf.view(2, 64, 9, 144).permute(0, 3, 2, 1).reshape(2, 12, 12, 576)
+    assert c3.shape == ref.shape and torch.equal(c3, ref.to(dt))
+    odd = rnd(1, 9, 9, 8, dev=cuda, seed=3)   # odd sizes: (9 + 1 - 3) // 2 + 1 = 4
+    c4 = K.im2col(odd, 1, 2, 72, pad_lo=0)
+    unf = F.unfold(F.pad(odd.permute(0, 3, 1, 2), (0, 1, 0, 1)), 3, padding=0, stride=2)
+    assert torch.equal(c4, unf.view(1, 8, 9, 16).permute(0, 3, 2, 1).reshape(1, 4, 4, 72).to(dt))
 
 
 def test_upsample2x(K, cuda):
@@ -338,6 +351,46 @@ def test_flash_attention_large_logits_rescale(K, cuda):
     qf, kf, vf = (t.float().view(1, s, heads, 64).transpose(1, 2) for t in (q, k, v))
     ref = (torch.softmax(qf @ kf.transpose(-1, -2) * 0.5, -1) @ vf).transpose(1, 2).reshape(s, c)
     assert rel(out, ref) < 2 * out_tol(dt)
+
+
+@pytest.mark.parametrize("env", [{"B200SD_ATTN_LAYOUT": "1"}, {"B200SD_ATTN_PAIR_BAR": "0"},
+                                 {"B200SD_ATTN_LAYOUT": "1", "B200SD_ATTN_EXP_EMU": "0", "B200SD_ATTN_STAGGER": "0"}])
+def test_flash_attention_other_kernel_switches(cuda, lib_built, env):
+    """the attention kernel's non-default variants (quad-row softmax layout, tile-wide row-max barrier, no polynomial
+    exponentials, no stagger) read their switches once per process, so they are exercised in a child process: self-,
+    cross- (ragged kv tile, persistent CTAs) and causal attention, fp16 and bf16, against explicit softmax"""
+    import subprocess
+    import sys
+    code = r"""
+import sys, torch
+sys.path[:0] = [%r, %r]
+import b200sd
+from b200sd.layers import Kernels
+dev = torch.device('cuda:0')
+worst = 0.0
+for dt in (torch.float16, torch.bfloat16):
+    K = Kernels(dev, torch.float32, dt)
+    for batch, heads, sq, skv, causal in [(2, 2, 576, 576, False), (1, 5, 1024, 1024, False), (3, 4, 320, 77, False),
+                                          (2, 2, 300, 300, True), (32, 20, 144, 77, False), (1, 1, 4, 4, False)]:
+        g = torch.Generator('cpu').manual_seed(sq + skv)
+        c = heads * 64
+        q = torch.randn(batch * sq, c, generator=g).to(dev).to(dt)
+        k = torch.randn(batch * skv, c, generator=g).to(dev).to(dt)
+        v = torch.randn(batch * skv, c, generator=g).to(dev).to(dt)
+        out = K.attention(q, k, v, batch, heads, sq, skv, 0.125, causal=causal)
+        qf, kf, vf = (t.float().view(batch, -1, heads, 64).transpose(1, 2) for t in (q, k, v))
+        sc = qf @ kf.transpose(-1, -2) * 0.125
+        if causal:
+            sc = sc.masked_fill(torch.ones(sq, skv, device=dev).triu(1).bool(), float('-inf'))
+        ref = (torch.softmax(sc, -1) @ vf).transpose(1, 2).reshape(batch * sq, c)
+        err = ((out.float() - ref).norm() / ref.norm()).item()
+        tol = 2 * (6e-4 if dt == torch.float16 else 4e-3)
+        assert err < tol, (dt, batch, heads, sq, skv, causal, err)
+        worst = max(worst, err)
+print('ok', worst)
+""" % (str(ROOT), str(ROOT / "scalable-hw-agnostic-inference_b200"))
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, **env), capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and r.stdout.strip().startswith("ok"), r.stdout[-2000:] + r.stderr[-4000:]
 
 
 # ------------------------------------------------------------------------------------------------ text-encoder ops
