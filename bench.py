@@ -552,11 +552,16 @@ def run_patch_parallel(args):
     for _ in range(max(args.warmup, 1)):
         one()
     torch.cuda.synchronize()
+    # accounting pass, eager: a graph replay re-issues the captured launches and NCCL calls without passing through the
+    # Python counters
+    saved = (pipe.use_cuda_graph, pipe._graph)
+    pipe.use_cuda_graph, pipe._graph = False, None
     n0, comm.bytes_gathered, comm.bytes_halo, comm.n_allreduce = ops.launch_count(), 0, 0, 0
     one()
     torch.cuda.synchronize()
     launches = ops.launch_count() - n0
     gathered, halo, n_ar = comm.bytes_gathered, comm.bytes_halo, comm.n_allreduce
+    pipe.use_cuda_graph, pipe._graph = saved
     clocks = ClockSampler(local)
     dist.barrier()
     torch.cuda.synchronize()
@@ -607,6 +612,7 @@ def run_patch_parallel(args):
                 "whole_image_tensor_roofline_frac": round(value * tflop_img / (world * pk["tflops"]), 4) if tflop_img else None,
                 "gpu_launches": int(launches * args.steps), "clocks": clk}
         _emit(line)
+    pipe.release()   # the captured step holds NCCL kernels: drop it before the group goes away
     dist.barrier()
     dist.destroy_process_group()
 

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200SD_ABI_VERSION 6
+#define B200SD_ABI_VERSION 7
 
 typedef struct CUstream_st* b200sd_stream_t; /* == cudaStream_t / CUstream */
 
@@ -96,6 +96,12 @@ typedef struct {
                                still in registers (b200sd_gn_tile_sums reduces it); NULL = off */
     int32_t rows_per_image; /* only with tile_sums on a plain [M, K] problem (img_h == 1, n_img == 1): rows of `out`
                                that belong to one image; must be a multiple of 128.  0 for NHWC problems. */
+    int32_t conv_stride;    /* taps == 9 only.  0 or 1: stride 1.  2: Downsample2D's stride-2 convolution, read straight from
+                               the NHWC input by a TMA box that takes every second pixel (no im2col copy).  img_h / img_w
+                               stay the INPUT size; `out`, `residual`, `tile_sums` have the output size
+                               out_h = (img_h + pad_before + 1 - 3) / stride + 1 (likewise out_w). */
+    int32_t conv_pad_mode;  /* 0: Conv2d(padding=1), one zero row / column before and after.  1: nothing before, one after
+                               -- the VAE encoder's Downsample2D(padding=0): F.pad(x, (0,1,0,1)) then no padding. */
 } b200sd_gemm_params;
 int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stream);
 /* slices per image that `tile_sums` would hold for this problem, or 0 if this problem cannot emit them (a tile that

@@ -7,7 +7,7 @@ from pathlib import Path
 
 _HERE = Path(__file__).resolve().parent
 LIB_PATH = _HERE / "libb200sd.so"
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 BF16, F32, F16 = 1, 2, 3
 
@@ -20,7 +20,8 @@ class GemmParams(C.Structure):
                 ("bias_along_m", c_i32), ("row_bias", c_vp), ("row_bias_stride", c_i64), ("residual", c_vp),
                 ("residual_dtype", c_i32), ("ld_res", c_i64), ("out", c_vp), ("out_dtype", c_i32), ("ld_out", c_i64),
                 ("geglu", c_i32), ("block_n", c_i32), ("workspace", c_vp), ("workspace_bytes", c_i64),
-                ("split_k", c_i32), ("act", c_i32), ("tile_sums", c_vp), ("rows_per_image", c_i32)]
+                ("split_k", c_i32), ("act", c_i32), ("tile_sums", c_vp), ("rows_per_image", c_i32),
+                ("conv_stride", c_i32), ("conv_pad_mode", c_i32)]
 
 
 class AttentionParams(C.Structure):

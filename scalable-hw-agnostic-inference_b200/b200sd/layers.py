@@ -131,23 +131,38 @@ class Kernels:
         return y
 
     def conv3x3(self, a: torch.Tensor, w: torch.Tensor, bias, *, row_bias=None, residual=None,
-                out_dtype=None, gn_next: bool = False) -> torch.Tensor:
-        """a 16-bit NHWC, w packed [Cout, 9*Cin]; stride 1, pad 1.  gn_next: the output feeds a GroupNorm -- have the
-        epilogue emit its column sums (when this problem's tiling allows it) and attach them to the result."""
+                out_dtype=None, gn_next: bool = False, stride: int = 1, pad_mode: int = 0) -> torch.Tensor:
+        """a 16-bit NHWC, w packed [Cout, 9*Cin].  stride 1 or 2 (Downsample2D: the TMA box takes every second pixel, no
+        im2col copy); pad_mode 0 = Conv2d(padding=1), 1 = pad (0,1,0,1) and no padding (the VAE encoder's Downsample2D).
+        gn_next: the output feeds a GroupNorm -- have the epilogue emit its column sums (when this problem's tiling
+        allows it) and attach them to the result."""
+        if a.dtype != self.op_dtype:
+            # a trunk tensor fed straight to a convolution (Downsample2D) while the trunk is kept in another format than the
+            # tensor-core operands (B200SD_TRUNK_DTYPE=fp32 / bf16 with fp16 operands): one conversion pass
+            a16 = torch.empty(a.shape, device=self.device, dtype=self.op_dtype)
+            ops.cast(a.contiguous(), a16)
+            a = a16
         n, h, wd, cin = a.shape
         cout = w.shape[0]
-        out = torch.empty(n, h, wd, cout, device=self.device, dtype=out_dtype or self.trunk_dtype)
+        pad_lo = 0 if pad_mode == 1 else 1
+        oh, ow = ((h + pad_lo - 2) // stride + 1, (wd + pad_lo - 2) // stride + 1) if (stride == 2 or pad_mode) else (h, wd)
+        out = torch.empty(n, oh, ow, cout, device=self.device, dtype=out_dtype or self.trunk_dtype)
         rb_stride = 0
         if row_bias is not None and row_bias.shape[0] > 1:
             rb_stride = row_bias.stride(0)
         res2 = residual.view(-1, cout) if residual is not None else None
         args = (a, n, h, wd, cin, 9, w, bias, False, row_bias, rb_stride, res2, out.view(-1, cout), False, 0)
-        ts = self._tile_sums_buffer(args, n, cout) if gn_next else None
+        conv = {"conv_stride": stride, "conv_pad_mode": pad_mode}
+        ts = None
+        if gn_next and self.fuse_gn_stats:
+            parts = ops.gemm_tile_sum_parts(*args, **conv)
+            if parts > 0:
+                ts = torch.empty(n, parts, cout, 2, device=self.device, dtype=torch.float32)
         if ts is not None:
-            ops.gemm(*args, None, 1, 0, ts, 0)
+            ops.gemm(*args, None, 1, 0, ts, 0, stride, pad_mode)
             out._b200_tile_sums = ts
         else:
-            ops.gemm(*args, self.gemm_ws, 0)
+            ops.gemm(*args, self.gemm_ws, 0, 0, None, 0, stride, pad_mode)
         return out
 
     def linear(self, a: torch.Tensor, w: torch.Tensor, bias, *, residual=None, out_dtype=None, geglu=False,

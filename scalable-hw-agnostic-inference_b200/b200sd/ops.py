@@ -104,7 +104,8 @@ def _nbytes(*ts) -> float:
 
 # ------------------------------------------------------------------------------------------------ impls
 def _gemm_params(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, row_bias_stride, residual, out,
-                 geglu, block_n, workspace=None, split_k=0, act=0, tile_sums=None, rows_per_image=0):
+                 geglu, block_n, workspace=None, split_k=0, act=0, tile_sums=None, rows_per_image=0, conv_stride=1,
+                 conv_pad_mode=0):
     p = L.GemmParams()
     p.a, p.a_dtype, p.n_img, p.img_h, p.img_w, p.cin, p.taps = _ptr(a), _dt(a), n_img, img_h, img_w, cin, taps
     p.w, p.w_dtype, p.n_out = _ptr(w), _dt(w), w.shape[0]
@@ -115,6 +116,7 @@ def _gemm_params(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_b
         p.residual, p.residual_dtype, p.ld_res = _ptr(residual), _dt(residual), residual.stride(-2)
     p.out, p.out_dtype, p.ld_out = _ptr(out), _dt(out), out.stride(-2)
     p.geglu, p.block_n, p.split_k, p.act = int(geglu), block_n, split_k, act
+    p.conv_stride, p.conv_pad_mode = conv_stride, conv_pad_mode
     if workspace is not None:
         p.workspace, p.workspace_bytes = _ptr(workspace), workspace.numel() * workspace.element_size()
     if tile_sums is not None:
@@ -123,19 +125,20 @@ def _gemm_params(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_b
     return p
 
 
-def gemm_tile_sum_parts(*args, rows_per_image=0) -> int:
+def gemm_tile_sum_parts(*args, rows_per_image=0, conv_stride=1, conv_pad_mode=0) -> int:
     """slices per image of the column-sum table this problem's epilogue can emit for the next GroupNorm (0 = it cannot);
     same arguments as `gemm`"""
     p = _gemm_params(*args)
-    p.rows_per_image = rows_per_image
+    p.rows_per_image, p.conv_stride, p.conv_pad_mode = rows_per_image, conv_stride, conv_pad_mode
     return int(L.load().b200sd_gemm_tile_sum_parts(C.byref(p)))
 
 
 def _gemm(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, row_bias_stride, residual, out,
-          geglu, block_n, workspace=None, split_k=0, act=0, tile_sums=None, rows_per_image=0):
+          geglu, block_n, workspace=None, split_k=0, act=0, tile_sums=None, rows_per_image=0, conv_stride=1,
+          conv_pad_mode=0):
     p = _gemm_params(a, n_img, img_h, img_w, cin, taps, w, bias, bias_along_m, row_bias, row_bias_stride, residual, out,
-                     geglu, block_n, workspace, split_k, act, tile_sums, rows_per_image)
-    m = n_img * img_h * img_w
+                     geglu, block_n, workspace, split_k, act, tile_sums, rows_per_image, conv_stride, conv_pad_mode)
+    m = out.numel() // out.shape[-1] if conv_stride == 2 else n_img * img_h * img_w
     _run("gemm", 2.0 * m * w.shape[0] * taps * cin, L.load().b200sd_gemm, p,
          f"M{m} N{w.shape[0]} K{taps * cin} taps{taps} img{n_img}x{img_h}x{img_w}{' geglu' if geglu else ''}")
 
@@ -277,7 +280,8 @@ def umma_selftest(a: torch.Tensor, b: torch.Tensor, b_mn_major: bool) -> torch.T
 _SCHEMAS = {
     "gemm": ("(Tensor a, int n_img, int img_h, int img_w, int cin, int taps, Tensor w, Tensor? bias, bool bias_along_m, "
              "Tensor? row_bias, int row_bias_stride, Tensor? residual, Tensor(a!) out, bool geglu, int block_n, "
-             "Tensor(b!)? workspace=None, int split_k=0, int act=0, Tensor(c!)? tile_sums=None, int rows_per_image=0) -> ()",
+             "Tensor(b!)? workspace=None, int split_k=0, int act=0, Tensor(c!)? tile_sums=None, int rows_per_image=0, "
+             "int conv_stride=1, int conv_pad_mode=0) -> ()",
              _gemm),
     "attention": ("(Tensor q, Tensor k, Tensor v, Tensor(a!) out, int batch, int heads, int sq, int skv, float scale, "
                   "bool causal=False) -> ()", _attention),

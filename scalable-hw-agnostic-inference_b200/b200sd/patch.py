@@ -150,13 +150,12 @@ class PatchParallelUNet:
 
     def _conv3x3_stride2(self, a, w, bias):
         """Downsample2D: output row R reads input rows 2R-1..2R+1, i.e. rows 2i..2i+2 of the halo-extended band, and input
-        columns 2x-1..2x+1, i.e. columns 2x..2x+2 after one zero column is put in front: im2col with pad_lo = 0."""
-        K = self.K
+        columns 2x-1..2x+1, i.e. columns 2x..2x+2 after one zero column is put in front: the conv kernel's stride-2 form
+        with pad_mode 1 (nothing before, one zero row / column after).  The last output row lies past the band."""
         n, r, wd, c = a.shape
         ap = self.comm.halo_pad(a, left_pad=1)
-        cols = K.im2col(ap, n, 2, 9 * c, pad_lo=0)          # [n, r/2 + 1, wd/2, 9c]; the last row is past the band
-        cols = cols[:, : r // 2].contiguous()
-        return K.linear(cols, w, bias)
+        out = self.K.conv3x3(ap, w, bias, stride=2, pad_mode=1)      # [n, r/2 + 1, wd/2, cout]
+        return out[:, : r // 2].contiguous()
 
     def _conv_in(self, latent_band, n_img: int):
         K, u = self.K, self.unet
@@ -189,12 +188,14 @@ class PatchParallelUNet:
         # K|V of the local rows first, so that their gather is in flight while Q is projected
         kv_local = K.linear(ln, T.qkv_w[c:], None, out_dtype=BF)                     # [m, 2c]
         cur = torch.cuda.current_stream()
+        # [n, S, 2c] in local memory; allocated on the compute stream (which joins the side stream before the buffer is
+        # read or freed), filled on the side stream
+        kv_all = torch.empty(n, comm.world * s_local, 2 * c, device=K.device, dtype=BF)
         self._side.wait_stream(cur)
         with torch.cuda.stream(self._side):
-            kv_all = comm.all_gather_rows(kv_local.view(n, s_local, 2 * c))          # [n, S, 2c] in local memory
+            comm.all_gather_rows(kv_local.view(n, s_local, 2 * c), out=kv_all)
         q = K.linear(ln, T.qkv_w[:c], None, out_dtype=BF)
         cur.wait_stream(self._side)
-        kv_all.record_stream(cur)
         kv2 = kv_all.view(n * comm.world * s_local, 2 * c)
         o = K.attention(q, kv2[:, :c], kv2[:, c:], n, T.heads, s_local, comm.world * s_local, 0.125)
         t = K.linear(o, T.o1_w, T.o1_b, residual=t, out=t)
@@ -204,7 +205,10 @@ class PatchParallelUNet:
         t = K.linear(o, T.o2_w, T.o2_b, residual=t, out=t)
         ln = K.layernorm(t, *T.ln[2])
         g = K.linear(ln, T.ff1_w, T.ff1_b, out_dtype=BF, geglu=True, block_n=T.ff_block_n)
-        t2 = K.linear(g, T.ff2_w, T.ff2_b, residual=t, out_dtype=BF)
+        # (in place on the token stream when it is already in the operand format: the epilogue then adds its chunk to it
+        # by a TMA reduce instead of reading it)
+        t2 = K.linear(g, T.ff2_w, T.ff2_b, residual=t, out=t) if t.dtype == BF else \
+            K.linear(g, T.ff2_w, T.ff2_b, residual=t, out_dtype=BF)
         xr = x.view(m, c)
         return K.linear(t2, T.pout_w, T.pout_b, residual=xr, out=xr).view(n, r, w, c)
 
@@ -252,15 +256,36 @@ class PatchParallelPipeline:
     """One image (or a small batch) denoised by all ranks together: every rank calls this with the SAME latents and
     embeddings; each denoises its band (UNet band forward + the fused CFG / scheduler kernel on the band), the final
     latent bands are all-gathered and every rank decodes the whole image (the VAE decode is 5 % of an image; it is not
-    split).  No CUDA graph here: the step contains NCCL calls on two streams."""
+    split).  The step -- ~900 kernel launches, ~140 NCCL calls on two streams, the halo copies -- is captured into ONE CUDA
+    graph per rank and replayed for every step (timestep and step index live in device memory, as in B200Pipeline);
+    eager, the step is bound by the host's launch rate, not by the GPUs."""
 
-    def __init__(self, unet, vae_decoder, scheduler, comm: BandComm, guidance_scale: float = 7.5):
+    def __init__(self, unet, vae_decoder, scheduler, comm: BandComm, guidance_scale: float = 7.5,
+                 use_cuda_graph: Optional[bool] = None):
+        import os
+
         from .pipeline import B200Pipeline
         self.comm = comm
         self.pp_unet = PatchParallelUNet(unet, comm)
         self.unet, self.scheduler, self.guidance_scale = unet, scheduler, guidance_scale
         self._single = B200Pipeline(unet, vae_decoder, scheduler, use_cuda_graph=False)
+        self.use_cuda_graph = (os.environ.get("B200SD_PP_GRAPH", "1") != "0") if use_cuda_graph is None else use_cuda_graph
         self.step_ms: List[float] = []
+        self._key, self._st, self._graph = None, None, None
+
+    def release(self) -> None:
+        """drops the captured step.  Call it before the process group is destroyed: a CUDA graph that holds captured
+        NCCL kernels keeps their communicators busy, and tearing the group down underneath it does not return."""
+        self._graph, self._st, self._key = None, None, None
+        torch.cuda.synchronize()
+
+    def _step_body(self, st) -> None:
+        sch = self.scheduler
+        x_in = st["x"]
+        if sch.kind == "euler":
+            x_in = st["x"] * st["in_scale"].index_select(0, st["step_idx"].long()).view(1, 1, 1, 1)
+        eps2 = self.pp_unet.forward_band(x_in, 2 * st["B"], st["t"], st["ctx_kv"], st["ctx_len"])
+        sch.step_cfg(eps2, st["step_idx"], st["x"], st["x0_prev"], self.guidance_scale)
 
     @torch.no_grad()
     def denoise(self, latents_nhwc: torch.Tensor, ctx2: torch.Tensor, steps: int, time_steps: bool = False) -> torch.Tensor:
@@ -269,27 +294,64 @@ class PatchParallelPipeline:
         B, h, w, _ = latents_nhwc.shape
         r0, rows = comm.band(h)
         sch.set_timesteps(steps, dev)
-        sch.coef_table(self.guidance_scale)
-        x = latents_nhwc[:, r0:r0 + rows].to(dev, torch.float32).contiguous()
+        coef = sch.coef_table(self.guidance_scale)
+        key = (B, h, w, steps, sch.kind, tuple(ctx2.shape), coef.data_ptr())
+        if self._key != key:
+            self._st = {"B": B, "ctx_len": ctx2.shape[1],
+                        "x": torch.zeros(B, rows, w, 4, device=dev, dtype=torch.float32),
+                        "x0_prev": torch.zeros(B, rows, w, 4, device=dev, dtype=torch.float32) if sch.needs_x0_prev else None,
+                        "t": torch.zeros(1, device=dev, dtype=torch.float32),
+                        "step_idx": torch.zeros(1, device=dev, dtype=torch.int32)}
+            self._key, self._graph = key, None
+        st = self._st
+        st["x"].copy_(latents_nhwc[:, r0:r0 + rows].to(dev, torch.float32))
         if sch.init_noise_sigma != 1.0:
-            x.mul_(sch.init_noise_sigma)
-        x0_prev = torch.zeros_like(x) if sch.needs_x0_prev else None
-        ctx_kv = self.unet.project_context(ctx2.to(dev))
+            st["x"].mul_(sch.init_noise_sigma)
+        if st["x0_prev"] is not None:
+            st["x0_prev"].zero_()
+        kv = self.unet.project_context(ctx2.to(dev))
+        if "ctx_kv" in st:
+            for dst, src in zip(st["ctx_kv"], kv):
+                dst.copy_(src)
+        else:
+            st["ctx_kv"] = kv
         t_table = sch.timesteps.to(torch.float32)
-        in_scale = torch.tensor(sch._in_scale, dtype=torch.float32, device=dev)
+        idx_table = torch.arange(steps, device=dev, dtype=torch.int32)
+        st["in_scale"] = torch.tensor(sch._in_scale, dtype=torch.float32, device=dev)
+        if self.use_cuda_graph and self._graph is None:
+            # one eager step on a side stream (lazy initialisation, NCCL communicators for every peer), then the capture;
+            # every rank does the same, in the same order
+            st["t"].copy_(t_table[0:1]); st["step_idx"].copy_(idx_table[0:1])
+            keep = st["x"].clone()
+            s = torch.cuda.Stream(device=dev)
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                self._step_body(st)
+            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=s, capture_error_mode="thread_local"):
+                self._step_body(st)
+            self._graph = graph
+            st["x"].copy_(keep)
+            if st["x0_prev"] is not None:
+                st["x0_prev"].zero_()
         self.step_ms = []
         for i in range(steps):
             if time_steps:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
-            x_in = x * in_scale[i] if sch.kind == "euler" else x
-            eps2 = self.pp_unet.forward_band(x_in, 2 * B, t_table[i:i + 1], ctx_kv, ctx2.shape[1])
-            sch.step_cfg(eps2, torch.full((1,), i, device=dev, dtype=torch.int32), x, x0_prev, self.guidance_scale)
+            st["t"].copy_(t_table[i:i + 1], non_blocking=True)
+            st["step_idx"].copy_(idx_table[i:i + 1], non_blocking=True)
+            if self._graph is not None:
+                self._graph.replay()
+            else:
+                self._step_body(st)
             if time_steps:
                 e1.record()
                 e1.synchronize()
                 self.step_ms.append(e0.elapsed_time(e1))
-        return comm.all_gather_bands(x)
+        return comm.all_gather_bands(st["x"])
 
     @torch.no_grad()
     def __call__(self, prompt_embeds: torch.Tensor, negative_prompt_embeds: torch.Tensor, latents: torch.Tensor,

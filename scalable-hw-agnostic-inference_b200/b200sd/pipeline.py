@@ -127,7 +127,9 @@ class B200Pipeline:
             graph = torch.cuda.CUDAGraph()
             # capture on a stream of THIS pipeline's device: torch.cuda.graph's default capture stream is created once per
             # process, on whichever device was current then, and entering it would switch a second replica to that device
-            with torch.cuda.graph(graph, stream=s):
+            # (thread_local: replicas of other GPUs run in other threads of this process and may allocate or synchronise
+            # while this one captures)
+            with torch.cuda.graph(graph, stream=s, capture_error_mode="thread_local"):
                 self._step_body(st)
             self._graph = graph
             st["x"].copy_(keep)

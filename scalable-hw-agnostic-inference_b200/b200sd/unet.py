@@ -170,7 +170,10 @@ class B200UNet(torch.nn.Module):
         t = K.linear(o, T.o2_w, T.o2_b, residual=t, out=t)
         ln = K.layernorm(t, *T.ln[2])
         g = K.linear(ln, T.ff1_w, T.ff1_b, out_dtype=BF, geglu=True, block_n=T.ff_block_n)
-        t2 = K.linear(g, T.ff2_w, T.ff2_b, residual=t, out_dtype=BF)
+        # (in place on the token stream when it is already in the operand format: the epilogue then adds its chunk to it
+        # by a TMA reduce instead of reading it)
+        t2 = K.linear(g, T.ff2_w, T.ff2_b, residual=t, out=t) if t.dtype == BF else \
+            K.linear(g, T.ff2_w, T.ff2_b, residual=t, out_dtype=BF)
         # in place on the block's input (nothing else reads it): an fp32 residual that is also the output is added by a TMA
         # reduce in L2 instead of being read by the epilogue
         # (the block's output is normalised next -- by the following resnet's norm1, possibly after a detour through the
@@ -201,9 +204,7 @@ class B200UNet(torch.nn.Module):
                 skips.append(h)
             if blk["down"] is not None:
                 w, b = blk["down"]
-                c = h.shape[-1]
-                cols = K.im2col(h, h.shape[0], 2, 9 * c)
-                h = K.linear(cols, w, b, gn_rows_per_image=cols.shape[1] * cols.shape[2])
+                h = K.conv3x3(h, w, b, stride=2, gn_next=True)   # Downsample2D: 3x3, stride 2, padding 1
                 skips.append(h)
         h = run_resnet(K, self.mid_res[0], h, None, eps, table)
         h = self._transformer(self.mid_attn, h, ctx_kv[kv_i], ctx_len)

@@ -151,7 +151,7 @@ class B200VAEEncoder(torch.nn.Module):
     """Drop-in for `pipe.vae.encoder` (+ `pipe.vae.quant_conv`): AutoencoderKL.encode of the img2img pipelines
     (the reference loads the whole AutoencoderKL at app/run-sd.py:107).  Same kernels as the decoder:
     GroupNorm+SiLU, implicit-GEMM conv3x3, the mid-block attention; the three Downsample2D(padding=0) convolutions --
-    pad (0,1,0,1), then 3x3 stride 2 -- go through im2col with `pad_lo = 0`.  The 1x1 quant_conv is folded exactly into
+    pad (0,1,0,1), then 3x3 stride 2 -- are the conv kernel's stride-2 / pad_mode 1 form.  The 1x1 quant_conv is folded exactly into
     conv_out (it follows it with nothing in between).  Returns the moments cat(mean, logvar)."""
 
     def __init__(self, state_dict: Dict[str, torch.Tensor], config=None, device="cuda", trunk_dtype=None, op_dtype=None,
@@ -211,9 +211,7 @@ class B200VAEEncoder(torch.nn.Module):
                 h = run_resnet(K, R, h, None, 1e-6, None)
             if blk["down"] is not None:
                 w, b = blk["down"]
-                c = h.shape[-1]
-                cols = K.im2col(h, h.shape[0], 2, 9 * c, pad_lo=0)
-                h = K.linear(cols, w, b, gn_rows_per_image=cols.shape[1] * cols.shape[2])
+                h = K.conv3x3(h, w, b, stride=2, pad_mode=1, gn_next=True)  # pad (0,1,0,1), 3x3 stride 2, no padding
         h = run_resnet(K, self.mid_res[0], h, None, 1e-6, None)
         h = self.mid_attn(K, h)
         h = run_resnet(K, self.mid_res[1], h, None, 1e-6, None)

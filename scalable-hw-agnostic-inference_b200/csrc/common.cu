@@ -61,7 +61,7 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 int32_t encode_tmap_bf16(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
-                         const uint64_t* strides_bytes, const uint32_t* box) {
+                         const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* elem_strides) {
     EncodeTiledFn fn = get_encode_fn();
     if (!fn) return set_error(B200SD_ERR_DEVICE, "cuTensorMapEncodeTiled not available from the driver");
     cuuint64_t gdim[5];
@@ -71,7 +71,7 @@ int32_t encode_tmap_bf16(CUtensorMap* map, const void* base, int rank, const uin
     for (int i = 0; i < rank; ++i) {
         gdim[i] = dims[i];
         bx[i] = box[i];
-        es[i] = 1;
+        es[i] = elem_strides ? elem_strides[i] : 1;
         if (i > 0) gstr[i - 1] = strides_bytes[i - 1];
     }
     CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx,
@@ -92,14 +92,18 @@ int32_t encode_tmap_bf16(CUtensorMap* map, const void* base, int rank, const uin
 // 2-D row-major tensor [rows][cols] of 2- or 4-byte elements, box = box_cols x box_rows, swizzle 64 or 128 bytes
 // (= box_cols * elem_bytes).  Used for the GEMM epilogue's TMA stores.
 int32_t encode_tmap_2d(CUtensorMap* map, const void* base, int elem_bytes, uint64_t cols, uint64_t rows,
-                       uint64_t row_stride_bytes, uint32_t box_cols, uint32_t box_rows, int swizzle_bytes) {
+                       uint64_t row_stride_bytes, uint32_t box_cols, uint32_t box_rows, int swizzle_bytes, int dtype) {
     EncodeTiledFn fn = get_encode_fn();
     if (!fn) return set_error(B200SD_ERR_DEVICE, "cuTensorMapEncodeTiled not available from the driver");
     cuuint64_t gdim[2] = {cols, rows};
     cuuint64_t gstr[1] = {row_stride_bytes};
     cuuint32_t bx[2] = {box_cols, box_rows};
     cuuint32_t es[2] = {1, 1};
-    CUresult r = fn(map, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT16, 2,
+    // a TMA reduce-add does arithmetic on the elements, so 16-bit maps name their floating-point format
+    const CUtensorMapDataType dt = elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                   : dtype == B200SD_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                   : dtype == B200SD_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_UINT16;
+    CUresult r = fn(map, dt, 2,
                     const_cast<void*>(base), gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                     swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
                     CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

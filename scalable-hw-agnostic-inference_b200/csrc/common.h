@@ -16,10 +16,12 @@ int num_sms();
 
 // Encode a bf16 tiled tensor map with SWIZZLE_128B (inner box = 64 elements = 128 bytes).
 // dims/strides innermost first; strides[i] is the byte stride of dim i+1 (dim 0 is contiguous).
+// elem_strides (optional): traversal stride per dimension -- a box of extent b with stride s delivers ceil(b / s) elements.
 int32_t encode_tmap_bf16(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
-                         const uint64_t* strides_bytes, const uint32_t* box);
+                         const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* elem_strides = nullptr);
 int32_t encode_tmap_2d(CUtensorMap* map, const void* base, int elem_bytes, uint64_t cols, uint64_t rows,
-                       uint64_t row_stride_bytes, uint32_t box_cols, uint32_t box_rows, int swizzle_bytes);
+                       uint64_t row_stride_bytes, uint32_t box_cols, uint32_t box_rows, int swizzle_bytes,
+                       int dtype = -1);  // dtype: b200sd_dtype of 2-byte elements (needed by reduce-adds), -1 = opaque
 
 #define B200SD_CHECK_ARG(cond, ...)                                  \
     do {                                                             \

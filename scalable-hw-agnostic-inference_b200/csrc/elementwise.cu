@@ -227,8 +227,47 @@ __global__ void gn_reduce_splits_kernel(const float* __restrict__ partial, int s
 
 // Per-(image, group) sums from the column sums a producing GEMM's epilogue left behind (gemm.cu, staged_store):
 // t[n][part][c] = (sum, sum of squares) of column c over one 32-row slice of a tile.  One CTA per (group, image);
-// thread i adds the elements i, i + 128, ... of its group's [parts x channels-per-group] block in order, then the 128
+// every thread adds a fixed subset of its group's [parts x channels-per-group] block in a fixed order, then the 128
 // per-thread sums are added by a fixed tree: the result does not depend on scheduling.
+//
+// gn_tile_block_sum adds the [parts x w] block of (sum, sum of squares) pairs at `base` (row stride `ld` pairs) into (a, b): thread i of 128
+// walks a fixed set of elements in a fixed order.  Even widths go two channels (one 16-byte load) at a time, four rows in
+// flight per thread: the table was written a moment ago by the producing GEMM and sits in L2, so the loop is bound by
+// load latency, not bandwidth.
+__device__ __forceinline__ void gn_tile_block_sum(const float2* __restrict__ base, int parts, int w, int ld, float& a,
+                                                  float& b) {
+    if ((w & 1) == 0 && (ld & 1) == 0 && (reinterpret_cast<uintptr_t>(base) & 15) == 0) {
+        const int wp = w >> 1;
+        const int rows = 128 / wp;  // rows covered per pass (w <= 256)
+        const int r0 = threadIdx.x / wp, cp = threadIdx.x - r0 * wp;
+        if (rows == 0 || r0 >= rows) {
+            if (rows != 0) return;
+        } else {
+            const float4* src = reinterpret_cast<const float4*>(base + 2 * cp);
+            const size_t ld4 = (size_t)ld >> 1;
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, b0 = 0.f, b1 = 0.f, b2 = 0.f, b3 = 0.f;
+            int part = r0;
+            for (; part + 3 * rows < parts; part += 4 * rows) {
+                const float4 v0 = src[(size_t)part * ld4], v1 = src[(size_t)(part + rows) * ld4];
+                const float4 v2 = src[(size_t)(part + 2 * rows) * ld4], v3 = src[(size_t)(part + 3 * rows) * ld4];
+                a0 += v0.x + v0.z, b0 += v0.y + v0.w, a1 += v1.x + v1.z, b1 += v1.y + v1.w;
+                a2 += v2.x + v2.z, b2 += v2.y + v2.w, a3 += v3.x + v3.z, b3 += v3.y + v3.w;
+            }
+            for (; part < parts; part += rows) {
+                const float4 v0 = src[(size_t)part * ld4];
+                a0 += v0.x + v0.z, b0 += v0.y + v0.w;
+            }
+            a += (a0 + a1) + (a2 + a3), b += (b0 + b1) + (b2 + b3);
+            return;
+        }
+    }
+    for (int i = threadIdx.x; i < parts * w; i += 128) {
+        const int part = i / w, c = i - part * w;
+        const float2 v = base[(size_t)part * ld + c];
+        a += v.x, b += v.y;
+    }
+}
+
 __global__ void __launch_bounds__(128)
     gn_tile_sums_kernel(const float2* __restrict__ t1, int parts1, int c1, const float2* __restrict__ t2, int parts2,
                         int c2, int groups, float* __restrict__ out) {
@@ -240,25 +279,9 @@ __global__ void __launch_bounds__(128)
     float a = 0.f, b = 0.f;
     // channels [ch0, ch1) of the concatenation: [ch0, min(ch1, c1)) from the first producer, the rest from the second
     const int e1 = min(ch1, c1);
-    if (ch0 < e1) {
-        const int w = e1 - ch0;
-        const float2* base = t1 + (size_t)n * parts1 * c1 + ch0;
-        for (int i = threadIdx.x; i < parts1 * w; i += 128) {
-            const int part = i / w, c = i - part * w;
-            const float2 v = base[(size_t)part * c1 + c];
-            a += v.x, b += v.y;
-        }
-    }
+    if (ch0 < e1) gn_tile_block_sum(t1 + (size_t)n * parts1 * c1 + ch0, parts1, e1 - ch0, c1, a, b);
     const int b2 = max(ch0, c1);
-    if (b2 < ch1) {
-        const int w = ch1 - b2;
-        const float2* base = t2 + (size_t)n * parts2 * c2 + (b2 - c1);
-        for (int i = threadIdx.x; i < parts2 * w; i += 128) {
-            const int part = i / w, c = i - part * w;
-            const float2 v = base[(size_t)part * c2 + c];
-            a += v.x, b += v.y;
-        }
-    }
+    if (b2 < ch1) gn_tile_block_sum(t2 + (size_t)n * parts2 * c2 + (b2 - c1), parts2, ch1 - b2, c2, a, b);
     sa[threadIdx.x] = a, sb[threadIdx.x] = b;
     __syncthreads();
     for (int o = 64; o > 0; o >>= 1) {

@@ -35,7 +35,8 @@ constexpr int AUTO_SPLIT_MAX_M_TILES = 4;  // ... and at most 512 output rows
 constexpr int WS_COUNTERS = 1024;  // int32 tile counters at the start of the split-K workspace
 
 struct GemmKernelParams {
-    int n_img, img_h, img_w, cin, taps;
+    int n_img, img_h, img_w, cin, taps;  // img_h / img_w: the OUTPUT feature map (= the input's for stride 1)
+    int conv_stride, pad_lo;             // input pixel of output pixel x and tap s: x * conv_stride + s - pad_lo
     int a_bf16, b_bf16;  // operand formats for the instruction descriptor (0 = fp16, 1 = bf16)
     int bw, bh, bn;
     int tiles_x, tiles_y, m_tiles, n_tiles, kb_per_tap;
@@ -57,7 +58,7 @@ struct GemmKernelParams {
     int geglu;
     int act;       // 1: erf-GELU on (acc + bias), before the residual
     int fast_epi;  // 1: outputs leave through the per-warp staging tile as full 128-byte row segments
-    int tma_reduce;  // 1: (with tma_epi) out IS the fp32 residual: the chunk is added to it by a TMA reduce, no residual read
+    int tma_reduce;  // 1: (with tma_epi) out IS the residual (same dtype): the chunk is added to it by a TMA reduce, no residual read
     int tma_epi;   // 1: (linear layout, no residual) the staging tile is written in the output dtype, row per thread, and
                    //    leaves with one TMA store per 32x32 chunk: no shared-memory read-back on the epilogue's chain
     float2* tile_sums;  // (staged epilogue only) [m_tile * 4 + lane quadrant][n_out] (sum, sum of squares) of the stored
@@ -502,10 +503,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
             for (int kb = kb0; kb < kb1; ++kb) {
                 const int tap = kb / p.kb_per_tap;
                 const int c0 = (kb - tap * p.kb_per_tap) * BLOCK_K;
-                int dx = 0, dy = 0;
+                // first input pixel of the box for this tap: x0 * stride + s - pad_lo (stride 2: the tensor map's element
+                // strides make the box take every second pixel from there)
+                int dx = x0, dy = y0;
                 if (p.taps == 9) {
-                    dy = tap / 3 - 1;
-                    dx = tap - (tap / 3) * 3 - 1;
+                    dy = y0 * p.conv_stride + tap / 3 - p.pad_lo;
+                    dx = x0 * p.conv_stride + tap - (tap / 3) * 3 - p.pad_lo;
                 }
                 mbar_wait(&empty_bar[stage], phase ^ 1);
                 uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
@@ -514,12 +517,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                     if (PAIR) {
                         // both CTAs' bytes are counted on the leader's barrier; each CTA brings its half of the weight rows
                         if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * (p.a_box_bytes + Cfg::B_TILE_BYTES));
-                        tma_load_4d_pair(sa, &tmA, &full_bar[stage], c0, x0 + dx, y0 + dy, n0);
+                        tma_load_4d_pair(sa, &tmA, &full_bar[stage], c0, dx, dy, n0);
                         tma_load_2d_pair(sb, &tmB, &full_bar[stage], tap * p.cin + c0,
                                          n_tile * BLOCK_N + rank * (n_this_of(n_tile) >> 1));
                     } else {
                         mbar_expect_tx(&full_bar[stage], p.a_box_bytes + Cfg::B_TILE_BYTES);
-                        tma_load_4d(sa, &tmA, &full_bar[stage], c0, x0 + dx, y0 + dy, n0);
+                        tma_load_4d(sa, &tmA, &full_bar[stage], c0, dx, dy, n0);
                         tma_load_2d(sb, &tmB, &full_bar[stage], tap * p.cin + c0, n_tile * BLOCK_N);
                     }
                 }
@@ -1035,10 +1038,22 @@ static int32_t make_plan(const b200sd_gemm_params* p, bool have_ws, GemmPlan* pl
     B200SD_CHECK_ARG(p->cin % 8 == 0, "gemm: cin (%d) must be a multiple of 8", p->cin);
     GemmKernelParams& kp = plan->kp;
     kp = GemmKernelParams{};
-    kp.n_img = p->n_img, kp.img_h = p->img_h, kp.img_w = p->img_w, kp.cin = p->cin, kp.taps = p->taps;
-    choose_box(p->n_img, p->img_h, p->img_w, &kp.bw, &kp.bh, &kp.bn);
-    kp.tiles_x = (p->img_w + kp.bw - 1) / kp.bw;
-    kp.tiles_y = (p->img_h + kp.bh - 1) / kp.bh;
+    B200SD_CHECK_ARG(p->conv_stride >= 0 && p->conv_stride <= 2 && (p->conv_pad_mode == 0 || p->conv_pad_mode == 1),
+                     "gemm: conv_stride %d / conv_pad_mode %d", p->conv_stride, p->conv_pad_mode);
+    B200SD_CHECK_ARG((p->conv_stride <= 1 && p->conv_pad_mode == 0) || p->taps == 9,
+                     "gemm: conv_stride / conv_pad_mode apply to 3x3 convolutions only");
+    kp.conv_stride = p->conv_stride == 2 ? 2 : 1;
+    kp.pad_lo = p->conv_pad_mode == 1 ? 0 : 1;
+    int out_h = p->img_h, out_w = p->img_w;
+    if (p->taps == 9 && (kp.conv_stride == 2 || kp.pad_lo == 0)) {
+        B200SD_CHECK_ARG(p->img_h + kp.pad_lo >= 2 && p->img_w + kp.pad_lo >= 2, "gemm: image smaller than the filter");
+        out_h = (p->img_h + kp.pad_lo + 1 - 3) / kp.conv_stride + 1;
+        out_w = (p->img_w + kp.pad_lo + 1 - 3) / kp.conv_stride + 1;
+    }
+    kp.n_img = p->n_img, kp.img_h = out_h, kp.img_w = out_w, kp.cin = p->cin, kp.taps = p->taps;
+    choose_box(p->n_img, out_h, out_w, &kp.bw, &kp.bh, &kp.bn);
+    kp.tiles_x = (out_w + kp.bw - 1) / kp.bw;
+    kp.tiles_y = (out_h + kp.bh - 1) / kp.bh;
     const int tiles_n = (p->n_img + kp.bn - 1) / kp.bn;
     kp.m_tiles = kp.tiles_x * kp.tiles_y * tiles_n;
     kp.kb_per_tap = (p->cin + BLOCK_K - 1) / BLOCK_K;
@@ -1180,8 +1195,11 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
         // An fp32 residual that IS the output (h += linear(x), the transformer's projections back onto the trunk) needs no
         // residual read at all: the chunk (acc + bias) is added to it in L2 by a TMA reduce -- same fp32 sum, same order.
         static const bool red_off = getenv("B200SD_GEMM_NO_TMA_REDUCE") != nullptr;
-        const bool inplace32 = p->residual == p->out && p->ld_res == p->ld_out && p->out_dtype == B200SD_F32 &&
-                               p->residual_dtype == B200SD_F32 && !p->act && !red_off;
+        // The same holds for a 16-bit trunk (the default): the chunk is rounded to the trunk's format and added to it in
+        // L2 -- two roundings (chunk, then sum) where the read path has one; B200SD_GEMM_NO_TMA_REDUCE16 keeps the read path.
+        static const bool red16_off = getenv("B200SD_GEMM_NO_TMA_REDUCE16") != nullptr;
+        const bool inplace32 = p->residual == p->out && p->ld_res == p->ld_out && p->residual_dtype == p->out_dtype &&
+                               (p->out_dtype == B200SD_F32 || !red16_off) && !p->act && !red_off;
         // (column sums are taken in the staged epilogue's transposed read-back, so they rule the TMA store out)
         kp.tma_epi = (kp.fast_epi && !tma_off && (!p->residual || inplace32) && kp.splits == 1 && p->taps == 1 &&
                       p->img_h == 1 && p->n_img == 1 && (p->ld_out * osz) % 16 == 0 && !p->tile_sums) ? 1 : 0;
@@ -1200,8 +1218,12 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
         const uint64_t c = (uint64_t)p->cin;
         uint64_t dims[4] = {c, (uint64_t)p->img_w, (uint64_t)p->img_h, (uint64_t)p->n_img};
         uint64_t strides[3] = {c * 2, c * 2 * p->img_w, c * 2 * p->img_w * p->img_h};
-        uint32_t box[4] = {BLOCK_K, (uint32_t)kp.bw, (uint32_t)kp.bh, (uint32_t)kp.bn};
-        int32_t r = encode_tmap_bf16(&tmA, p->a, 4, dims, strides, box);
+        // stride 2: the box spans 2 * bw x 2 * bh input pixels and the element strides keep every second one, so the
+        // shared-memory tile is the same dense [bn x bh x bw pixels] x 64 channels as for stride 1
+        const uint32_t cs = (uint32_t)kp.conv_stride;
+        uint32_t box[4] = {BLOCK_K, (uint32_t)kp.bw * cs, (uint32_t)kp.bh * cs, (uint32_t)kp.bn};
+        uint32_t estr[4] = {1, cs, cs, 1};
+        int32_t r = encode_tmap_bf16(&tmA, p->a, 4, dims, strides, box, estr);
         if (r) return r;
     }
     {
@@ -1216,7 +1238,7 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
     if (kp.tma_epi) {
         const int osz = p->out_dtype == B200SD_F32 ? 4 : 2;
         int32_t r = encode_tmap_2d(&tmOut, p->out, osz, (uint64_t)n_cols, (uint64_t)p->img_w,
-                                   (uint64_t)p->ld_out * osz, 32, 32, osz == 4 ? 128 : 64);
+                                   (uint64_t)p->ld_out * osz, 32, 32, osz == 4 ? 128 : 64, p->out_dtype);
         if (r) return r;
     }
     cudaStream_t s = as_stream(stream);

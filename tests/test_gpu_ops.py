@@ -121,7 +121,8 @@ def test_linear_residual_inplace_and_bias_along_m(K, cuda, res_dtype):
     ref = a.float() @ w.float().t() + bias + res.float()
     t = res.clone()
     K.linear(a, w, bias, residual=t, out=t)  # aliasing out == residual
-    assert rel(t, ref) < (2e-5 if res_dtype == torch.float32 else out_tol(res_dtype))
+    # 16-bit in place: the chunk is rounded to the residual's format and added to it in L2 by a TMA reduce -- two roundings
+    assert rel(t, ref) < (2e-5 if res_dtype == torch.float32 else 1.5 * out_tol(res_dtype))
     bm = rnd(m, dev=cuda, seed=5)
     out = K.linear(a, w, bm, out_dtype=torch.float32, bias_along_m=True)
     assert rel(out, a.float() @ w.float().t() + bm[:, None]) < 2e-5
@@ -156,6 +157,38 @@ def test_conv3x3_implicit_gemm(K, cuda, n, h, w, cin, cout):
     out = K.conv3x3(x, pack_conv3x3(wt, dt), bias, out_dtype=torch.float32)
     ref = F.conv2d(x.float().permute(0, 3, 1, 2), wt.to(dt).float(), bias, padding=1).permute(0, 2, 3, 1)
     assert out.shape == ref.shape and rel(out, ref) < 2e-5
+
+
+@pytest.mark.parametrize("pad_mode", [0, 1])
+@pytest.mark.parametrize("n,h,w,cin,cout", [
+    (2, 96, 96, 64, 64), (2, 48, 48, 128, 160), (4, 24, 24, 64, 128), (32, 24, 24, 128, 128), (3, 10, 14, 64, 96),
+    (2, 9, 9, 64, 64), (1, 2, 2, 64, 64), (2, 192, 192, 64, 64), (6, 48, 48, 320, 320)])
+def test_conv3x3_stride2_without_im2col(K, cuda, n, h, w, cin, cout, pad_mode):
+    """Downsample2D through the conv kernel's stride-2 form (TMA box with element strides 2 in x and y):
+    pad_mode 0 = Conv2d(3, stride=2, padding=1) of the UNet; pad_mode 1 = F.pad(x, (0,1,0,1)) + Conv2d(3, stride=2,
+    padding=0) of the VAE encoder.  Even, odd and tiny sizes, multi-image pixel boxes (24x24 at 32 images), and the
+    producer-side GroupNorm column sums."""
+    from b200sd import ops
+    from b200sd.layers import pack_conv3x3, tile_sums_of
+    dt = K.op_dtype
+    x = rnd(n, h, w, cin, dev=cuda, seed=1, dtype=dt)
+    wt = rnd(cout, cin, 3, 3, dev=cuda, seed=2, scale=(9 * cin) ** -0.5)
+    bias = rnd(cout, dev=cuda, seed=3)
+    xin = x.float().permute(0, 3, 1, 2)
+    if pad_mode == 1:
+        ref = F.conv2d(F.pad(xin, (0, 1, 0, 1)), wt.to(dt).float(), bias, stride=2)
+    else:
+        ref = F.conv2d(xin, wt.to(dt).float(), bias, stride=2, padding=1)
+    ref = ref.permute(0, 2, 3, 1)
+    out = K.conv3x3(x, pack_conv3x3(wt, dt), bias, out_dtype=torch.float32, stride=2, pad_mode=pad_mode, gn_next=True)
+    assert out.shape == ref.shape and rel(out, ref) < 2e-5
+    ts = tile_sums_of(out)
+    if ts is not None and cout % 32 == 0:   # the column sums describe the stored values
+        sums = torch.empty(n, 32, 2, device=cuda)
+        ops.gn_tile_sums(ts, None, n, 32, sums)
+        g = out.view(n, -1, 32, cout // 32)
+        want = torch.stack([g.sum(dim=(1, 3)), (g * g).sum(dim=(1, 3))], dim=-1)
+        assert rel(sums, want) < 1e-4
 
 
 def test_conv3x3_temb_rowbias_and_residual(K, cuda):

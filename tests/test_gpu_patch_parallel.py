@@ -69,6 +69,7 @@ def _worker(rank: int, world: int, port: int, out_dir: str, real_widths: bool):
                     height=8 * hw, width=8 * hw, output_type="uint8").images
         res["image_psnr"] = O.psnr(img_pp.float().cpu() / 255.0, img_1.float().cpu() / 255.0)
         res["image_shape"] = tuple(img_pp.shape)
+        ppl.release()
     torch.cuda.synchronize()
     torch.save(res, os.path.join(out_dir, f"pp{rank}.pt"))
     dist.barrier()
