@@ -4,13 +4,18 @@
 // All are coalesced, 8/16-byte vectorised, grid sized in multiples of the SM count where the shape allows.
 // Element types are selected at run time by a dtype code (warp-uniform branch; these kernels are bandwidth-bound).
 // Algorithmic bytes per element are listed per kernel in DESIGN.md section 4.
+#include <cstdlib>
+
 #include "common.h"
 #include "ptx.cuh"
 
 namespace b200sd {
 using namespace ptx;
 
-__device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)); }
+// x * sigmoid(x) with the approximate reciprocal (MUFU.RCP, ~1 ulp): the IEEE division's range-handling slow path was a
+// third of gn_apply's instructions (ncu: issue slots 64 % busy, XU 59 %, in a kernel that should only wait for HBM).
+// 1 + exp(-x) overflows to +inf only for x < -88, where the quotient is the correct limit 0.
+__device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
 
 // ---- 4-wide loads/stores; idx counts elements ---------------------------------------------------------------
 __device__ __forceinline__ float4 load4(const void* base, size_t idx, int dt) {
@@ -121,11 +126,17 @@ __global__ void gn_stats_kernel(const void* __restrict__ x1, int c1, const void*
     }
 }
 
-template <int VEC>
-__global__ void gn_apply_kernel(const void* __restrict__ x1, int c1, const void* __restrict__ x2, int c2, int dt,
+// The element formats and the activation are template parameters: selected at run time per element, every load carried
+// both 16-bit decodings plus a select and every store both encodings (ncu on the level-0 shape: 64 % of the issue slots
+// busy in a kernel that should only wait for HBM).
+template <int VEC, int DT, bool OF16, bool SILU>
+__global__ void gn_apply_kernel(const void* __restrict__ x1, int c1, const void* __restrict__ x2, int c2,
                                 int hw, int groups, int splits, const float* __restrict__ partial, float eps,
-                                const float* __restrict__ gamma, const float* __restrict__ beta, int silu,
-                                void* __restrict__ y, void* __restrict__ raw, int out_f16, int chunks, float stat_hw) {
+                                const float* __restrict__ gamma, const float* __restrict__ beta,
+                                void* __restrict__ y, void* __restrict__ raw, int chunks, float stat_hw) {
+    constexpr int dt = DT;
+    constexpr bool silu = SILU;
+    constexpr int out_f16 = OF16 ? 1 : 0;
     pdl_sync();
     __shared__ float s_mean[64], s_rstd[64];
     const int C = c1 + c2;
@@ -293,10 +304,12 @@ __global__ void __launch_bounds__(128)
 
 // =============================================================================================== LayerNorm
 // one warp per row, whole row held in registers (cols <= 1536): exact two-pass mean / variance.
-template <int MAXV>
-__global__ void layernorm_kernel(const void* __restrict__ x, int dt, long long rows, int cols, float eps,
+template <int MAXV, int DT, bool OF16>
+__global__ void layernorm_kernel(const void* __restrict__ x, long long rows, int cols, float eps,
                                  const float* __restrict__ gamma, const float* __restrict__ beta,
-                                 void* __restrict__ y, int out_f16) {
+                                 void* __restrict__ y) {
+    constexpr int dt = DT;          // formats fixed at compile time (see gn_apply_kernel): the generic version spent 81 % of
+    constexpr int out_f16 = OF16;   // its issue slots, most of them on decoding both 16-bit formats per element
     pdl_sync();
     const int lane = threadIdx.x & 31;
     const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -652,13 +665,31 @@ static int32_t gn_launch(const b200sd_groupnorm_params* p, int splits, float* sc
         const float* part = stats ? scratch : p->sums;
         const int nsplit = stats ? splits : 1;
         const float stat_hw = (float)((!stats && p->stat_hw > 0) ? p->stat_hw : (int64_t)p->hw);
-        if (vec8) {
-            B200SD_LAUNCH("gn_apply_kernel", (gn_apply_kernel<8>), g2, dim3(threads), 0, s, p->x1, p->c1, p->x2, c2, dt, p->hw,
-                          p->groups, nsplit, part, p->eps, p->gamma, p->beta, p->silu, p->y, p->raw, f16, chunks, stat_hw);
-        } else {
-            B200SD_LAUNCH("gn_apply_kernel", (gn_apply_kernel<4>), g2, dim3(threads), 0, s, p->x1, p->c1, p->x2, c2, dt, p->hw,
-                          p->groups, nsplit, part, p->eps, p->gamma, p->beta, p->silu, p->y, p->raw, f16, chunks, stat_hw);
-        }
+#define B200SD_GN_APPLY(V, D, O, S)                                                                                       \
+    B200SD_LAUNCH("gn_apply_kernel", (gn_apply_kernel<V, D, O, S>), g2, dim3(threads), 0, s, p->x1, p->c1, p->x2, c2, p->hw, \
+                  p->groups, nsplit, part, p->eps, p->gamma, p->beta, p->y, p->raw, chunks, stat_hw)
+#define B200SD_GN_APPLY_S(V, D, O)                                      \
+    do {                                                                \
+        if (p->silu) B200SD_GN_APPLY(V, D, O, true);                    \
+        else B200SD_GN_APPLY(V, D, O, false);                           \
+    } while (0)
+#define B200SD_GN_APPLY_O(V, D)                                         \
+    do {                                                                \
+        if (f16) B200SD_GN_APPLY_S(V, D, true);                         \
+        else B200SD_GN_APPLY_S(V, D, false);                            \
+    } while (0)
+#define B200SD_GN_APPLY_D(V)                                            \
+    do {                                                                \
+        if (dt == B200SD_F32) B200SD_GN_APPLY_O(V, B200SD_F32);         \
+        else if (dt == B200SD_F16) B200SD_GN_APPLY_O(V, B200SD_F16);    \
+        else B200SD_GN_APPLY_O(V, B200SD_BF16);                         \
+    } while (0)
+        if (vec8) B200SD_GN_APPLY_D(8);
+        else B200SD_GN_APPLY_D(4);
+#undef B200SD_GN_APPLY_D
+#undef B200SD_GN_APPLY_O
+#undef B200SD_GN_APPLY_S
+#undef B200SD_GN_APPLY
         ++launches;
     }
     count_launch(launches);
@@ -729,13 +760,26 @@ extern "C" int32_t b200sd_layernorm(const b200sd_layernorm_params* p, b200sd_str
     const unsigned grid = (unsigned)((p->rows + wpb - 1) / wpb);
     // registers per thread follow the row length (4 * MAXV floats), so short rows run at full occupancy
     const int nv = (p->cols / 4 + 31) / 32;
-#define B200SD_LN_LAUNCH(MV)                                                                                       \
-    B200SD_LAUNCH("layernorm_kernel", (layernorm_kernel<MV>), dim3(grid), dim3(wpb * 32), 0, as_stream(stream), p->x, p->in_dtype, p->rows, p->cols, p->eps,   \
-                                                                  p->gamma, p->beta, p->y, p->out_dtype == B200SD_F16)
+#define B200SD_LN_LAUNCH_T(MV, D, O)                                                                                 \
+    B200SD_LAUNCH("layernorm_kernel", (layernorm_kernel<MV, D, O>), dim3(grid), dim3(wpb * 32), 0, as_stream(stream), p->x, p->rows, \
+                  p->cols, p->eps, p->gamma, p->beta, p->y)
+#define B200SD_LN_LAUNCH_O(MV, D)                                                     \
+    do {                                                                              \
+        if (p->out_dtype == B200SD_F16) B200SD_LN_LAUNCH_T(MV, D, true);              \
+        else B200SD_LN_LAUNCH_T(MV, D, false);                                        \
+    } while (0)
+#define B200SD_LN_LAUNCH(MV)                                                          \
+    do {                                                                              \
+        if (p->in_dtype == B200SD_F32) B200SD_LN_LAUNCH_O(MV, B200SD_F32);            \
+        else if (p->in_dtype == B200SD_F16) B200SD_LN_LAUNCH_O(MV, B200SD_F16);       \
+        else B200SD_LN_LAUNCH_O(MV, B200SD_BF16);                                     \
+    } while (0)
     if (nv <= 3) B200SD_LN_LAUNCH(3);
     else if (nv <= 5) B200SD_LN_LAUNCH(5);
     else if (nv <= 10) B200SD_LN_LAUNCH(10);
     else B200SD_LN_LAUNCH(12);
+#undef B200SD_LN_LAUNCH_T
+#undef B200SD_LN_LAUNCH_O
 #undef B200SD_LN_LAUNCH
     count_launch();
     B200SD_CHECK_LAUNCH("layernorm");

@@ -61,6 +61,8 @@ struct GemmKernelParams {
     int tma_reduce;  // 1: (with tma_epi) out IS the residual (same dtype): the chunk is added to it by a TMA reduce, no residual read
     int tma_epi;   // 1: (linear layout, no residual) the staging tile is written in the output dtype, row per thread, and
                    //    leaves with one TMA store per 32x32 chunk: no shared-memory read-back on the epilogue's chain
+    int res_prefetch;   // 1: the producer warp asks the tile's residual rows into L2 ahead of the epilogue (one bulk prefetch
+                        //    per row, issued lane by lane)
     float2* tile_sums;  // (staged epilogue only) [m_tile * 4 + lane quadrant][n_out] (sum, sum of squares) of the stored
                         // values over the quadrant's valid rows: the next GroupNorm's statistics, or nullptr
 };
@@ -466,7 +468,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         uint32_t phase = 0;
         const int res_esz = p.res_dtype == B200SD_F32 ? 4 : 2;
         const bool res_l2_prefetch =
-            p.residual != nullptr && splits == 1 && !p.geglu &&
+            p.res_prefetch && p.residual != nullptr && splits == 1 && !p.geglu && !p.tma_reduce &&
             ((reinterpret_cast<uintptr_t>(p.residual) | (uintptr_t)(p.ld_res * res_esz)) & 15) == 0;
         for (int w = w_first; w < total_work; w += w_step) {
             const int t = w / splits, split = w - t * splits;
@@ -1205,6 +1207,8 @@ extern "C" int32_t b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream_t stre
                       p->img_h == 1 && p->n_img == 1 && (p->ld_out * osz) % 16 == 0 && !p->tile_sums) ? 1 : 0;
         kp.tile_sums = reinterpret_cast<float2*>(p->tile_sums);
         kp.tma_reduce = (kp.tma_epi && p->residual) ? 1 : 0;
+        static const bool res_pf = [] { const char* e = getenv("B200SD_GEMM_RES_PREFETCH"); return e && e[0] == '1'; }();
+        kp.res_prefetch = res_pf ? 1 : 0;
     }
     if (kp.splits > 1) {
         const long long tiles = (long long)kp.m_tiles * kp.n_tiles;

@@ -25,12 +25,18 @@ CASES = {  # name: (M, K, N, residual, geglu, out fp32)
     "ff2_320": (294912, 1280, 320, True, False, True),
     "ff2_320_out16": (294912, 1280, 320, True, False, False),   # fp32 residual, 16-bit output (the UNet's ff2)
     "res320_inplace": (294912, 320, 320, True, False, True),    # out is the residual: TMA reduce-add
+    "res320_16": (294912, 320, 320, True, False, False),        # 16-bit trunk: 16-bit residual and output (staged epilogue)
+    "res320_16_inplace": (294912, 320, 320, True, False, False),  # 16-bit trunk, out is the residual: 16-bit TMA reduce-add
+    "ff2_320_16_inplace": (294912, 1280, 320, True, False, False),
+    "res640_16": (73728, 640, 640, True, False, False),
 }
 M, Kd, N, has_res, geglu, out32 = CASES[case]
 a = torch.randn(M, Kd, device=dev).to(dt)
 w = (torch.randn(N, Kd, device=dev) / Kd ** 0.5).to(dt)
 bias = torch.randn(N, device=dev)
 res = torch.randn(M, N, device=dev) if has_res else None
+if res is not None and "_16" in case:
+    res = res.to(dt)
 n_cols = N // 2 if geglu else N
 out = torch.empty(M, n_cols, device=dev, dtype=torch.float32 if out32 else dt)
 if case.endswith("_inplace"):
@@ -57,5 +63,5 @@ for _ in range(reps):
 ts.sort()
 us = ts[len(ts) // 2]
 flops = 2.0 * M * N * Kd
-byts = a.numel() * 2 + out.numel() * out.element_size() + (res.numel() * 4 if has_res else 0)
+byts = a.numel() * 2 + out.numel() * out.element_size() + (res.numel() * res.element_size() if has_res else 0)
 print(f"{case}: M{M} N{N} K{Kd}  {us:8.1f} us  {flops / us / 1e6:7.1f} TF/s  {byts / us / 1e3:7.1f} GB/s (algorithmic)")
