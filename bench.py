@@ -562,6 +562,7 @@ def run_patch_parallel(args):
     launches = ops.launch_count() - n0
     gathered, halo, n_ar = comm.bytes_gathered, comm.bytes_halo, comm.n_allreduce
     pipe.use_cuda_graph, pipe._graph = saved
+    del saved   # (a second reference would keep the captured NCCL kernels alive past pipe.release())
     clocks = ClockSampler(local)
     dist.barrier()
     torch.cuda.synchronize()
