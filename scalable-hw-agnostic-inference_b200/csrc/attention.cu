@@ -664,7 +664,7 @@ static int emu_mask_from_env() {
     static int cached = -1;
     if (cached < 0) {
         const char* e = getenv("B200SD_ATTN_EXP_EMU");
-        cached = (e && e[0] >= '0' && e[0] <= '3') ? e[0] - '0' : 2;  // default: a quarter of the exponentials
+        cached = (e && e[0] >= '0' && e[0] <= '4') ? e[0] - '0' : 2;  // default: a quarter of the exponentials (4: an eighth)
     }
     return cached;
 }
@@ -736,6 +736,7 @@ extern "C" int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_str
         case 1: B200SD_ATTN_LAUNCH(F, 0b10101010)                                                             \
         case 2: B200SD_ATTN_LAUNCH(F, 0b10001000)                                                             \
         case 3: B200SD_ATTN_LAUNCH(F, 0b10010010)                                                             \
+        case 4: B200SD_ATTN_LAUNCH(F, 0b10000000)                                                             \
         default: B200SD_ATTN_LAUNCH(F, 0)                                                                     \
     }
     if (p->dtype == B200SD_F16) {

@@ -590,6 +590,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         const int eg = (warp - 2) >> 2;
         const int et = threadIdx.x - 64;  // 0..255 over the epilogue warps
         float* stg = reinterpret_cast<float*>(smem + Cfg::STG_OFF) + (warp - 2) * 1024;
+        // TMA-store epilogue with 16-bit outputs: a 32x32 chunk is 2 KiB, so the warp's 4 KiB staging region holds TWO
+        // tiles and the warp stages chunk c + 1 while the store of chunk c still reads the other one (with one tile the
+        // warp idled in bulk_wait_read for the whole store latency: 14 % of the samples of the level-0 QKV projection)
+        const bool stg2 = p.tma_epi != 0 && p.out_dtype != B200SD_F32;
+        int stg_sel = 0;
         const bool out32 = p.out_dtype == B200SD_F32;
         const bool fast = p.fast_epi != 0;
         const bool tma = p.tma_epi != 0;
@@ -746,9 +751,14 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 #pragma unroll
                                 for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
                             }
-                            if (lane == 0) bulk_wait_read0();  // the store that last read this staging tile let go of it
+                            float* stg_c = stg + (stg2 ? stg_sel * 512 : 0);
+                            stg_sel ^= 1;
+                            if (lane == 0) {  // the store that last read this staging tile let go of it
+                                if (stg2) bulk_wait_read1();
+                                else bulk_wait_read0();
+                            }
                             __syncwarp();
-                            stage_rows_out(p, stg, lane, v);
+                            stage_rows_out(p, stg_c, lane, v);
                             if (more) {
                                 tmem_ld_x32(t_addr + (c + 2) * 32, r);
                             } else {
@@ -761,8 +771,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                             if (lane == 0 && live) {
                                 // rows / columns past the edge are clipped; with tma_reduce the tile is added to the
                                 // residual that already sits in `out`
-                                if (p.tma_reduce) tma_reduce_add_2d(&tmOut, stg, col0, row0);
-                                else tma_store_2d(&tmOut, stg, col0, row0);
+                                if (p.tma_reduce) tma_reduce_add_2d(&tmOut, stg_c, col0, row0);
+                                else tma_store_2d(&tmOut, stg_c, col0, row0);
                                 bulk_commit();
                             }
                             continue;
@@ -836,13 +846,18 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                         }
                         const int col0 = n_tile * HALF + c * 32;
                         if (tma) {
-                            if (lane == 0) bulk_wait_read0();
+                            float* stg_c = stg + (stg2 ? stg_sel * 512 : 0);
+                            stg_sel ^= 1;
+                            if (lane == 0) {
+                                if (stg2) bulk_wait_read1();
+                                else bulk_wait_read0();
+                            }
                             __syncwarp();
-                            stage_rows_out(p, stg, lane, v);
+                            stage_rows_out(p, stg_c, lane, v);
                             fence_proxy_async_smem();
                             __syncwarp();
                             if (lane == 0 && row0 < p.img_w) {
-                                tma_store_2d(&tmOut, stg, col0, row0);
+                                tma_store_2d(&tmOut, stg_c, col0, row0);
                                 bulk_commit();
                             }
                         } else if (fast) {

@@ -29,6 +29,7 @@ CASES = {  # name: (M, K, N, residual, geglu, out fp32)
     "res320_16_inplace": (294912, 320, 320, True, False, False),  # 16-bit trunk, out is the residual: 16-bit TMA reduce-add
     "ff2_320_16_inplace": (294912, 1280, 320, True, False, False),
     "res640_16": (73728, 640, 640, True, False, False),
+    "qkv960": (294912, 320, 960, False, False, False),          # fused QKV projection of the 96x96 level
 }
 M, Kd, N, has_res, geglu, out32 = CASES[case]
 a = torch.randn(M, Kd, device=dev).to(dt)
