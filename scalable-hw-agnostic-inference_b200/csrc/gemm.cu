@@ -105,9 +105,12 @@ __device__ __forceinline__ float gelu_erf(float x) {
     return x * (x < 0.f ? e : 1.0f - e);
 }
 
-// GEGLU on two (value, gate) pairs at once, polynomial and products on packed fp32 (FFMA2 / FMUL2): ~10 issue slots per
-// output instead of ~17.  Same arithmetic as gelu_erf element by element.
-__device__ __forceinline__ void geglu_pair(float v0, float v1, float g0, float g1, float& o0, float& o1) {
+// GEGLU on two (value, gate) pairs at once, polynomial and products on packed fp32 (FFMA2 / FMUL2 / FADD2).
+// x * Phi(x) is formed as relu(x) - u * Phi(-u), u = min(|x|, 6): the same value as x * (x < 0 ? e : 1 - e) up to
+// |x| * Phi(-6) ~ 1e-9 |x|, without the compare + predicated subtract per element.  Same polynomial as gelu_erf.
+__device__ __forceinline__ void geglu_pair(uint64_t v2, uint64_t g2, float& o0, float& o1) {
+    float g0, g1;
+    unpack2(g2, g0, g1);
     const uint64_t u2 = pack2(fminf(fabsf(g0), 6.0f), fminf(fabsf(g1), 6.0f));
     uint64_t q2 = pack2(-1.889626233e-06f, -1.889626233e-06f);
     q2 = fma2(q2, u2, pack2(6.268140101e-05f, 6.268140101e-05f));
@@ -121,8 +124,9 @@ __device__ __forceinline__ void geglu_pair(float v0, float v1, float g0, float g
     unpack2(q2, q0, q1);
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(q0));
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(q1));
-    const uint64_t phi2 = pack2(g0 < 0.f ? e0 : 1.0f - e0, g1 < 0.f ? e1 : 1.0f - e1);
-    unpack2(mul2(mul2(pack2(g0, g1), phi2), pack2(v0, v1)), o0, o1);
+    // relu(g) - u * e, then times the value
+    const uint64_t gphi2 = fma2(u2, pack2(-e0, -e1), pack2(fmaxf(g0, 0.f), fmaxf(g1, 0.f)));
+    unpack2(mul2(gphi2, v2), o0, o1);
 }
 
 // Applies the epilogue to 32 consecutive output columns [col0, col0+32) of one row and stores them.
@@ -751,8 +755,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 #pragma unroll
                                 for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
                             }
+                            // (the tiles alternate per ISSUED store -- a chunk past the edge commits no bulk group, and
+                            // wait_group.read 1 only vouches for the store before the most recent one)
                             float* stg_c = stg + (stg2 ? stg_sel * 512 : 0);
-                            stg_sel ^= 1;
+                            if (live) stg_sel ^= 1;
                             if (lane == 0) {  // the store that last read this staging tile let go of it
                                 if (stg2) bulk_wait_read1();
                                 else bulk_wait_read0();
@@ -829,11 +835,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                         for (int j = 0; j < 8; ++j) {
                             const float4 bv = *reinterpret_cast<const float4*>(bs + c * 32 + 4 * j);
                             const float4 bg = *reinterpret_cast<const float4*>(bs + HALF + c * 32 + 4 * j);
-                            geglu_pair(__uint_as_float(rv[4 * j + 0]) + bv.x, __uint_as_float(rv[4 * j + 1]) + bv.y,
-                                       __uint_as_float(rg[4 * j + 0]) + bg.x, __uint_as_float(rg[4 * j + 1]) + bg.y,
+                            // bias adds on packed pairs as well (FADD2)
+                            geglu_pair(add2(pack2(__uint_as_float(rv[4 * j + 0]), __uint_as_float(rv[4 * j + 1])), pack2(bv.x, bv.y)),
+                                       add2(pack2(__uint_as_float(rg[4 * j + 0]), __uint_as_float(rg[4 * j + 1])), pack2(bg.x, bg.y)),
                                        v[4 * j + 0], v[4 * j + 1]);
-                            geglu_pair(__uint_as_float(rv[4 * j + 2]) + bv.z, __uint_as_float(rv[4 * j + 3]) + bv.w,
-                                       __uint_as_float(rg[4 * j + 2]) + bg.z, __uint_as_float(rg[4 * j + 3]) + bg.w,
+                            geglu_pair(add2(pack2(__uint_as_float(rv[4 * j + 2]), __uint_as_float(rv[4 * j + 3])), pack2(bv.z, bv.w)),
+                                       add2(pack2(__uint_as_float(rg[4 * j + 2]), __uint_as_float(rg[4 * j + 3])), pack2(bg.z, bg.w)),
                                        v[4 * j + 2], v[4 * j + 3]);
                         }
                         if (more) {
@@ -847,7 +854,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                         const int col0 = n_tile * HALF + c * 32;
                         if (tma) {
                             float* stg_c = stg + (stg2 ? stg_sel * 512 : 0);
-                            stg_sel ^= 1;
+                            if (row0 < p.img_w) stg_sel ^= 1;
                             if (lane == 0) {
                                 if (stg2) bulk_wait_read1();
                                 else bulk_wait_read0();
