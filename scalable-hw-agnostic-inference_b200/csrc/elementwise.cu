@@ -195,7 +195,11 @@ __global__ void gn_apply_kernel(const void* __restrict__ x1, int c1, const void*
         }
         storev_h<VEC>(y, o, r, f16);
     };
-    constexpr int U = VEC == 4 ? 4 : 2;
+#ifdef B200SD_GN_APPLY_U
+    constexpr int U = B200SD_GN_APPLY_U;
+#else
+    constexpr int U = 4;  // loads in flight per thread (16 bytes each with VEC = 8): 2 left the SM short of bytes in flight
+#endif
     int p = p0 + pl;
     for (; p + (U - 1) * lanes < p1; p += U * lanes) {
         float v[U][VEC];
@@ -304,46 +308,50 @@ __global__ void __launch_bounds__(128)
 
 // =============================================================================================== LayerNorm
 // one warp per row, whole row held in registers (cols <= 1536): exact two-pass mean / variance.
-template <int MAXV, int DT, bool OF16>
+// LW = lanes per row: 32 (a warp per row) or 16 (two rows per warp, for rows of at most 16 * 4 * MAXV columns: the 320
+// columns of the 96x96 level are 80 four-element vectors = 5 per lane of a half warp, where a full warp would idle half of
+// its lanes on the third vector)
+template <int MAXV, int DT, bool OF16, int LW>
 __global__ void layernorm_kernel(const void* __restrict__ x, long long rows, int cols, float eps,
                                  const float* __restrict__ gamma, const float* __restrict__ beta,
                                  void* __restrict__ y) {
     constexpr int dt = DT;          // formats fixed at compile time (see gn_apply_kernel): the generic version spent 81 % of
     constexpr int out_f16 = OF16;   // its issue slots, most of them on decoding both 16-bit formats per element
+    constexpr int RPW = 32 / LW;    // rows per warp
     pdl_sync();
-    const int lane = threadIdx.x & 31;
-    const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (row >= rows) return;
-    const int nvec = cols >> 2;
+    const int lane = threadIdx.x & (LW - 1);
+    const long long row = ((long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * RPW + ((threadIdx.x & 31) / LW);
+    const bool live = row < rows;   // (the other half of a warp may still hold a row: no early return before the shuffles)
+    const int nvec = live ? cols >> 2 : 0;
     const size_t base = (size_t)row * cols;
     float4 v[MAXV];
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
-        const int idx = lane + i * 32;
+        const int idx = lane + i * LW;
         if (idx < nvec) {
             v[i] = load4(x, base + idx * 4, dt);
             s += v[i].x + v[i].y + v[i].z + v[i].w;
         }
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    for (int o = LW / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     const float mean = s / (float)cols;
     float q = 0.f;
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
-        const int idx = lane + i * 32;
+        const int idx = lane + i * LW;
         if (idx < nvec) {
             float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
             q += a * a + b * b + c * c + d * d;
         }
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+    for (int o = LW / 2; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
     const float rstd = rsqrtf(q / (float)cols + eps);
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
-        const int idx = lane + i * 32;
+        const int idx = lane + i * LW;
         if (idx < nvec) {
             float4 g = *reinterpret_cast<const float4*>(gamma + idx * 4);
             float4 b = *reinterpret_cast<const float4*>(beta + idx * 4);
@@ -757,27 +765,30 @@ extern "C" int32_t b200sd_layernorm(const b200sd_layernorm_params* p, b200sd_str
                      "layernorm: pointers must be 16-byte aligned");
     if (p->rows <= 0) return B200SD_OK;
     const int wpb = 8;
-    const unsigned grid = (unsigned)((p->rows + wpb - 1) / wpb);
     // registers per thread follow the row length (4 * MAXV floats), so short rows run at full occupancy
-    const int nv = (p->cols / 4 + 31) / 32;
-#define B200SD_LN_LAUNCH_T(MV, D, O)                                                                                 \
-    B200SD_LAUNCH("layernorm_kernel", (layernorm_kernel<MV, D, O>), dim3(grid), dim3(wpb * 32), 0, as_stream(stream), p->x, p->rows, \
+    const int nvec4 = p->cols / 4;
+    const bool half_warp = nvec4 <= 80;           // two rows per warp, 16 lanes each, up to 5 vectors per lane
+    const int nv = (nvec4 + 31) / 32;
+    const long long rows_per_block = (long long)wpb * (half_warp ? 2 : 1);
+    const unsigned grid = (unsigned)((p->rows + rows_per_block - 1) / rows_per_block);
+#define B200SD_LN_LAUNCH_T(MV, D, O, LW)                                                                             \
+    B200SD_LAUNCH("layernorm_kernel", (layernorm_kernel<MV, D, O, LW>), dim3(grid), dim3(wpb * 32), 0, as_stream(stream), p->x, p->rows, \
                   p->cols, p->eps, p->gamma, p->beta, p->y)
-#define B200SD_LN_LAUNCH_O(MV, D)                                                     \
+#define B200SD_LN_LAUNCH_O(MV, D, LW)                                                 \
     do {                                                                              \
-        if (p->out_dtype == B200SD_F16) B200SD_LN_LAUNCH_T(MV, D, true);              \
-        else B200SD_LN_LAUNCH_T(MV, D, false);                                        \
+        if (p->out_dtype == B200SD_F16) B200SD_LN_LAUNCH_T(MV, D, true, LW);          \
+        else B200SD_LN_LAUNCH_T(MV, D, false, LW);                                    \
     } while (0)
-#define B200SD_LN_LAUNCH(MV)                                                          \
+#define B200SD_LN_LAUNCH(MV, LW)                                                      \
     do {                                                                              \
-        if (p->in_dtype == B200SD_F32) B200SD_LN_LAUNCH_O(MV, B200SD_F32);            \
-        else if (p->in_dtype == B200SD_F16) B200SD_LN_LAUNCH_O(MV, B200SD_F16);       \
-        else B200SD_LN_LAUNCH_O(MV, B200SD_BF16);                                     \
+        if (p->in_dtype == B200SD_F32) B200SD_LN_LAUNCH_O(MV, B200SD_F32, LW);        \
+        else if (p->in_dtype == B200SD_F16) B200SD_LN_LAUNCH_O(MV, B200SD_F16, LW);   \
+        else B200SD_LN_LAUNCH_O(MV, B200SD_BF16, LW);                                 \
     } while (0)
-    if (nv <= 3) B200SD_LN_LAUNCH(3);
-    else if (nv <= 5) B200SD_LN_LAUNCH(5);
-    else if (nv <= 10) B200SD_LN_LAUNCH(10);
-    else B200SD_LN_LAUNCH(12);
+    if (half_warp) B200SD_LN_LAUNCH(5, 16);
+    else if (nv <= 5) B200SD_LN_LAUNCH(5, 32);
+    else if (nv <= 10) B200SD_LN_LAUNCH(10, 32);
+    else B200SD_LN_LAUNCH(12, 32);
 #undef B200SD_LN_LAUNCH_T
 #undef B200SD_LN_LAUNCH_O
 #undef B200SD_LN_LAUNCH

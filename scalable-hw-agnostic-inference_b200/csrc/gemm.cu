@@ -213,14 +213,23 @@ __device__ __forceinline__ void stage_rows_out(const GemmKernelParams& p, float*
     if (p.out_dtype == B200SD_F32) {
         stage_rows(stg, lane, v);
     } else {
-        const bool f16 = p.out_dtype == B200SD_F16;
         uint8_t* row = reinterpret_cast<uint8_t*>(stg) + lane * 64;
         const int sw = (lane >> 1) & 3;
+        // one uniform branch around the sixteen conversions: chosen per conversion, the compiler issues BOTH encodings
+        // under opposite predicates (32 issue slots instead of 16 per chunk)
+        if (p.out_dtype == B200SD_F16) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-            *reinterpret_cast<uint4*>(row + ((j ^ sw) << 4)) =
-                make_uint4(pack_h2(v[8 * j], v[8 * j + 1], f16), pack_h2(v[8 * j + 2], v[8 * j + 3], f16),
-                           pack_h2(v[8 * j + 4], v[8 * j + 5], f16), pack_h2(v[8 * j + 6], v[8 * j + 7], f16));
+            for (int j = 0; j < 4; ++j)
+                *reinterpret_cast<uint4*>(row + ((j ^ sw) << 4)) =
+                    make_uint4(pack_f16x2(v[8 * j], v[8 * j + 1]), pack_f16x2(v[8 * j + 2], v[8 * j + 3]),
+                               pack_f16x2(v[8 * j + 4], v[8 * j + 5]), pack_f16x2(v[8 * j + 6], v[8 * j + 7]));
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                *reinterpret_cast<uint4*>(row + ((j ^ sw) << 4)) =
+                    make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                               pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+        }
     }
 }
 // Transposed lane mapping.  fp32 outputs: 8 passes, row = 4*i + lane/8, columns 4*(lane%8)..+3.
@@ -745,11 +754,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                             tmem_ld_wait();
                             float v[32];
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                v[4 * j + 0] = __uint_as_float(r[4 * j + 0]) + bq[j].x;
-                                v[4 * j + 1] = __uint_as_float(r[4 * j + 1]) + bq[j].y;
-                                v[4 * j + 2] = __uint_as_float(r[4 * j + 2]) + bq[j].z;
-                                v[4 * j + 3] = __uint_as_float(r[4 * j + 3]) + bq[j].w;
+                            for (int j = 0; j < 8; ++j) {  // bias adds on packed pairs (FADD2)
+                                unpack2(add2(pack2(__uint_as_float(r[4 * j + 0]), __uint_as_float(r[4 * j + 1])), pack2(bq[j].x, bq[j].y)),
+                                        v[4 * j + 0], v[4 * j + 1]);
+                                unpack2(add2(pack2(__uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3])), pack2(bq[j].z, bq[j].w)),
+                                        v[4 * j + 2], v[4 * j + 3]);
                             }
                             if (p.act) {
 #pragma unroll
@@ -1104,11 +1113,20 @@ static int32_t make_plan(const b200sd_gemm_params* p, bool have_ws, GemmPlan* pl
     const bool wide = kp.geglu ? (p->n_out % 256 == 0) : (p->n_out >= 512 || p->n_out % 256 == 0);
     // 320 output channels (the 96x96 level) pair up on 160-column tiles
     const bool wide160 = !kp.geglu && !wide && p->n_out >= 320 && p->n_out % 160 == 0;
-    const int pair_bn = wide160 ? 160 : 256;
+    int pair_bn = wide160 ? 160 : 256;
+    const long long clusters = num_sms() / 2;
+    if (wide && !kp.geglu && p->n_out % 160 == 0) {
+        // both widths tile the output exactly (1280 = 5 x 256 = 8 x 160): take the one with the lower waves x per-CTA
+        // operand rows, the same fetch-bound model as pick_block_n_auto.  The 12x12 level at batch 16 (36 row tiles) is
+        // 90 pair tiles of 256 = 1.2 waves of 74 clusters, but 144 of 160 = 1.95 waves.
+        const long long pm = (kp.m_tiles + 1) / 2;
+        const long long t256 = pm * ((p->n_out + 255) / 256), t160 = pm * (p->n_out / 160);
+        const long long c256 = ((t256 + clusters - 1) / clusters) * (128 + 128), c160 = ((t160 + clusters - 1) / clusters) * (128 + 80);
+        if (c160 < c256) pair_bn = 160;
+    }
     const long long pair_tiles = (long long)((kp.m_tiles + 1) / 2) * ((p->n_out + pair_bn - 1) / pair_bn);
     // ... and long enough to pay for the cluster start-up: at least one full wave of clusters and >= 64 k-blocks per
     // cluster in total (measured at batch 1: launches of 20-50 us lost 1-5 us each as pairs, the long ones gained 10-18 %)
-    const long long clusters = num_sms() / 2;
     const long long num_kb_total = (long long)p->taps * kp.kb_per_tap;
     plan->pair = (pair_allowed && (wide || wide160) && splits == 1 && (p->block_n == 0 || p->block_n == pair_bn) &&
                   kp.m_tiles >= 2 &&
