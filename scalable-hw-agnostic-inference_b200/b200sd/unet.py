@@ -106,6 +106,11 @@ class B200UNet(torch.nn.Module):
         self.temb_all_b = torch.cat(self._temb_b).contiguous()
         del self._temb_w, self._temb_b
         self._ctx_cache = None
+        # proj_out adds onto the block's input in place.  With its column sums (default) it takes the staged epilogue, which
+        # reads the residual; without them (B200SD_POUT_SUMS=0) a 16-bit trunk takes the TMA reduce-add and the next
+        # GroupNorm runs its own statistics pass.
+        import os
+        self._pout_sums = os.environ.get("B200SD_POUT_SUMS", "1") != "0"
 
     # ---- attributes the diffusers pipeline reads -------------------------------------------------------
     @property
@@ -179,7 +184,7 @@ class B200UNet(torch.nn.Module):
         # (the block's output is normalised next -- by the following resnet's norm1, possibly after a detour through the
         # skip stack -- so the epilogue leaves its column sums where the tiling allows; that epilogue reads the residual)
         xr = x.view(m, c)
-        o = K.linear(t2, T.pout_w, T.pout_b, residual=xr, out=xr, gn_rows_per_image=s)
+        o = K.linear(t2, T.pout_w, T.pout_b, residual=xr, out=xr, gn_rows_per_image=s if self._pout_sums else 0)
         return keep_tile_sums(o.view(n, h, w, c), o)
 
     # ---- the whole forward on NHWC tensors ---------------------------------------------------------------

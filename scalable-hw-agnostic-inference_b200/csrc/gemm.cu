@@ -1110,7 +1110,12 @@ static int32_t make_plan(const b200sd_gemm_params* p, bool have_ws, GemmPlan* pl
     // CTA pairs: wide outputs with enough 256-row tiles to fill the machine; B200SD_GEMM_PAIR=0 switches them off
     static const char* pair_env = getenv("B200SD_GEMM_PAIR");
     const bool pair_allowed = !(pair_env && pair_env[0] == '0');
+    static const long long pair_min_kb = [] { const char* e = getenv("B200SD_GEMM_PAIR_MIN_KB"); return e ? atoll(e) : 12LL; }();
     const bool wide = kp.geglu ? (p->n_out % 256 == 0) : (p->n_out >= 512 || p->n_out % 256 == 0);
+    // wide linear layers whose epilogue only stores (TMA store, nothing read back) also gain from pairs at K = 320..704
+    // (measured: 294912 x 960 x 320 231 -> 209 us); with a staged residual epilogue they lose (190 -> 203 us)
+    const bool store_only = wide && p->taps == 1 && p->img_h == 1 && p->n_img == 1 && !p->residual && !p->tile_sums &&
+                            !p->bias_along_m;
     // 320 output channels (the 96x96 level) pair up on 160-column tiles
     const bool wide160 = !kp.geglu && !wide && p->n_out >= 320 && p->n_out % 160 == 0;
     int pair_bn = wide160 ? 160 : 256;
@@ -1131,7 +1136,7 @@ static int32_t make_plan(const b200sd_gemm_params* p, bool have_ws, GemmPlan* pl
     plan->pair = (pair_allowed && (wide || wide160) && splits == 1 && (p->block_n == 0 || p->block_n == pair_bn) &&
                   kp.m_tiles >= 2 &&
                   pair_tiles >= clusters && pair_tiles * num_kb_total >= 64 * clusters &&
-                  (num_kb_total >= 12 || kp.geglu)) ? 1 : 0;  // K < 768 with a residual epilogue: measured 10-20 % slower
+                  (num_kb_total >= pair_min_kb || kp.geglu || (store_only && num_kb_total >= 5))) ? 1 : 0;  // K < 768 with a residual epilogue: measured 10-20 % slower
                                                               // as pairs (the epilogue, not the operand fetch, is the bound)
     if (plan->pair) block_n = pair_bn;
     kp.n_tiles = (p->n_out + block_n - 1) / block_n;
