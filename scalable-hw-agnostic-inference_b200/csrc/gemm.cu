@@ -32,6 +32,7 @@ constexpr int MAX_SPLITS = 8;
 constexpr int AUTO_SPLITS = 3;          // automatic K split factor (see plan_tiles)
 constexpr int AUTO_SPLIT_MIN_KB = 128;  // ... only for K >= 8192
 constexpr int AUTO_SPLIT_MAX_M_TILES = 4;  // ... and at most 512 output rows
+constexpr int AUTO_FILL_MIN_KB = 64;       // second automatic rule: fill the machine when tiles <= SMs / 2 and K >= 4096
 constexpr int WS_COUNTERS = 1024;  // int32 tile counters at the start of the split-K workspace
 
 struct GemmKernelParams {
@@ -978,6 +979,13 @@ static void plan_tiles(int n_out, int geglu, long long m_tiles, int num_kb, int 
             s = AUTO_SPLITS;
         }
     }
+    if (s == 1 && user_split == 0 && !user_block_n && num_kb >= AUTO_FILL_MIN_KB && tiles * 2 <= sms) {
+        // Under-filled problems with a long K loop (the 24x24 level at CFG batch 2: 72 tiles of 180 k-blocks on 148 SMs):
+        // as many splits as fit the machine.  Shorter loops stay whole -- parking and re-reading the partial tiles costs
+        // more than the idle SMs.
+        s = (int)(sms / tiles);
+        if (s > num_kb / 16) s = num_kb / 16;
+    }
     if (s > MAX_SPLITS) s = MAX_SPLITS;
     if (s > num_kb) s = num_kb;
     if (s >= 2 && tiles <= WS_COUNTERS) *splits = s;
@@ -1157,6 +1165,13 @@ extern "C" int32_t b200sd_gemm_pick_block_n(int32_t n_out, int32_t geglu) {
 extern "C" int32_t b200sd_gemm_tile_sum_parts(const b200sd_gemm_params* p) {
     if (!p) return 0;
     GemmPlan plan;
+    {
+        // an under-filled problem is better served by splitting K (which rules the column sums out: they come from
+        // whole-K accumulators) -- its output is small, so the statistics pass it then needs is cheap
+        b200sd_gemm_params w = *p;
+        w.split_k = 0;
+        if (make_plan(&w, true, &plan) == B200SD_OK && plan.kp.splits > 1) return 0;
+    }
     // planned as b200sd_gemm will plan it when it is handed tile_sums: never split along K
     b200sd_gemm_params q = *p;
     q.split_k = 1;
