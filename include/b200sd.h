@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200SD_ABI_VERSION 7
+#define B200SD_ABI_VERSION 8
 
 typedef struct CUstream_st* b200sd_stream_t; /* == cudaStream_t / CUstream */
 
@@ -130,6 +130,11 @@ typedef struct {
     int32_t causal;         /* 1 = key j is visible to query i only if j <= i (text encoder); needs sq == skv */
 } b200sd_attention_params;
 int32_t b200sd_attention(const b200sd_attention_params* p, b200sd_stream_t stream);
+/* Same parameters for ONE head of dimension 512 (heads == 1, head_dim == 512, causal == 0): the mid-block attention of
+ * AutoencoderKL's decoder and encoder (diffusers Attention inside UNetMidBlock2D, reached through pipe.vae.decode at
+ * app/run-sd.py:140).  Flash form as well: the score matrix never leaves the SM.  Each CTA computes the scores of its
+ * 128 query rows against every key over all 512 dims and one 256-column half of the output. */
+int32_t b200sd_attention512(const b200sd_attention_params* p, b200sd_stream_t stream);
 
 /* ---- K1b: GroupNorm(32) (+SiLU) over NHWC, optional channel-concat of two inputs ------------------
  * Replaces torch.nn.GroupNorm + F.silu in ResnetBlock2D.norm1/norm2, Transformer2DModel.norm,

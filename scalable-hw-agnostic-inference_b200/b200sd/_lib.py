@@ -7,7 +7,7 @@ from pathlib import Path
 
 _HERE = Path(__file__).resolve().parent
 LIB_PATH = _HERE / "libb200sd.so"
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 BF16, F32, F16 = 1, 2, 3
 
@@ -98,6 +98,7 @@ SYMBOLS = {
     "b200sd_gemm_tile_sum_parts": (c_i32, [C.POINTER(GemmParams)]),
     "b200sd_gn_tile_sums": (c_i32, [C.POINTER(GnTileSumsParams), c_vp]),
     "b200sd_attention": (c_i32, [C.POINTER(AttentionParams), c_vp]),
+    "b200sd_attention512": (c_i32, [C.POINTER(AttentionParams), c_vp]),
     "b200sd_groupnorm_workspace_bytes": (c_i64, [C.POINTER(GroupNormParams)]),
     "b200sd_groupnorm": (c_i32, [C.POINTER(GroupNormParams), c_vp]),
     "b200sd_groupnorm_static_scratch": (c_i32, [C.POINTER(GroupNormParams), c_vp]),

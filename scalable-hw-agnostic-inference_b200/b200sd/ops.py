@@ -154,6 +154,17 @@ def _attention(q, k, v, out, batch, heads, sq, skv, scale, causal=False):
          f"b{batch} h{heads} sq{sq} skv{skv}")
 
 
+def _attention512(q, k, v, out, batch, sq, skv, scale):
+    """one head of dimension 512 (the VAE mid block); q / k / v / out [batch * s, 512] views, any leading dimension"""
+    assert q.dtype == k.dtype == v.dtype == out.dtype and q.shape[-1] == 512
+    p = L.AttentionParams()
+    p.q, p.k, p.v, p.out = _ptr(q), _ptr(k), _ptr(v), _ptr(out)
+    p.ld_q, p.ld_k, p.ld_v, p.ld_out = q.stride(-2), k.stride(-2), v.stride(-2), out.stride(-2)
+    p.dtype, p.batch, p.heads, p.head_dim, p.sq, p.skv, p.scale = _dt(q), batch, 1, 512, sq, skv, scale
+    p.causal = 0
+    _run("attention", 4.0 * batch * sq * skv * 512, L.load().b200sd_attention512, p, f"b{batch} h1 d512 sq{sq} skv{skv}")
+
+
 def groupnorm_workspace_bytes(n_img: int, hw: int, groups: int = 32) -> int:
     p = L.GroupNormParams()
     p.n_img, p.hw, p.groups = n_img, hw, groups
@@ -285,6 +296,8 @@ _SCHEMAS = {
              _gemm),
     "attention": ("(Tensor q, Tensor k, Tensor v, Tensor(a!) out, int batch, int heads, int sq, int skv, float scale, "
                   "bool causal=False) -> ()", _attention),
+    "attention512": ("(Tensor q, Tensor k, Tensor v, Tensor(a!) out, int batch, int sq, int skv, float scale) -> ()",
+                     _attention512),
     "embed_tokens": ("(Tensor ids, Tensor token_table, Tensor position_table, Tensor(a!) out) -> ()", _embed_tokens),
     "groupnorm": ("(Tensor x1, Tensor? x2, int n_img, int hw, int groups, float eps, Tensor? gamma, Tensor? beta, bool silu, "
                   "Tensor(a!)? y, Tensor(b!)? raw, Tensor(c!)? workspace, Tensor? sums=None, int stat_hw=0, "
@@ -322,6 +335,7 @@ def _register() -> None:
 _register()
 gemm = torch.ops.b200sd.gemm
 attention = torch.ops.b200sd.attention
+attention512 = torch.ops.b200sd.attention512
 groupnorm = torch.ops.b200sd.groupnorm
 gn_tile_sums = torch.ops.b200sd.gn_tile_sums
 layernorm = torch.ops.b200sd.layernorm

@@ -4,7 +4,8 @@ app/run-sd.py:124-134 and reaches through `vae.decode(latents / scaling_factor)`
 The 1x1 post_quant_conv is folded exactly into conv_in: the latent gets a fifth, all-ones channel so that the
 folded bias is present at in-image taps and absent in the zero padding, as in the unfused pair.  `B200PostQuantConv`
 is the identity that takes post_quant_conv's place on the pipeline object.
-Mid-block attention (1 head x 512) runs as GEMM (fp32 scores) -> row softmax -> GEMM on the same tcgen05 kernel.
+Mid-block attention (1 head x 512) runs on the d = 512 flash kernel (`attention512.cu`); other widths (toy
+configurations) as GEMM (fp32 scores) -> row softmax -> GEMM on the tcgen05 GEMM kernel.
 """
 from __future__ import annotations
 
@@ -35,6 +36,11 @@ class _MidAttention:
         self.wk, self.bk = b("to_k.weight"), f("to_k.bias")
         self.wv, self.bv = b("to_v.weight"), f("to_v.bias")
         self.wo, self.bo = b("to_out.0.weight"), f("to_out.0.bias")
+        # fused Q|K|V projection for the flash path (head dimension 512)
+        self.wqkv = torch.cat([self.wq, self.wk, self.wv]).contiguous()
+        self.bqkv = torch.cat([self.bq, self.bk, self.bv]).contiguous()
+        import os
+        self.flash = os.environ.get("B200SD_VAE_FLASH", "1") != "0"
 
     def __call__(self, K: Kernels, h: torch.Tensor) -> torch.Tensor:
         BF = K.op_dtype
@@ -42,6 +48,15 @@ class _MidAttention:
         n, hh, ww, c = h.shape
         s = hh * ww
         a = K.groupnorm(h, None, self.at_g, self.at_b, 1e-6, False).view(n, s, c)
+        if c == 512 and self.flash:
+            # one head of dimension 512: the flash kernel (the score matrix never leaves the SM); all images in one launch
+            qkv = K.linear(a.view(n * s, c), self.wqkv, self.bqkv, out_dtype=BF)
+            o = torch.empty(n * s, c, device=dev, dtype=BF)
+            ops.attention512(qkv[:, :c], qkv[:, c:2 * c], qkv[:, 2 * c:], o, n, s, s, float(c) ** -0.5)
+            hr = h.view(n * s, c)
+            r = K.linear(o, self.wo, self.bo, residual=hr, out=hr, gn_rows_per_image=s)
+            return keep_tile_sums(r.view(n, hh, ww, c), r)
+        # other widths (toy configurations): GEMM (fp32 scores) -> row softmax -> GEMM, image by image
         q = K.linear(a, self.wq, self.bq, out_dtype=BF)
         k = K.linear(a, self.wk, self.bk, out_dtype=BF)
         o = torch.empty(n, s, c, device=dev, dtype=BF)

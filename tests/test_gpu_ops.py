@@ -426,6 +426,39 @@ print('ok', worst)
     assert r.returncode == 0 and r.stdout.strip().startswith("ok"), r.stdout[-2000:] + r.stderr[-4000:]
 
 
+@pytest.mark.parametrize("batch,s", [(1, 128), (2, 256), (1, 1024), (3, 320), (2, 77), (1, 2304)])
+def test_flash_attention_head_dim_512(K, cuda, batch, s):
+    """the VAE mid block's single 512-wide head: full, ragged and multi-tile sequences, strided Q|K|V views of one fused
+    projection, against explicit softmax(q k^T / sqrt(512)) v"""
+    from b200sd import ops
+    dt = K.op_dtype
+    c = 512
+    qkv = rnd(batch * s, 3 * c, dev=cuda, seed=s, dtype=dt)
+    q, k, v = qkv[:, :c], qkv[:, c:2 * c], qkv[:, 2 * c:]
+    guard = torch.full((batch * s + 2, c), 7.0, device=cuda, dtype=dt)
+    out = guard[1:-1]
+    ops.attention512(q, k, v, out, batch, s, s, c ** -0.5)
+    qf, kf, vf = (t.float().view(batch, s, c) for t in (q, k, v))
+    ref = (torch.softmax(qf @ kf.transpose(-1, -2) * c ** -0.5, -1) @ vf).reshape(batch * s, c)
+    assert rel(out, ref) < 2 * out_tol(dt)
+    assert float(guard[0].float().min()) == 7.0 and float(guard[-1].float().max()) == 7.0   # nothing outside the output
+
+
+def test_flash_attention_head_dim_512_large_logits(K, cuda):
+    """running max grows by far more than 2^8 between kv tiles -> the lazy O rescale over all 256 O columns runs"""
+    from b200sd import ops
+    dt = K.op_dtype
+    s, c = 512, 512
+    q = rnd(s, c, dev=cuda, seed=1, dtype=dt)
+    k = rnd(s, c, dev=cuda, seed=2, dtype=dt)
+    k[256:] *= 6.0
+    v = rnd(s, c, dev=cuda, seed=3, dtype=dt)
+    out = torch.empty(s, c, device=cuda, dtype=dt)
+    ops.attention512(q, k, v, out, 1, s, s, 0.25)
+    ref = torch.softmax(q.float() @ k.float().t() * 0.25, -1) @ v.float()
+    assert rel(out, ref) < 2 * out_tol(dt)
+
+
 # ------------------------------------------------------------------------------------------------ text-encoder ops
 @pytest.mark.parametrize("batch,heads,s", [(3, 2, 77), (2, 16, 77), (1, 2, 33), (2, 2, 300), (1, 1, 640)])
 def test_flash_attention_causal(K, cuda, batch, heads, s):

@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol(lib_built):
     lib = ctypes.CDLL(str(lib_built))
     for name in declared:
         assert hasattr(lib, name), name
-    assert _lib.load().b200sd_abi_version() == _lib.ABI_VERSION == 7
+    assert _lib.load().b200sd_abi_version() == _lib.ABI_VERSION == 8
 
 
 def test_ctypes_struct_layout_matches_c(lib_built, tmp_path):
