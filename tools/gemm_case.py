@@ -30,6 +30,9 @@ CASES = {  # name: (M, K, N, residual, geglu, out fp32)
     "ff2_320_16_inplace": (294912, 1280, 320, True, False, False),
     "res640_16": (73728, 640, 640, True, False, False),
     "qkv960": (294912, 320, 960, False, False, False),          # fused QKV projection of the 96x96 level
+    "res640_16_inplace": (73728, 640, 640, True, False, False),
+    "ff2_640_16_inplace": (73728, 2560, 640, True, False, False),
+    "qkv1920": (73728, 640, 1920, False, False, False),
 }
 M, Kd, N, has_res, geglu, out32 = CASES[case]
 a = torch.randn(M, Kd, device=dev).to(dt)
