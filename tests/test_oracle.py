@@ -23,6 +23,45 @@ def test_vae_decoder_param_count_matches_sd21():
     assert sum(p.numel() for p in v.parameters()) == 49_490_179 + 20
 
 
+def test_vae_encoder_param_count_and_keys_match_sd21():
+    """AutoencoderKL.encode restatement: the published sizes (encoder 34,163,592, quant_conv 72; with the decoder half
+    the AutoencoderKL total 83,653,863) and diffusers' key names"""
+    e = O.VAEEncoder()
+    assert sum(p.numel() for p in e.encoder.parameters()) == 34_163_592
+    assert sum(p.numel() for p in e.quant_conv.parameters()) == 72
+    v = O.VAEDecoder()
+    assert sum(p.numel() for m in (e, v) for p in m.parameters()) == 83_653_863
+    keys = set(e.state_dict().keys())
+    for k in ["encoder.conv_in.weight", "encoder.down_blocks.0.resnets.1.conv2.bias",
+              "encoder.down_blocks.1.resnets.0.conv_shortcut.weight", "encoder.down_blocks.2.downsamplers.0.conv.weight",
+              "encoder.mid_block.attentions.0.to_q.bias", "encoder.mid_block.attentions.0.group_norm.weight",
+              "encoder.mid_block.resnets.1.norm2.weight", "encoder.conv_norm_out.bias", "encoder.conv_out.weight",
+              "quant_conv.bias"]:
+        assert k in keys, k
+    assert "encoder.down_blocks.3.downsamplers.0.conv.weight" not in keys   # the last block does not downsample
+
+
+def test_vae_encoder_downsample_padding_and_gaussian_sample():
+    """Downsample2D(padding=0) pads (0,1,0,1): an impulse in the LAST row / column must reach the output, one in a
+    virtual row -1 cannot; the distribution's sample follows mean + exp(0.5 * clamp(logvar)) * noise"""
+    d = O.EncoderDownsample2D(1)
+    with torch.no_grad():
+        d.conv.weight.fill_(1.0)
+        d.conv.bias.zero_()
+        x = torch.zeros(1, 1, 6, 6)
+        x[0, 0, 5, 5] = 1.0
+        y = d(x)
+        assert y.shape == (1, 1, 3, 3) and float(y[0, 0, 2, 2]) == 1.0 and float(y.sum()) == 1.0
+        x = torch.zeros(1, 1, 6, 6)
+        x[0, 0, 0, 0] = 1.0
+        assert float(d(x)[0, 0, 0, 0]) == 1.0 and float(d(x).sum()) == 1.0   # window 0 starts AT row 0: nothing before it
+    m = torch.tensor([1.0, -2.0, 0.0, 40.0]).view(1, 4, 1, 1)   # mean (1, -2), logvar (0, 40 -> clamped to 20)
+    n = torch.tensor([0.5, 1.0]).view(1, 2, 1, 1)
+    z = O.gaussian_sample(m, n)
+    assert torch.allclose(z.flatten(), torch.tensor([1.0 + 0.5, -2.0 + float(torch.exp(torch.tensor(10.0)))]))
+    assert torch.equal(O.gaussian_sample(m), m[:, :2])
+
+
 def test_state_dict_keys_follow_diffusers_scheme():
     keys = set(O.UNet2DCondition(O.tiny_unet_config()).state_dict().keys())
     for k in ["conv_in.weight", "time_embedding.linear_1.weight", "time_embedding.linear_2.bias",
