@@ -1,7 +1,7 @@
 """Weight packing and the per-layer call helpers shared by B200UNet and B200VAEDecoder.
 
 Layouts: activations NHWC; every tensor-core operand 16-bit in `op_dtype` (fp16 by default,
-bf16 selectable -- see DESIGN.md "operand format"); the residual trunk in `trunk_dtype` (fp32 by default);
+bf16 selectable -- see DESIGN.md "operand format"); the residual trunk in `trunk_dtype` (fp16 by default, fp32 / bf16 selectable);
 conv weights KRSC [Cout, 9*Cin]; linear weights [out, in].
 """
 from __future__ import annotations

@@ -1,7 +1,8 @@
 """B200UNet -- drop-in for `pipe.unet` (diffusers UNet2DConditionModel; swapped at app/run-sd.py:110-116).
 
-Same call signature and config attributes the pipeline reads; internally NHWC, bf16 operands, every FLOP in
-libb200sd's sm_100a kernels (implicit-GEMM conv / linear on tcgen05, flash attention, fused norms).
+Same call signature and config attributes the pipeline reads; internally NHWC, 16-bit tensor-core operands (fp16 by
+default, bf16 selectable) and a 16-bit residual trunk, every FLOP in libb200sd's sm_100a kernels (implicit-GEMM conv /
+linear on tcgen05 whose epilogues also emit the next GroupNorm's statistics, flash attention, GroupNorm / LayerNorm).
 Weights come from a diffusers-layout state_dict and are packed once at construction.
 """
 from __future__ import annotations
